@@ -1,0 +1,207 @@
+/*
+ * pk_route.h — C ABI of the B200 batched request-routing stage (libpkroute.so).
+ *
+ * This is the drop-in boundary for the ExecuteTool hot path of
+ * spounge-ai/polykey-service.  The reference has no FFI of its own (it is pure Go,
+ * CGO_ENABLED=0, Makefile:69,71); the seam this library plugs into is the one-method
+ * plugin interface
+ *
+ *     service.Service.ExecuteTool(ctx, toolName, parameters, secretId, metadata)
+ *                                              (internal/service/service.go:13-15)
+ *
+ * injected at server.NewServer(polykeySvc) (cmd/polykey/main.go:85-86) and called
+ * at internal/server/server.go:36.  A Go `BatchingService` decorator coalesces the
+ * concurrent per-RPC calls into flat byte arenas and crosses cgo ONCE per batch
+ * through the entry points below (binding shown in INTEGRATION.md).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types cross the boundary.
+ *   - every function returns 0 (PK_OK) or a negative pk_status; nothing aborts or
+ *     throws.  CUDA runtime failures are folded into PK_ERR_CUDA and the numeric
+ *     cudaError_t is kept per handle (pk_last_cuda_error) — the Go side maps any
+ *     non-zero code to a gRPC status exactly as server.go:37-40 passes an error
+ *     through, and flips health to NOT_SERVING (cmd/polykey/main.go:93-94).
+ *   - the caller owns every buffer it passes; the library owns device memory,
+ *     streams and events.  Pointers must stay valid until the call (or, for
+ *     pk_submit, the matching pk_wait) returns.
+ *   - a handle may be used by ONE thread at a time (the batcher's flusher);
+ *     different handles (one per GPU) may be used concurrently.
+ *   - there is NO CPU fallback inside this library.
+ *
+ * Batch layout (flat SoA; see DESIGN.md "Data layout")
+ *   payload   : one contiguous byte arena; request i owns
+ *               payload[pay_off[i] .. pay_off[i] + pay_len[i]) where
+ *               pay_len[i] = pay_end(i) - pay_off[i].  pay_off has n+1 entries;
+ *               every pay_off[i] MUST be a multiple of 16 (PK_ALIGN); the bytes of
+ *               request i end at pay_off[i] + pay_len[i] <= pay_off[i+1] and the
+ *               gap up to pay_off[i+1] is padding whose content is ignored.
+ *               Because of the padding the true length travels separately in
+ *               pay_len[] (u32, one per request).
+ *   names     : packed tool-name bytes, request i owns
+ *               names[name_off[i] .. name_off[i+1]); no alignment requirement.
+ *   out       : n fixed-size decision records (24 bytes each).
+ */
+#ifndef PK_ROUTE_H
+#define PK_ROUTE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define PK_API __attribute__((visibility("default")))
+#else
+#define PK_API
+#endif
+
+#define PK_ABI_VERSION        1u
+#define PK_ALIGN              16u      /* payload start alignment in the arena      */
+#define PK_MAX_TOOLS          16u
+#define PK_MAX_TOOL_NAME      64u
+#define PK_MAX_PROVIDERS      32u
+#define PK_MAX_NAME_LEN       0xFFFFFFu /* a request's tool name, bytes              */
+#define PK_PROVIDER_NONE      0xFFu
+
+/* decision flags */
+#define PK_FLAG_NONASCII      0x0001u  /* payload holds a byte >= 0x80              */
+#define PK_FLAG_NO_PROVIDER   0x0002u  /* no provider eligible; provider = 0xFF     */
+#define PK_FLAG_EMPTY_PAYLOAD 0x0004u  /* pay_len == 0                              */
+#define PK_FLAG_UNKNOWN_TOOL  0x0008u  /* name matched no table entry: the default
+                                          branch of the switch, mock.go:60-64 —
+                                          still status 200, never an error          */
+
+typedef enum pk_status {
+    PK_OK              =  0,
+    PK_ERR_ARG         = -1,   /* null pointer / bad count / bad table              */
+    PK_ERR_ALIGN       = -2,   /* a pay_off[i] is not a multiple of PK_ALIGN        */
+    PK_ERR_OFFSETS     = -3,   /* offsets not monotone, or pay_len overruns a slot  */
+    PK_ERR_CAPACITY    = -4,   /* batch exceeds the limits given to pk_init         */
+    PK_ERR_CUDA        = -5,   /* CUDA runtime error; see pk_last_cuda_error        */
+    PK_ERR_NO_DEVICE   = -6,   /* no usable CUDA device / device ordinal invalid    */
+    PK_ERR_BUSY        = -7,   /* slot has a submit in flight (missing pk_wait)     */
+    PK_ERR_STATE       = -8    /* call not valid in this state (e.g. wait w/o submit)*/
+} pk_status;
+
+/* One entry of the tool table: the `case "...":` labels of the switch at
+ * internal/service/mock.go:32-59.  Matching is whole-name, case-sensitive byte
+ * equality (Go string switch semantics); the first matching entry wins. */
+typedef struct pk_tool {
+    uint8_t  name[PK_MAX_TOOL_NAME];
+    uint32_t name_len;
+    uint32_t class_id;            /* < 32 */
+} pk_tool;
+
+/* One provider row of the device-resident routing table (build-defined: the
+ * reference has no provider list — SURVEY.md §0.3, §8 a6). */
+typedef struct pk_provider {
+    uint32_t max_tokens;          /* eligible iff est_tokens <= max_tokens          */
+    uint32_t weight;              /* 0 disables the provider                        */
+    uint32_t tool_mask;           /* bit c set: serves tool class c                 */
+    uint32_t salt;                /* per-provider hash salt                         */
+} pk_provider;
+
+typedef struct pk_table {
+    uint32_t    n_tools;          /* <= PK_MAX_TOOLS                                */
+    uint32_t    default_class;    /* class of the `default:` branch, mock.go:60     */
+    uint32_t    n_providers;      /* <= PK_MAX_PROVIDERS                            */
+    uint32_t    reserved;
+    pk_tool     tools[PK_MAX_TOOLS];
+    pk_provider providers[PK_MAX_PROVIDERS];
+} pk_table;
+
+/* 24-byte decision record, one per request. */
+typedef struct pk_decision {
+    uint32_t byte_len;            /* payload length                                 */
+    uint32_t est_tokens;          /* token-count estimate (SPEC §B)                 */
+    uint64_t route_hash;          /* 64-bit route key hash (SPEC §C)                */
+    uint8_t  tool_class;          /* mock.go:32-64                                  */
+    uint8_t  provider;            /* index into table.providers, or 0xFF            */
+    uint16_t flags;               /* PK_FLAG_*                                      */
+    uint32_t status;              /* always 200: Status.Code, mock.go:25-28         */
+} pk_decision;
+
+typedef struct pk_config {
+    uint32_t max_requests;        /* per batch                                      */
+    uint32_t n_slots;             /* independent in-flight batches (>=1)            */
+    uint64_t max_payload_bytes;   /* arena bytes per batch (incl. padding)          */
+    uint64_t max_name_bytes;      /* name arena bytes per batch                     */
+} pk_config;
+
+typedef struct pk_handle pk_handle;
+
+/* Fills *t with the reference table: example_tool→0, struct_tool→1, file_tool→2,
+ * default→3 (mock.go:33,37,52,60) and 8 default providers.               */
+PK_API int  pk_default_table(pk_table* t);
+
+/* Replaces server start-up wiring at cmd/polykey/main.go:85-86: creates the CUDA
+ * context on `device`, uploads the routing table, allocates every device buffer,
+ * stream and event for cfg->n_slots batches.  Nothing is allocated afterwards.   */
+PK_API int  pk_init(int device, const pk_table* tbl, const pk_config* cfg, pk_handle** out);
+
+/* Teardown hook for cmd/polykey/main.go:118-119 (before GracefulStop returns).    */
+PK_API void pk_destroy(pk_handle* h);
+
+/* Re-uploads the routing table (stream-ordered after all submitted work).         */
+PK_API int  pk_update_table(pk_handle* h, const pk_table* tbl);
+
+/* THE hot call — the batched replacement for N calls of
+ * MockService.ExecuteTool's routing decision (internal/service/mock.go:22-67):
+ * H2D copies, the fused scan+hash+select kernel, D2H copy of the records, all on
+ * slot 0's stream, synchronous.  Host pointers.                                  */
+PK_API int  pk_route_batch(pk_handle* h,
+                    const uint8_t* payload, const uint64_t* pay_off /* n+1 */,
+                    const uint32_t* pay_len /* n */,
+                    const uint8_t* names, const uint32_t* name_off /* n+1 */,
+                    uint32_t n, pk_decision* out /* n */);
+
+/* Asynchronous form of the same call for a pipelined flusher: pk_submit enqueues
+ * H2D → kernel → D2H on slot `slot`'s stream and returns; pk_wait blocks until
+ * that slot's records are in `out`.  Use pinned buffers (pk_host_alloc) or the
+ * copies degrade to synchronous staging inside the CUDA driver.                 */
+PK_API int  pk_submit(pk_handle* h, uint32_t slot,
+               const uint8_t* payload, const uint64_t* pay_off, const uint32_t* pay_len,
+               const uint8_t* names, const uint32_t* name_off,
+               uint32_t n, pk_decision* out);
+PK_API int  pk_wait(pk_handle* h, uint32_t slot);
+
+/* Device-resident form (used to time the kernels alone, inputs already in HBM):
+ * pk_stage copies a batch into slot `slot` and returns when it is resident;
+ * pk_launch runs the kernels over the staged batch (no copies, asynchronous on the
+ * slot's stream); pk_launch_many issues `count` launches back to back, launch k
+ * using slot slots[k % n_slots_in_list], all on ONE stream (slot slots[0]'s), either
+ * as `count` plain launches or (use_graph != 0) as one CUDA graph of `count` kernel
+ * nodes; it brackets them with CUDA events on that stream, waits, and reports the
+ * device time in *elapsed_ms; pk_fetch copies the slot's records out (synchronous). */
+PK_API int  pk_stage(pk_handle* h, uint32_t slot,
+              const uint8_t* payload, const uint64_t* pay_off, const uint32_t* pay_len,
+              const uint8_t* names, const uint32_t* name_off, uint32_t n);
+PK_API int  pk_launch(pk_handle* h, uint32_t slot);
+PK_API int  pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_slots_in_list,
+                    uint32_t count, int use_graph, float* elapsed_ms /* may be NULL */);
+PK_API int  pk_fetch(pk_handle* h, uint32_t slot, pk_decision* out /* staged n */);
+PK_API int  pk_sync(pk_handle* h);                 /* waits for every slot's stream        */
+
+/* The cudaStream_t of a slot, as an opaque pointer, so a caller can record its own
+ * CUDA events on the launching stream (bench.py does).                            */
+PK_API void* pk_slot_stream(pk_handle* h, uint32_t slot);
+
+/* Number of kernel launches this handle has issued (bench.py's gpu_launches).     */
+PK_API uint64_t pk_launch_count(const pk_handle* h);
+
+/* Pinned host memory owned by the C side: gRPC buffers live on the Go heap and
+ * cannot be DMA sources, so the batcher copies each request into an arena from
+ * here (SURVEY.md §7 "Pinned host memory from Go").                              */
+PK_API void* pk_host_alloc(pk_handle* h, size_t bytes);
+PK_API void  pk_host_free(pk_handle* h, void* p);
+
+PK_API const char* pk_strerror(int status);
+PK_API int         pk_last_cuda_error(const pk_handle* h);   /* cudaError_t of last failure */
+PK_API uint32_t    pk_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PK_ROUTE_H */

@@ -1,0 +1,481 @@
+// pk_abi.cu — the C-ABI of libpkroute.so (declared in include/pk_route.h).
+//
+// Host side of the drop-in boundary: validates a flat batch, stages its small metadata
+// through one pinned blob, copies the payload arena, launches the fused kernel and copies
+// the 24-byte decision records back — all on the slot's own stream.  No CPU fallback:
+// if there is no CUDA device pk_init fails with PK_ERR_NO_DEVICE and nothing else works.
+#include <cuda_runtime.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/pk_route.h"
+#include "pk_kernels.cuh"
+#include "pk_spec.cuh"
+
+namespace {
+
+constexpr size_t kSectionAlign = 256;
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t  done = nullptr;
+    uint8_t*     d_payload = nullptr;
+    uint8_t*     d_meta = nullptr;
+    pk_decision* d_out = nullptr;
+    pk::SegScratch* d_scratch = nullptr;
+    uint8_t*     h_meta = nullptr;      // pinned staging for the metadata blob
+    uint32_t     n = 0;
+    bool         staged = false;        // params describe a resident batch
+    bool         inflight = false;      // pk_submit without pk_wait
+    pk::RouteParams params{};
+};
+
+}  // namespace
+
+struct pk_handle {
+    int        device = 0;
+    int        num_sms = 0;
+    pk_config  cfg{};
+    pk_table*  d_table = nullptr;
+    size_t     meta_cap = 0;
+    uint64_t   max_extra = 0;
+    std::vector<Slot> slots;
+    int        last_cuda = 0;
+    uint64_t   launches = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+namespace {
+
+#define PK_CUDA(h, call)                                   \
+    do {                                                   \
+        cudaError_t e__ = (call);                          \
+        if (e__ != cudaSuccess) {                          \
+            if (h) (h)->last_cuda = (int)e__;              \
+            (void)cudaGetLastError();                      \
+            return PK_ERR_CUDA;                            \
+        }                                                  \
+    } while (0)
+
+int validate_table(const pk_table* t)
+{
+    if (!t || t->n_tools > PK_MAX_TOOLS || t->n_providers > PK_MAX_PROVIDERS) return PK_ERR_ARG;
+    if (t->default_class >= 32) return PK_ERR_ARG;
+    for (uint32_t k = 0; k < t->n_tools; ++k)
+        if (t->tools[k].name_len > PK_MAX_TOOL_NAME || t->tools[k].class_id >= 32) return PK_ERR_ARG;
+    return PK_OK;
+}
+
+// Validates the batch and writes the metadata blob
+//   [pay_off (n+1) u64, rebased to 0][pay_len n u32][name_off (n+1) u32, rebased][extra (req,seg) u32x2][names]
+// into slot.h_meta; fills slot.params with device pointers.  Returns bytes used in *meta_bytes
+// and the payload byte range to copy in *pay_begin / *pay_bytes.
+int prepare(pk_handle* h, Slot& s, const uint64_t* pay_off, const uint32_t* pay_len,
+            const uint8_t* names, const uint32_t* name_off, uint32_t n, size_t* meta_bytes,
+            uint64_t* pay_begin, uint64_t* pay_bytes)
+{
+    if (n > h->cfg.max_requests) return PK_ERR_CAPACITY;
+    if (!pay_off || !pay_len || !name_off) return PK_ERR_ARG;
+
+    const size_t o_off   = 0;
+    const size_t o_len   = align_up(o_off + (size_t)(n + 1) * 8, kSectionAlign);
+    const size_t o_noff  = align_up(o_len + (size_t)n * 4, kSectionAlign);
+    const size_t o_extra = align_up(o_noff + (size_t)(n + 1) * 4, kSectionAlign);
+
+    uint64_t* m_off  = reinterpret_cast<uint64_t*>(s.h_meta + o_off);
+    uint32_t* m_len  = reinterpret_cast<uint32_t*>(s.h_meta + o_len);
+    uint32_t* m_noff = reinterpret_cast<uint32_t*>(s.h_meta + o_noff);
+    uint32_t* m_ext  = reinterpret_cast<uint32_t*>(s.h_meta + o_extra);
+
+    const uint64_t base = pay_off[0];
+    const uint32_t nbase = name_off[0];
+    uint64_t n_extra = 0;
+    uint64_t end = base;
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint64_t o = pay_off[i], nx = pay_off[i + 1];
+        const uint32_t l = pay_len[i];
+        if (o % PK_ALIGN) return PK_ERR_ALIGN;
+        if (nx < o || (uint64_t)l > nx - o) return PK_ERR_OFFSETS;
+        if (name_off[i + 1] < name_off[i]) return PK_ERR_OFFSETS;
+        if (name_off[i + 1] - name_off[i] > PK_MAX_NAME_LEN) return PK_ERR_ARG;
+        if (o - base + l > h->cfg.max_payload_bytes) return PK_ERR_CAPACITY;
+        m_off[i]  = o - base;
+        m_len[i]  = l;
+        m_noff[i] = name_off[i] - nbase;
+        if (l > pk::kSegBytes) {
+            const uint32_t nseg = (l + pk::kSegBytes - 1) / pk::kSegBytes;
+            if (n_extra + (nseg - 1) > h->max_extra) return PK_ERR_CAPACITY;
+            for (uint32_t g = 1; g < nseg; ++g) {
+                m_ext[2 * n_extra] = i;
+                m_ext[2 * n_extra + 1] = g;
+                ++n_extra;
+            }
+        }
+        end = o + l;
+    }
+    m_off[n]  = pay_off[n] - base;
+    m_noff[n] = name_off[n] - nbase;
+    const uint64_t name_bytes = (uint64_t)name_off[n] - nbase;
+    if (name_bytes > h->cfg.max_name_bytes) return PK_ERR_CAPACITY;
+    if (name_bytes && !names) return PK_ERR_ARG;
+    const size_t o_names = align_up(o_extra + (size_t)n_extra * 8, kSectionAlign);
+    if (o_names + name_bytes > h->meta_cap) return PK_ERR_CAPACITY;
+    if (name_bytes) std::memcpy(s.h_meta + o_names, names + nbase, name_bytes);
+
+    *meta_bytes = o_names + name_bytes;
+    *pay_begin = base;
+    *pay_bytes = end - base;
+
+    pk::RouteParams& P = s.params;
+    P.payload  = s.d_payload;
+    P.pay_off  = reinterpret_cast<const uint64_t*>(s.d_meta + o_off);
+    P.pay_len  = reinterpret_cast<const uint32_t*>(s.d_meta + o_len);
+    P.name_off = reinterpret_cast<const uint32_t*>(s.d_meta + o_noff);
+    P.extra    = reinterpret_cast<const uint2*>(s.d_meta + o_extra);
+    P.names    = s.d_meta + o_names;
+    P.table    = h->d_table;
+    P.scratch  = s.d_scratch;
+    P.out      = s.d_out;
+    P.n        = n;
+    P.n_extra  = (uint32_t)n_extra;
+    s.n = n;
+    return PK_OK;
+}
+
+int enqueue_uploads(pk_handle* h, Slot& s, const uint8_t* payload, size_t meta_bytes,
+                    uint64_t pay_begin, uint64_t pay_bytes)
+{
+    PK_CUDA(h, cudaMemcpyAsync(s.d_meta, s.h_meta, meta_bytes, cudaMemcpyHostToDevice, s.stream));
+    if (pay_bytes) {
+        if (!payload) return PK_ERR_ARG;
+        PK_CUDA(h, cudaMemcpyAsync(s.d_payload, payload + pay_begin, pay_bytes,
+                                   cudaMemcpyHostToDevice, s.stream));
+    }
+    return PK_OK;
+}
+
+int launch_slot(pk_handle* h, const Slot& s, cudaStream_t stream)
+{
+    if (s.params.n == 0) return PK_OK;
+    PK_CUDA(h, pk::launch_route(s.params, h->num_sms, stream));
+    ++h->launches;
+    return PK_OK;
+}
+
+void free_slot(Slot& s)
+{
+    if (s.d_payload) cudaFree(s.d_payload);
+    if (s.d_meta) cudaFree(s.d_meta);
+    if (s.d_out) cudaFree(s.d_out);
+    if (s.d_scratch) cudaFree(s.d_scratch);
+    if (s.h_meta) cudaFreeHost(s.h_meta);
+    if (s.done) cudaEventDestroy(s.done);
+    if (s.stream) cudaStreamDestroy(s.stream);
+    s = Slot{};
+}
+
+}  // namespace
+
+extern "C" {
+
+uint32_t pk_abi_version(void) { return PK_ABI_VERSION; }
+
+const char* pk_strerror(int status)
+{
+    switch (status) {
+    case PK_OK:            return "ok";
+    case PK_ERR_ARG:       return "invalid argument";
+    case PK_ERR_ALIGN:     return "payload offset is not a multiple of 16";
+    case PK_ERR_OFFSETS:   return "offsets are not monotone or a length overruns its slot";
+    case PK_ERR_CAPACITY:  return "batch exceeds the capacity given to pk_init";
+    case PK_ERR_CUDA:      return "CUDA runtime error (see pk_last_cuda_error)";
+    case PK_ERR_NO_DEVICE: return "no usable CUDA device";
+    case PK_ERR_BUSY:      return "slot busy: pk_submit without pk_wait";
+    case PK_ERR_STATE:     return "call not valid in this state";
+    default:               return "unknown pk_status";
+    }
+}
+
+int pk_last_cuda_error(const pk_handle* h) { return h ? h->last_cuda : 0; }
+uint64_t pk_launch_count(const pk_handle* h) { return h ? h->launches : 0; }
+
+int pk_default_table(pk_table* t)
+{
+    // the three case labels of internal/service/mock.go:33,37,52 and its default (:60)
+    static const char* const names[3] = {"example_tool", "struct_tool", "file_tool"};
+    static const uint32_t max_tokens[8] = {4096, 8192, 8192, 32768, 32768, 131072, 131072, 1048576};
+    if (!t) return PK_ERR_ARG;
+    std::memset(t, 0, sizeof *t);
+    t->n_tools = 3;
+    t->default_class = 3;
+    for (uint32_t k = 0; k < 3; ++k) {
+        t->tools[k].name_len = (uint32_t)std::strlen(names[k]);
+        std::memcpy(t->tools[k].name, names[k], t->tools[k].name_len);
+        t->tools[k].class_id = k;
+    }
+    t->n_providers = 8;
+    for (uint32_t p = 0; p < 8; ++p) {
+        t->providers[p].max_tokens = max_tokens[p];
+        t->providers[p].weight = p + 1;
+        t->providers[p].tool_mask = (p % 4 == 3) ? 0x7u : 0xFu;
+        t->providers[p].salt = (p + 1u) * 0x9E3779B9u;
+    }
+    return PK_OK;
+}
+
+int pk_init(int device, const pk_table* tbl, const pk_config* cfg, pk_handle** out)
+{
+    if (!out) return PK_ERR_ARG;
+    *out = nullptr;
+    if (!cfg || cfg->n_slots == 0 || cfg->n_slots > 4096 || cfg->max_requests == 0) return PK_ERR_ARG;
+    int rc = validate_table(tbl);
+    if (rc) return rc;
+
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { (void)cudaGetLastError(); return PK_ERR_NO_DEVICE; }
+    if (device < 0 || device >= count) return PK_ERR_NO_DEVICE;
+
+    pk_handle* h = new (std::nothrow) pk_handle();
+    if (!h) return PK_ERR_ARG;
+    h->device = device;
+    h->cfg = *cfg;
+
+#define PK_INIT_CUDA(call)                                              \
+    do {                                                                \
+        cudaError_t e__ = (call);                                       \
+        if (e__ != cudaSuccess) {                                       \
+            h->last_cuda = (int)e__;                                    \
+            (void)cudaGetLastError();                                   \
+            pk_destroy(h);                                              \
+            return PK_ERR_CUDA;                                         \
+        }                                                               \
+    } while (0)
+
+    PK_INIT_CUDA(cudaSetDevice(device));
+    PK_INIT_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
+    PK_INIT_CUDA(cudaMalloc(&h->d_table, sizeof(pk_table)));
+    PK_INIT_CUDA(cudaMemcpy(h->d_table, tbl, sizeof(pk_table), cudaMemcpyHostToDevice));
+    PK_INIT_CUDA(cudaEventCreate(&h->ev0));
+    PK_INIT_CUDA(cudaEventCreate(&h->ev1));
+
+    const size_t n = cfg->max_requests;
+    h->max_extra = cfg->max_payload_bytes / pk::kSegBytes + 1;
+    h->meta_cap = align_up((n + 1) * 8, kSectionAlign) + align_up(n * 4, kSectionAlign) +
+                  align_up((n + 1) * 4, kSectionAlign) + align_up(h->max_extra * 8, kSectionAlign) +
+                  align_up(cfg->max_name_bytes, kSectionAlign) + kSectionAlign;
+
+    h->slots.resize(cfg->n_slots);
+    for (Slot& s : h->slots) {
+        PK_INIT_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        PK_INIT_CUDA(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        PK_INIT_CUDA(cudaMalloc(&s.d_payload, cfg->max_payload_bytes + 64));
+        PK_INIT_CUDA(cudaMalloc(&s.d_meta, h->meta_cap));
+        PK_INIT_CUDA(cudaMalloc(&s.d_out, n * sizeof(pk_decision)));
+        PK_INIT_CUDA(cudaMalloc(&s.d_scratch, n * sizeof(pk::SegScratch)));
+        PK_INIT_CUDA(cudaMemset(s.d_scratch, 0, n * sizeof(pk::SegScratch)));
+        PK_INIT_CUDA(cudaHostAlloc(&s.h_meta, h->meta_cap, cudaHostAllocDefault));
+    }
+    PK_INIT_CUDA(cudaDeviceSynchronize());
+#undef PK_INIT_CUDA
+    *out = h;
+    return PK_OK;
+}
+
+void pk_destroy(pk_handle* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    for (Slot& s : h->slots) free_slot(s);
+    if (h->d_table) cudaFree(h->d_table);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    (void)cudaGetLastError();
+    delete h;
+}
+
+int pk_sync(pk_handle* h)
+{
+    if (!h) return PK_ERR_ARG;
+    PK_CUDA(h, cudaSetDevice(h->device));
+    for (Slot& s : h->slots) PK_CUDA(h, cudaStreamSynchronize(s.stream));
+    return PK_OK;
+}
+
+int pk_update_table(pk_handle* h, const pk_table* tbl)
+{
+    if (!h) return PK_ERR_ARG;
+    int rc = validate_table(tbl);
+    if (rc) return rc;
+    rc = pk_sync(h);
+    if (rc) return rc;
+    PK_CUDA(h, cudaMemcpy(h->d_table, tbl, sizeof(pk_table), cudaMemcpyHostToDevice));
+    return PK_OK;
+}
+
+int pk_submit(pk_handle* h, uint32_t slot, const uint8_t* payload, const uint64_t* pay_off,
+              const uint32_t* pay_len, const uint8_t* names, const uint32_t* name_off, uint32_t n,
+              pk_decision* out)
+{
+    if (!h || slot >= h->slots.size()) return PK_ERR_ARG;
+    Slot& s = h->slots[slot];
+    if (s.inflight) return PK_ERR_BUSY;
+    if (n == 0) { s.n = 0; s.params.n = 0; s.staged = false; s.inflight = true; return PK_OK; }
+    if (!out) return PK_ERR_ARG;
+    PK_CUDA(h, cudaSetDevice(h->device));
+    size_t meta_bytes = 0;
+    uint64_t pb = 0, pbytes = 0;
+    s.staged = false;
+    int rc = prepare(h, s, pay_off, pay_len, names, name_off, n, &meta_bytes, &pb, &pbytes);
+    if (rc) return rc;
+    rc = enqueue_uploads(h, s, payload, meta_bytes, pb, pbytes);
+    if (rc) return rc;
+    rc = launch_slot(h, s, s.stream);
+    if (rc) return rc;
+    PK_CUDA(h, cudaMemcpyAsync(out, s.d_out, (size_t)n * sizeof(pk_decision), cudaMemcpyDeviceToHost, s.stream));
+    PK_CUDA(h, cudaEventRecord(s.done, s.stream));
+    s.staged = true;
+    s.inflight = true;
+    return PK_OK;
+}
+
+int pk_wait(pk_handle* h, uint32_t slot)
+{
+    if (!h || slot >= h->slots.size()) return PK_ERR_ARG;
+    Slot& s = h->slots[slot];
+    if (!s.inflight) return PK_ERR_STATE;
+    s.inflight = false;
+    if (s.n == 0) return PK_OK;
+    PK_CUDA(h, cudaSetDevice(h->device));
+    PK_CUDA(h, cudaEventSynchronize(s.done));
+    return PK_OK;
+}
+
+int pk_route_batch(pk_handle* h, const uint8_t* payload, const uint64_t* pay_off,
+                   const uint32_t* pay_len, const uint8_t* names, const uint32_t* name_off,
+                   uint32_t n, pk_decision* out)
+{
+    int rc = pk_submit(h, 0, payload, pay_off, pay_len, names, name_off, n, out);
+    if (rc) return rc;
+    return pk_wait(h, 0);
+}
+
+int pk_stage(pk_handle* h, uint32_t slot, const uint8_t* payload, const uint64_t* pay_off,
+             const uint32_t* pay_len, const uint8_t* names, const uint32_t* name_off, uint32_t n)
+{
+    if (!h || slot >= h->slots.size()) return PK_ERR_ARG;
+    Slot& s = h->slots[slot];
+    if (s.inflight) return PK_ERR_BUSY;
+    s.staged = false;
+    if (n == 0) { s.n = 0; s.params.n = 0; s.staged = true; return PK_OK; }
+    PK_CUDA(h, cudaSetDevice(h->device));
+    size_t meta_bytes = 0;
+    uint64_t pb = 0, pbytes = 0;
+    int rc = prepare(h, s, pay_off, pay_len, names, name_off, n, &meta_bytes, &pb, &pbytes);
+    if (rc) return rc;
+    rc = enqueue_uploads(h, s, payload, meta_bytes, pb, pbytes);
+    if (rc) return rc;
+    PK_CUDA(h, cudaStreamSynchronize(s.stream));
+    s.staged = true;
+    return PK_OK;
+}
+
+int pk_launch(pk_handle* h, uint32_t slot)
+{
+    if (!h || slot >= h->slots.size()) return PK_ERR_ARG;
+    Slot& s = h->slots[slot];
+    if (!s.staged) return PK_ERR_STATE;
+    PK_CUDA(h, cudaSetDevice(h->device));
+    return launch_slot(h, s, s.stream);
+}
+
+int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_t count,
+                   int use_graph, float* elapsed_ms)
+{
+    if (!h || !slots || n_list == 0) return PK_ERR_ARG;
+    for (uint32_t k = 0; k < n_list; ++k) {
+        if (slots[k] >= h->slots.size()) return PK_ERR_ARG;
+        if (!h->slots[slots[k]].staged) return PK_ERR_STATE;
+    }
+    if (elapsed_ms) *elapsed_ms = 0.f;
+    if (count == 0) return PK_OK;
+    PK_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->slots[slots[0]].stream;
+    // every listed slot's earlier work must be visible to this stream
+    for (uint32_t k = 1; k < n_list; ++k) PK_CUDA(h, cudaStreamSynchronize(h->slots[slots[k]].stream));
+
+    if (!use_graph) {
+        PK_CUDA(h, cudaEventRecord(h->ev0, st));
+        for (uint32_t k = 0; k < count; ++k) {
+            int rc = launch_slot(h, h->slots[slots[k % n_list]], st);
+            if (rc) return rc;
+        }
+        PK_CUDA(h, cudaEventRecord(h->ev1, st));
+    } else {
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        PK_CUDA(h, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int rc = PK_OK;
+        for (uint32_t k = 0; k < count && rc == PK_OK; ++k)
+            rc = launch_slot(h, h->slots[slots[k % n_list]], st);
+        cudaError_t ce = cudaStreamEndCapture(st, &graph);
+        if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+        PK_CUDA(h, ce);
+        ce = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        PK_CUDA(h, ce);
+        ce = cudaGraphUpload(exec, st);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+        if (ce == cudaSuccess) ce = cudaEventRecord(h->ev0, st);
+        if (ce == cudaSuccess) ce = cudaGraphLaunch(exec, st);
+        if (ce == cudaSuccess) ce = cudaEventRecord(h->ev1, st);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+        cudaGraphExecDestroy(exec);
+        PK_CUDA(h, ce);
+    }
+    PK_CUDA(h, cudaEventSynchronize(h->ev1));
+    if (elapsed_ms) PK_CUDA(h, cudaEventElapsedTime(elapsed_ms, h->ev0, h->ev1));
+    return PK_OK;
+}
+
+int pk_fetch(pk_handle* h, uint32_t slot, pk_decision* out)
+{
+    if (!h || slot >= h->slots.size()) return PK_ERR_ARG;
+    Slot& s = h->slots[slot];
+    if (!s.staged) return PK_ERR_STATE;
+    if (s.n == 0) return PK_OK;
+    if (!out) return PK_ERR_ARG;
+    PK_CUDA(h, cudaSetDevice(h->device));
+    PK_CUDA(h, cudaMemcpyAsync(out, s.d_out, (size_t)s.n * sizeof(pk_decision), cudaMemcpyDeviceToHost, s.stream));
+    PK_CUDA(h, cudaStreamSynchronize(s.stream));
+    return PK_OK;
+}
+
+void* pk_slot_stream(pk_handle* h, uint32_t slot)
+{
+    if (!h || slot >= h->slots.size()) return nullptr;
+    return (void*)h->slots[slot].stream;
+}
+
+void* pk_host_alloc(pk_handle* h, size_t bytes)
+{
+    if (!h || bytes == 0) return nullptr;
+    if (cudaSetDevice(h->device) != cudaSuccess) return nullptr;
+    void* p = nullptr;
+    cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocPortable);
+    if (e != cudaSuccess) { h->last_cuda = (int)e; (void)cudaGetLastError(); return nullptr; }
+    return p;
+}
+
+void pk_host_free(pk_handle* h, void* p)
+{
+    if (!p) return;
+    if (h) cudaSetDevice(h->device);
+    cudaFreeHost(p);
+}
+
+}  // extern "C"

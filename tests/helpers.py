@@ -1,0 +1,78 @@
+"""Shared helpers for the parity tests (test infrastructure)."""
+import json
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def load_golden():
+    with open(os.path.join(HERE, "golden", "route_golden.json")) as f:
+        return json.load(f)
+
+
+def pattern(n, a=131, b=7):
+    i = np.arange(n, dtype=np.int64)
+    return ((i * a + i // b) % 251).astype(np.uint8).tobytes()
+
+
+def text(n):
+    words = [b"route", b"the", b"Request", b"to", b"a", b"provider", b"internationalization", b"42",
+             b"{\"k\":1}", "naïve".encode(), "例え".encode(), b"x_y", b"\n", b"END."]
+    out = bytearray()
+    i = 0
+    while len(out) < n:
+        out += words[(i * 5 + i // 3) % len(words)] + b" "
+        i += 1
+    return bytes(out[:n])
+
+
+def golden_payload(vec):
+    if "payload_hex" in vec:
+        return bytes.fromhex(vec["payload_hex"])
+    kind, n = vec["payload_gen"]
+    return pattern(n) if kind == "pattern" else text(n)
+
+
+def golden_requests(g):
+    """[(name, payload, expect)] for every fixture row that carries a full expected record."""
+    rows = [(bytes.fromhex(v["name_hex"]), golden_payload(v), v["expect"]) for v in g["vectors"]]
+    d = g["dev_client_request"]
+    rows.append((bytes.fromhex(d["name_hex"]), bytes.fromhex(d["payload_hex"]), d["expect"]))
+    return rows
+
+
+def assert_records_equal(got, want, what=""):
+    """Bit-exact comparison of decision records (integer/byte work: tolerance is zero)."""
+    assert got.shape == want.shape, (what, got.shape, want.shape)
+    if (got == want).all():
+        return
+    bad = np.nonzero(got != want)[0]
+    i = int(bad[0])
+    raise AssertionError(f"{what}: {bad.size} of {got.size} records differ; first at {i}: "
+                         f"got {got[i]} want {want[i]}")
+
+
+def record_as_dict(r):
+    return {k: int(r[k]) for k in r.dtype.names}
+
+
+def permute_batch(batch, perm):
+    """Reorders the requests of a flat batch (payload starts stay 16-byte aligned)."""
+    n = len(perm)
+    pay_len = batch["pay_len"][perm]
+    pay_off = np.zeros(n + 1, dtype=np.uint64)
+    np.cumsum((pay_len.astype(np.uint64) + np.uint64(15)) & np.uint64(0xFFFFFFFFFFFFFFF0), out=pay_off[1:])
+    payload = np.full(max(int(pay_off[-1]), 16), 0x5A, dtype=np.uint8)[:int(pay_off[-1])]
+    nlen = (batch["name_off"][1:] - batch["name_off"][:-1])[perm]
+    name_off = np.zeros(n + 1, dtype=np.uint32)
+    np.cumsum(nlen, out=name_off[1:])
+    names = np.empty(int(name_off[-1]), dtype=np.uint8)
+    for j, i in enumerate(perm):
+        o, l = int(batch["pay_off"][i]), int(batch["pay_len"][i])
+        payload[int(pay_off[j]):int(pay_off[j]) + l] = batch["payload"][o:o + l]
+        a, b = int(batch["name_off"][i]), int(batch["name_off"][i + 1])
+        names[int(name_off[j]):int(name_off[j + 1])] = batch["names"][a:b]
+    return {"payload": payload, "pay_off": pay_off, "pay_len": pay_len.copy(), "names": names,
+            "name_off": name_off}

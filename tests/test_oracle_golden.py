@@ -1,0 +1,146 @@
+"""CPU: the C oracle against the golden fixtures and against the pure-Python restatement.
+
+Reference pins: the tool switch and status 200 (internal/service/mock.go:22-67).  The
+scan/hash/provider expectations are build-defined ("parity unpinned" by the reference); the
+fixture values were produced by oracle/pk_spec_py.py, which shares no code with pk_oracle.c.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from helpers import golden_requests, load_golden, record_as_dict
+
+
+def test_tool_class_literals(oracle):
+    """mock.go:32-64: exact, case-sensitive, whole-name equality; unknown -> default, not an error."""
+    g = load_golden()
+    t = oracle.default_table()
+    assert [(bytes(t.tools[k].name[:t.tools[k].name_len]).decode(), t.tools[k].class_id)
+            for k in range(t.n_tools)] == [tuple(x) for x in g["tools"]]
+    for row in g["tool_class"]:
+        name = bytes.fromhex(row["name_hex"])
+        unknown = C.c_int(-1)
+        buf = (C.c_uint8 * max(1, len(name))).from_buffer_copy(name or b"\0")
+        cls = oracle.lib().pk_ref_tool_class(C.byref(t), buf, len(name), C.byref(unknown))
+        assert (cls, bool(unknown.value)) == (row["tool_class"], row["unknown"]), name
+
+
+def test_golden_records(oracle):
+    g = load_golden()
+    rows = golden_requests(g)
+    batch = oracle.pack_batch([(nm, p) for nm, p, _ in rows])
+    rc, out = oracle.route_batch(oracle.default_table(), batch)
+    assert rc == 0
+    for r, (nm, p, want) in zip(out, rows):
+        assert record_as_dict(r) == want, (nm, len(p))
+    assert (out["status"] == 200).all()          # mock.go:25-28: always 200
+
+
+def test_default_table_matches_fixture(oracle):
+    g = load_golden()
+    t = oracle.default_table()
+    got = [[t.providers[p].max_tokens, t.providers[p].weight, t.providers[p].tool_mask, t.providers[p].salt]
+           for p in range(t.n_providers)]
+    assert got == g["providers"] and t.default_class == g["default_class"]
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
+def test_oracle_vs_python_restatement(oracle, mode):
+    from oracle import pk_spec_py as S
+    t = oracle.default_table()
+    tools = [(bytes(t.tools[k].name[:t.tools[k].name_len]), t.tools[k].class_id) for k in range(t.n_tools)]
+    provs = [(p.max_tokens, p.weight, p.tool_mask, p.salt) for p in list(t.providers)[:t.n_providers]]
+    b = oracle.gen_batch(oracle.SEED_BASE + 17 * mode, 48, 0, 1200, mode=mode)
+    rc, out = oracle.route_batch(t, b)
+    assert rc == 0
+    for i in range(48):
+        o, l = int(b["pay_off"][i]), int(b["pay_len"][i])
+        nm = bytes(b["names"][b["name_off"][i]:b["name_off"][i + 1]])
+        assert record_as_dict(out[i]) == S.route_one(tools, 3, provs, nm, bytes(b["payload"][o:o + l]))
+
+
+def test_oracle_multisegment_vs_python(oracle):
+    from oracle import pk_spec_py as S
+    t = oracle.default_table()
+    tools = [(bytes(t.tools[k].name[:t.tools[k].name_len]), t.tools[k].class_id) for k in range(t.n_tools)]
+    provs = [(p.max_tokens, p.weight, p.tool_mask, p.salt) for p in list(t.providers)[:t.n_providers]]
+    b = oracle.gen_batch(99, 3, 16380, 50000, mode=0)
+    rc, out = oracle.route_batch(t, b)
+    assert rc == 0
+    for i in range(3):
+        o, l = int(b["pay_off"][i]), int(b["pay_len"][i])
+        nm = bytes(b["names"][b["name_off"][i]:b["name_off"][i + 1]])
+        assert record_as_dict(out[i]) == S.route_one(tools, 3, provs, nm, bytes(b["payload"][o:o + l]))
+
+
+def test_mt_equals_single_thread(oracle):
+    t = oracle.default_table()
+    b = oracle.gen_batch(5, 777, 0, 5000, mode=-1)
+    rc1, a = oracle.route_batch(t, b, threads=1)
+    rc2, m = oracle.route_batch(t, b, threads=5)
+    assert rc1 == 0 and rc2 == 0 and (a == m).all()
+    rc3, s = oracle.route_batch(t, b, threads=3, switch_only=True)
+    assert rc3 == 0 and (s["tool_class"] == a["tool_class"]).all() and (s["status"] == 200).all()
+
+
+def test_oracle_error_codes(oracle):
+    t = oracle.default_table()
+    b = oracle.pack_batch([(b"example_tool", b"hello world"), (b"file_tool", b"x" * 40)])
+    bad = dict(b)
+    bad["pay_off"] = b["pay_off"].copy()
+    bad["pay_off"][1] += 8
+    assert oracle.route_batch(t, bad)[0] == -2              # PK_ERR_ALIGN
+    bad["pay_off"] = b["pay_off"][::-1].copy()
+    assert oracle.route_batch(t, bad)[0] in (-2, -3)        # not monotone
+    bad = dict(b)
+    bad["pay_len"] = np.array([11, 4000], dtype=np.uint32)
+    assert oracle.route_batch(t, bad)[0] == -3              # length overruns its slot
+    rc, out = oracle.route_batch(t, oracle.pack_batch([]))
+    assert rc == 0 and out.size == 0
+
+
+def test_mock_responses(oracle):
+    """Response literals of mock.go:24-63 (pk_ref_execute_tool restates them)."""
+    g = load_golden()["responses"]
+    r = oracle.execute_tool(b"example_tool", 1700000000)
+    assert r.status_code == g["status_code"] and r.status_message.decode() == g["status_message"]
+    assert r.kind == 0 and r.string_output.decode() == g["example_tool"]["prefix"] + "2023-11-14T22:13:20Z"
+    r = oracle.execute_tool(b"struct_tool", 1700000000)
+    assert r.kind == 1 and b'"count":42' in r.string_output and b'"processed":true' in r.string_output
+    assert b'"result":"success"' in r.string_output and b'"timestamp":1700000000' in r.string_output
+    r = oracle.execute_tool(b"file_tool", 0)
+    assert (r.kind, r.file_name, r.mime_type, r.file_content) == (
+        2, g["file_tool"]["file_name"].encode(), g["file_tool"]["mime_type"].encode(),
+        g["file_tool"]["content"].encode())
+    r = oracle.execute_tool(b"nope", 0)                     # mock.go:60-64: still 200, nil error
+    assert r.status_code == 200 and r.kind == 0 and r.string_output == b"Unknown tool: nope"
+
+
+def test_generator_is_deterministic_and_sliceable(oracle):
+    a = oracle.gen_batch(42, 64, 10, 300, mode=0)
+    b = oracle.gen_batch(42, 64, 10, 300, mode=0, threads=3)
+    assert all((a[k] == b[k]).all() for k in a)
+    # a rank generating requests [32, 64) of the stream gets the same requests
+    c = oracle.gen_batch(42, 32, 10, 300, mode=0, first_id=32)
+    assert (c["pay_len"] == a["pay_len"][32:]).all()
+    o = int(a["pay_off"][32])
+    assert (c["payload"] == a["payload"][o:]).all()
+    # valid UTF-8 in the text modes (Go's proto3 decode would reject anything else upstream)
+    for mode in (0, 2):
+        x = oracle.gen_batch(7, 16, 100, 400, mode=mode)
+        for i in range(16):
+            s, l = int(x["pay_off"][i]), int(x["pay_len"][i])
+            bytes(x["payload"][s:s + l]).decode("utf-8")
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
+def test_fast_cpu_port_equals_plain_oracle(oracle, mode):
+    """oracle/pk_cpu_fast.c (the timed CPU baseline) against the plain checker."""
+    t = oracle.default_table()
+    for n, lo, hi in [(300, 0, 40000), (3000, 0, 70), (40, 16370, 16400)]:
+        b = oracle.gen_batch(900 + mode, n, lo, hi, mode=mode)
+        plain = oracle.route_batch(t, b, threads=4)[1]
+        for th in (1, 3):
+            rc, fast = oracle.route_batch(t, b, threads=th, fast=True)
+            assert rc == 0 and (fast == plain).all(), (mode, n, th)
