@@ -64,9 +64,10 @@ extern "C" {
 #define PK_MAX_PROVIDERS      32u
 #define PK_MAX_NAME_LEN       0xFFFFFFu /* a request's tool name, bytes              */
 #define PK_PROVIDER_NONE      0xFFu
+#define PK_MAX_WEIGHT         (1u << 20) /* provider weight upper bound              */
 
 /* decision flags */
-#define PK_FLAG_NONASCII      0x0001u  /* payload holds a byte >= 0x80              */
+                                       /* 0x0001u is reserved (always 0)            */
 #define PK_FLAG_NO_PROVIDER   0x0002u  /* no provider eligible; provider = 0xFF     */
 #define PK_FLAG_EMPTY_PAYLOAD 0x0004u  /* pay_len == 0                              */
 #define PK_FLAG_UNKNOWN_TOOL  0x0008u  /* name matched no table entry: the default
@@ -98,9 +99,10 @@ typedef struct pk_tool {
  * reference has no provider list — SURVEY.md §0.3, §8 a6). */
 typedef struct pk_provider {
     uint32_t max_tokens;          /* eligible iff est_tokens <= max_tokens          */
-    uint32_t weight;              /* 0 disables the provider                        */
+    uint32_t weight;              /* share of traffic among the eligible providers;
+                                     0 disables the provider; <= PK_MAX_WEIGHT      */
     uint32_t tool_mask;           /* bit c set: serves tool class c                 */
-    uint32_t salt;                /* per-provider hash salt                         */
+    uint32_t reserved;            /* ignored                                        */
 } pk_provider;
 
 typedef struct pk_table {

@@ -16,7 +16,6 @@
 
 #define P1 0x9E3779B1u
 #define P2 0x85EBCA77u
-#define P3 0xC2B2AE3Du
 #define P5 0x165667B1u
 #define NAME_MUL 0xD6E8FEB86659FD93ull
 
@@ -115,19 +114,25 @@ static void route_one(const pk_table* t, const uint8_t* p, uint32_t len, const u
         s += (uint64_t)x * NAME_MUL;
     }
     uint64_t h = fmix64(s + ((uint64_t)nlen << 32) + len);
-    uint32_t best = PK_PROVIDER_NONE;
-    uint64_t best_score = 0;
+    uint64_t total = 0;
     for (uint32_t q = 0; q < t->n_providers; ++q) {
         const pk_provider* e = &t->providers[q];
-        if (e->weight == 0 || !((e->tool_mask >> cls) & 1u) || tok > e->max_tokens) continue;
-        uint32_t r = ((uint32_t)h ^ e->salt) * P2 + (uint32_t)(h >> 32);
-        r ^= r >> 15; r *= P3; r ^= r >> 13;
-        uint64_t sc = (uint64_t)r * e->weight;
-        if (best == PK_PROVIDER_NONE || sc > best_score) { best = q; best_score = sc; }
+        if (e->weight != 0 && ((e->tool_mask >> cls) & 1u) && tok <= e->max_tokens) total += e->weight;
+    }
+    uint32_t best = PK_PROVIDER_NONE;
+    if (total) {
+        uint64_t x = ((h >> 32) * total) >> 32, running = 0;
+        for (uint32_t q = 0; q < t->n_providers; ++q) {
+            const pk_provider* e = &t->providers[q];
+            if (!(e->weight != 0 && ((e->tool_mask >> cls) & 1u) && tok <= e->max_tokens)) continue;
+            running += e->weight;
+            if (running > x) { best = q; break; }
+        }
     }
     d->byte_len = len; d->est_tokens = tok; d->route_hash = h;
     d->tool_class = (uint8_t)cls; d->provider = (uint8_t)best;
-    d->flags = (uint16_t)((nonascii ? PK_FLAG_NONASCII : 0) | (best == PK_PROVIDER_NONE ? PK_FLAG_NO_PROVIDER : 0) |
+    (void)nonascii;
+    d->flags = (uint16_t)((best == PK_PROVIDER_NONE ? PK_FLAG_NO_PROVIDER : 0) |
                           (len == 0 ? PK_FLAG_EMPTY_PAYLOAD : 0) | (unknown ? PK_FLAG_UNKNOWN_TOOL : 0));
     d->status = 200;                                                  /* mock.go:25-28 */
 }

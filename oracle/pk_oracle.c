@@ -43,7 +43,6 @@
 #define SPEC_SEG_BLOCKS   1024u                 /* 16 KiB segments                 */
 #define SPEC_P1           0x9E3779B1u
 #define SPEC_P2           0x85EBCA77u
-#define SPEC_P3           0xC2B2AE3Du
 #define SPEC_P5           0x165667B1u
 #define SPEC_NAME_MUL     0xD6E8FEB86659FD93ull
 #define SPEC_FMIX_C1      0xFF51AFD7ED558CCDull
@@ -170,27 +169,29 @@ uint64_t pk_ref_route_hash(const uint8_t* p, uint64_t len, const uint8_t* name, 
 }
 
 /* ------------------------------------------------------------------ SPEC §D ---- */
+/* Among the eligible providers choose one with probability weight / total weight, the random
+ * number being the top 32 bits of the route hash: x = (hi32(hash) * W) >> 32 lies in [0, W);
+ * the winner is the first eligible provider whose running weight total exceeds x. */
+static int provider_eligible(const pk_provider* e, uint32_t est_tokens, uint32_t tool_class)
+{
+    return e->weight != 0 && ((e->tool_mask >> tool_class) & 1u) != 0 && est_tokens <= e->max_tokens;
+}
+
 uint32_t pk_ref_select_provider(const pk_table* t, uint64_t route_hash, uint32_t est_tokens,
                                 uint32_t tool_class)
 {
-    uint32_t best = PK_PROVIDER_NONE;
-    uint64_t best_score = 0;
+    uint64_t total = 0;
+    for (uint32_t p = 0; p < t->n_providers; ++p)
+        if (provider_eligible(&t->providers[p], est_tokens, tool_class)) total += t->providers[p].weight;
+    if (total == 0) return PK_PROVIDER_NONE;
+    uint64_t x = ((route_hash >> 32) * total) >> 32;
+    uint64_t running = 0;
     for (uint32_t p = 0; p < t->n_providers; ++p) {
-        const pk_provider* e = &t->providers[p];
-        if (e->weight == 0) continue;
-        if (((e->tool_mask >> tool_class) & 1u) == 0) continue;
-        if (est_tokens > e->max_tokens) continue;
-        uint32_t r = ((uint32_t)route_hash ^ e->salt) * SPEC_P2 + (uint32_t)(route_hash >> 32);
-        r ^= r >> 15;
-        r *= SPEC_P3;
-        r ^= r >> 13;
-        uint64_t score = (uint64_t)r * (uint64_t)e->weight;
-        if (best == PK_PROVIDER_NONE || score > best_score) {   /* ties: lowest index */
-            best = p;
-            best_score = score;
-        }
+        if (!provider_eligible(&t->providers[p], est_tokens, tool_class)) continue;
+        running += t->providers[p].weight;
+        if (running > x) return p;
     }
-    return best;
+    return PK_PROVIDER_NONE;   /* unreachable */
 }
 
 /* ------------------------------------------------------------ one request ------ */
@@ -205,8 +206,8 @@ void pk_ref_route_one(const pk_table* t, const uint8_t* p, uint32_t len, const u
     d->route_hash = pk_ref_route_hash(p, len, name, name_len);
     uint32_t prov = pk_ref_select_provider(t, d->route_hash, d->est_tokens, d->tool_class);
     d->provider = (uint8_t)prov;
-    d->flags = (uint16_t)((nonascii ? PK_FLAG_NONASCII : 0) |
-                          (prov == PK_PROVIDER_NONE ? PK_FLAG_NO_PROVIDER : 0) |
+    (void)nonascii;
+    d->flags = (uint16_t)((prov == PK_PROVIDER_NONE ? PK_FLAG_NO_PROVIDER : 0) |
                           (len == 0 ? PK_FLAG_EMPTY_PAYLOAD : 0) |
                           (unknown ? PK_FLAG_UNKNOWN_TOOL : 0));
     d->status = 200;                       /* mock.go:25-28 */
@@ -218,6 +219,8 @@ static int validate_table(const pk_table* t)
     if (t->default_class >= 32) return PK_ERR_ARG;
     for (uint32_t k = 0; k < t->n_tools; ++k)
         if (t->tools[k].name_len > PK_MAX_TOOL_NAME || t->tools[k].class_id >= 32) return PK_ERR_ARG;
+    for (uint32_t p = 0; p < t->n_providers; ++p)
+        if (t->providers[p].weight > PK_MAX_WEIGHT) return PK_ERR_ARG;
     return PK_OK;
 }
 
@@ -395,7 +398,7 @@ int pk_ref_default_table(pk_table* t)
         t->providers[p].max_tokens = max_tokens[p];
         t->providers[p].weight = weight[p];
         t->providers[p].tool_mask = (p % 4 == 3) ? 0x7u : 0xFu;  /* every 4th: known tools only */
-        t->providers[p].salt = (p + 1u) * 0x9E3779B9u;
+        t->providers[p].reserved = 0;
     }
     return PK_OK;
 }

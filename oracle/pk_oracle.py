@@ -31,7 +31,7 @@ class PkTool(C.Structure):
 
 class PkProvider(C.Structure):
     _fields_ = [("max_tokens", C.c_uint32), ("weight", C.c_uint32), ("tool_mask", C.c_uint32),
-                ("salt", C.c_uint32)]
+                ("reserved", C.c_uint32)]
 
 
 class PkTable(C.Structure):
@@ -116,7 +116,7 @@ def make_table(tools, providers, default_class=3) -> PkTable:
             t.tools[k].name[j] = b
     for p, (mt, w, mask, salt) in enumerate(providers):
         e = t.providers[p]
-        e.max_tokens, e.weight, e.tool_mask, e.salt = mt, w, mask, salt
+        e.max_tokens, e.weight, e.tool_mask, e.reserved = mt, w, mask, salt
     return t
 
 

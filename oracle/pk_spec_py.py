@@ -7,7 +7,7 @@ build-defined (parity unpinned by the reference).
 """
 M32 = 0xFFFFFFFF
 M64 = 0xFFFFFFFFFFFFFFFF
-P1, P2, P3, P5 = 0x9E3779B1, 0x85EBCA77, 0xC2B2AE3D, 0x165667B1
+P1, P2, P5 = 0x9E3779B1, 0x85EBCA77, 0x165667B1
 NAME_MUL = 0xD6E8FEB86659FD93
 
 
@@ -90,19 +90,20 @@ def route_hash(p: bytes, name: bytes):
 
 
 def select_provider(providers, h, tokens, cls):
-    """providers: [(max_tokens, weight, tool_mask, salt)] -> index or 0xFF."""
-    best, best_score = 0xFF, -1
-    for i, (mt, w, mask, salt) in enumerate(providers):
-        if w == 0 or not (mask >> cls) & 1 or tokens > mt:
-            continue
-        r = ((((h & M32) ^ salt) * P2) + (h >> 32)) & M32
-        r ^= r >> 15
-        r = (r * P3) & M32
-        r ^= r >> 13
-        score = r * w
-        if score > best_score:
-            best, best_score = i, score
-    return best
+    """providers: [(max_tokens, weight, tool_mask, reserved)] -> index or 0xFF.
+    Weighted choice among the eligible providers, driven by the top 32 bits of the hash."""
+    eligible = [(i, w) for i, (mt, w, mask, _) in enumerate(providers)
+                if w != 0 and (mask >> cls) & 1 and tokens <= mt]
+    total = sum(w for _, w in eligible)
+    if total == 0:
+        return 0xFF
+    x = ((h >> 32) * total) >> 32
+    running = 0
+    for i, w in eligible:
+        running += w
+        if running > x:
+            return i
+    raise AssertionError("unreachable")
 
 
 def route_one(tools, default_class, providers, name: bytes, p: bytes):
@@ -110,7 +111,6 @@ def route_one(tools, default_class, providers, name: bytes, p: bytes):
     tokens, nonascii = est_tokens(p)
     h = route_hash(p, name)
     prov = select_provider(providers, h, tokens, cls)
-    flags = (1 if nonascii else 0) | (2 if prov == 0xFF else 0) | (4 if len(p) == 0 else 0) | \
-            (8 if unknown else 0)
+    flags = (2 if prov == 0xFF else 0) | (4 if len(p) == 0 else 0) | (8 if unknown else 0)
     return dict(byte_len=len(p), est_tokens=tokens, route_hash=h, tool_class=cls, provider=prov,
                 flags=flags, status=200)

@@ -16,13 +16,12 @@ import os
 import numpy as np
 
 __all__ = ["Router", "PkError", "PkTable", "PkTool", "PkProvider", "DECISION_DTYPE", "default_table",
-           "make_table", "pack_requests", "round16", "lib", "LIB_PATH", "STATUS", "FLAG_NONASCII",
-           "FLAG_NO_PROVIDER", "FLAG_EMPTY_PAYLOAD", "FLAG_UNKNOWN_TOOL", "PROVIDER_NONE"]
+           "make_table", "pack_requests", "round16", "lib", "LIB_PATH", "STATUS", "FLAG_NO_PROVIDER", "FLAG_EMPTY_PAYLOAD", "FLAG_UNKNOWN_TOOL", "PROVIDER_NONE"]
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libpkroute.so")
 
 PK_MAX_TOOLS, PK_MAX_TOOL_NAME, PK_MAX_PROVIDERS = 16, 64, 32
-FLAG_NONASCII, FLAG_NO_PROVIDER, FLAG_EMPTY_PAYLOAD, FLAG_UNKNOWN_TOOL = 1, 2, 4, 8
+FLAG_NO_PROVIDER, FLAG_EMPTY_PAYLOAD, FLAG_UNKNOWN_TOOL = 2, 4, 8
 PROVIDER_NONE = 0xFF
 STATUS = {0: "PK_OK", -1: "PK_ERR_ARG", -2: "PK_ERR_ALIGN", -3: "PK_ERR_OFFSETS", -4: "PK_ERR_CAPACITY",
           -5: "PK_ERR_CUDA", -6: "PK_ERR_NO_DEVICE", -7: "PK_ERR_BUSY", -8: "PK_ERR_STATE"}
@@ -40,7 +39,7 @@ class PkTool(C.Structure):
 
 class PkProvider(C.Structure):
     _fields_ = [("max_tokens", C.c_uint32), ("weight", C.c_uint32), ("tool_mask", C.c_uint32),
-                ("salt", C.c_uint32)]
+                ("reserved", C.c_uint32)]
 
 
 class PkTable(C.Structure):
@@ -124,7 +123,7 @@ def make_table(tools, providers, default_class: int = 3) -> PkTable:
             t.tools[k].name[j] = b
     for p, (mt, w, mask, salt) in enumerate(providers[:PK_MAX_PROVIDERS]):
         e = t.providers[p]
-        e.max_tokens, e.weight, e.tool_mask, e.salt = mt, w, mask, salt
+        e.max_tokens, e.weight, e.tool_mask, e.reserved = mt, w, mask, salt
     return t
 
 

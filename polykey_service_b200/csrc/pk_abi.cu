@@ -29,6 +29,7 @@ struct Slot {
     pk::SegScratch* d_scratch = nullptr;
     uint8_t*     h_meta = nullptr;      // pinned staging for the metadata blob
     uint32_t     n = 0;
+    uint32_t     max_len = 0;           // longest payload of the prepared batch
     bool         staged = false;        // params describe a resident batch
     bool         inflight = false;      // pk_submit without pk_wait
     pk::RouteParams params{};
@@ -67,6 +68,8 @@ int validate_table(const pk_table* t)
     if (t->default_class >= 32) return PK_ERR_ARG;
     for (uint32_t k = 0; k < t->n_tools; ++k)
         if (t->tools[k].name_len > PK_MAX_TOOL_NAME || t->tools[k].class_id >= 32) return PK_ERR_ARG;
+    for (uint32_t p = 0; p < t->n_providers; ++p)
+        if (t->providers[p].weight > PK_MAX_WEIGHT) return PK_ERR_ARG;
     return PK_OK;
 }
 
@@ -95,6 +98,7 @@ int prepare(pk_handle* h, Slot& s, const uint64_t* pay_off, const uint32_t* pay_
     const uint32_t nbase = name_off[0];
     uint64_t n_extra = 0;
     uint64_t end = base;
+    uint32_t max_len = 0;
     for (uint32_t i = 0; i < n; ++i) {
         const uint64_t o = pay_off[i], nx = pay_off[i + 1];
         const uint32_t l = pay_len[i];
@@ -105,6 +109,7 @@ int prepare(pk_handle* h, Slot& s, const uint64_t* pay_off, const uint32_t* pay_
         if (o - base + l > h->cfg.max_payload_bytes) return PK_ERR_CAPACITY;
         m_off[i]  = o - base;
         m_len[i]  = l;
+        if (l > max_len) max_len = l;
         m_noff[i] = name_off[i] - nbase;
         if (l > pk::kSegBytes) {
             const uint32_t nseg = (l + pk::kSegBytes - 1) / pk::kSegBytes;
@@ -143,6 +148,7 @@ int prepare(pk_handle* h, Slot& s, const uint64_t* pay_off, const uint32_t* pay_
     P.n        = n;
     P.n_extra  = (uint32_t)n_extra;
     s.n = n;
+    s.max_len = max_len;
     return PK_OK;
 }
 
@@ -161,7 +167,7 @@ int enqueue_uploads(pk_handle* h, Slot& s, const uint8_t* payload, size_t meta_b
 int launch_slot(pk_handle* h, const Slot& s, cudaStream_t stream)
 {
     if (s.params.n == 0) return PK_OK;
-    PK_CUDA(h, pk::launch_route(s.params, h->num_sms, stream));
+    PK_CUDA(h, pk::launch_route(s.params, s.max_len, h->num_sms, stream));
     ++h->launches;
     return PK_OK;
 }
@@ -222,7 +228,7 @@ int pk_default_table(pk_table* t)
         t->providers[p].max_tokens = max_tokens[p];
         t->providers[p].weight = p + 1;
         t->providers[p].tool_mask = (p % 4 == 3) ? 0x7u : 0xFu;
-        t->providers[p].salt = (p + 1u) * 0x9E3779B9u;
+        t->providers[p].reserved = 0;
     }
     return PK_OK;
 }

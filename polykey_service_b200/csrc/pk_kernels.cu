@@ -2,19 +2,30 @@
 //
 // One pass over the payload bytes does all three steps of the routing decision:
 //   (1) SIMD-in-word byte classification / token estimate         (SPEC §B)
-//   (2) lane-striped route-key hash, merged with warp shuffles     (SPEC §C)
+//   (2) lane-striped route-key hash                                (SPEC §C)
 //   (3) tool-class match against the device-resident table — the batched form of the
 //       `switch toolName` at internal/service/mock.go:32-64 — and provider selection
-//       (SPEC §A, §D), folded into the same warp's epilogue.
+//       (SPEC §A, §D).
 //
-// Work decomposition: a TASK is one (request, 16 KiB segment) pair and is owned by one
-// warp.  Lane l loads 16-byte block (32*i + l) of the segment with one 128-bit streaming
-// load, so a warp reads 512 contiguous bytes per step — four steps are issued before the
-// first is consumed.  Requests of at most one segment are finished by the warp that
-// scanned them; longer requests accumulate per-segment partials in a 32-byte scratch
-// entry with integer atomics (the merge is a commutative sum, so any order gives the same
-// bits) and the warp that arrives last finalises.  HBM-bound integer/byte work: no tensor
-// cores, nothing here is a contraction.
+// Shape of a CTA (256 threads = 8 warps), which owns R consecutive requests:
+//   phase 1  warp-cooperative scan.  A group of G lanes (G = 32, or 16 / 8 when every
+//            payload of the batch fits one step of G 16-byte blocks) owns one request; lane l
+//            of the group loads block (G*i + l) with one 128-bit streaming load, so a warp
+//            reads 512 contiguous bytes per step, four steps in flight.  Each lane keeps its
+//            own hash stripe and token counter and parks them in shared memory — no
+//            cross-lane traffic at all in the scan (a letter run is cut at every 8th offset,
+//            and every block starts at one).
+//   phase 2  one THREAD per request: sums the G partials, adds the tool-name terms, runs the
+//            tool switch and the provider choice and stores the 24-byte record.  32 requests
+//            per warp instruction instead of one.
+// Requests longer than one 16 KiB segment are split: the extra segments are scanned by
+// separate warps (listed by the host), partials are folded into a 32-byte scratch entry with
+// integer atomics (a commutative sum: any order gives the same bits) and the warp that
+// arrives last finalises the request.
+//
+// HBM-bound integer/byte work: no tensor cores — nothing here is a contraction.
+#include <cstdlib>
+
 #include "pk_kernels.cuh"
 #include "pk_spec.cuh"
 
@@ -25,6 +36,7 @@ constexpr int      kWarpsPerCta = 8;
 constexpr int      kThreads     = kWarpsPerCta * 32;
 constexpr int      kUnroll      = 4;          // 128-bit loads in flight per lane
 constexpr unsigned kFull        = 0xFFFFFFFFu;
+constexpr int      kPartialSlots = 32 * 65;   // >= G * (R + 1) for every (G, R) launch_route picks
 
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p)
 {
@@ -41,213 +53,203 @@ __device__ __forceinline__ uint64_t warp_sum64(uint64_t v)
     return v;
 }
 
-struct Partial {
-    uint64_t sum;      // this lane's stripe digest (0 if the lane saw no block)
-    uint32_t tok;      // this lane's token count
-    uint32_t orbits;   // OR of this lane's words
-};
-
-// Scan one segment of one payload.  pay points at the payload's first byte (16-byte
-// aligned), len is the payload length, seg the segment index.
-__device__ __forceinline__ Partial scan_segment(const uint8_t* __restrict__ pay, uint32_t len,
-                                                uint32_t seg, uint32_t lane)
+// Scan one 16 KiB segment of one payload with a full warp.  pay points at the payload's first
+// byte (16-byte aligned).  Returns this lane's stripe digest (0 if it saw no block) and its
+// token count.
+__device__ __forceinline__ void scan_segment(const uint8_t* __restrict__ pay, uint32_t len,
+                                             uint32_t seg, uint32_t lane, uint32_t one,
+                                             uint64_t& digest, uint32_t& tok)
 {
-    const uint32_t nblk  = (len >> 4) + ((len & 15u) ? 1u : 0u);
-    const uint32_t first = seg * kSegBlocks;
-    const uint32_t nb    = min(kSegBlocks, nblk - first);      // blocks of this segment
-    const uint4*   base  = reinterpret_cast<const uint4*>(pay) + first;
+    const uint32_t nblk   = (len >> 4) + ((len & 15u) ? 1u : 0u);
+    const uint32_t first  = seg * kSegBlocks;
+    const uint32_t nb     = min(kSegBlocks, nblk - first);          // blocks of this segment
+    const uint32_t nwhole = min(kSegBlocks, (len >> 4) - first);    // ... lying wholly inside the payload
+    const uint4*   base   = reinterpret_cast<const uint4*>(pay) + first + lane;
 
     Stripe st;
     stripe_init(st, seg * kStripes + lane);
-    uint32_t tok128 = 0, orb = 0;
+    uint32_t tok128 = 0;
+    uint32_t b0 = 0;
 
-    // letter flag of the byte just before this segment: lane 0's carry-in
-    uint32_t carry = 0;
-    if (first != 0 && lane == 0) carry = letter_mask_of_byte(pay[(size_t)first * kBlockBytes - 1]);
-
-    for (uint32_t b0 = 0; b0 < nb; b0 += 32 * kUnroll) {
+    // main loop: four whole warp-steps (2 KiB) per iteration, no predicates
+    for (; b0 + 32u * kUnroll <= nwhole; b0 += 32u * kUnroll) {
+        uint4 x[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) x[u] = ldg_stream(base + b0 + u * 32);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const Words4 w = {{x[u].x, x[u].y, x[u].z, x[u].w}};
+            stripe_round(st, w);
+            scan_block(w, one, tok128);
+        }
+    }
+    // remainder: ragged steps, the payload's last (partial) block
+    for (; b0 < nb; b0 += 32u * kUnroll) {
         uint4 x[kUnroll];
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
             const uint32_t k = b0 + u * 32 + lane;
-            x[u] = (k < nb) ? ldg_stream(base + k) : make_uint4(0u, 0u, 0u, 0u);
+            x[u] = (k < nb) ? ldg_stream(base + b0 + u * 32) : make_uint4(0u, 0u, 0u, 0u);
         }
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-            if (b0 + u * 32 >= nb) break;                       // warp-uniform
+            if (b0 + u * 32 >= nb) break;                                 // warp-uniform
             const uint32_t k = b0 + u * 32 + lane;
-            const bool act = k < nb;
             Words4 w = {{x[u].x, x[u].y, x[u].z, x[u].w}};
-            if (act) {
+            if (k < nb) {
                 const uint32_t valid = len - (first + k) * kBlockBytes;   // >= 1
-                if (valid < kBlockBytes) mask_tail(w, valid);              // payload's last block
+                if (valid < kBlockBytes) mask_tail(w, valid);
                 stripe_round(st, w);
             }
-            // neighbour hand-off of "my last byte is a letter": lane l-1 -> lane l, and
-            // lane 31 of this step -> lane 0 of the next step
-            const uint32_t l3 = letter_mask(w.w[3]);
-            const uint32_t r  = __shfl_sync(kFull, l3, (lane + 31u) & 31u);
-            const uint32_t prev = (lane == 0) ? carry : r;
-            carry = r;
-            scan_block(w, prev, tok128, orb);
+            scan_block(w, one, tok128);          // an all-zero block counts nothing
         }
     }
-    Partial p;
-    p.sum    = (lane < nb) ? stripe_digest(st) : 0ull;
-    p.tok    = tok128 >> 7;
-    p.orbits = orb;
-    return p;
+    digest = (lane < nb) ? stripe_digest(st) : 0ull;
+    tok    = tok128 >> 7;
 }
 
-// Everything after the scan, executed by a full warp for one request:
-// name terms of the hash, tool-class match, final hash, provider selection, record store.
-//   sum_lane   per-lane partial of the payload stripe-digest sum (summed here)
-//   tok, orb   warp-uniform totals
-__device__ __forceinline__ void finalize_request(const RouteParams& P, uint32_t req, uint32_t len,
-                                                 uint64_t sum_lane, uint32_t tok, uint32_t orb,
-                                                 uint32_t lane)
+// A payload of at most G blocks scanned by a group of G lanes: one block per lane, one step.
+template <int G>
+__device__ __forceinline__ void scan_tiny(const uint8_t* __restrict__ pay, uint32_t len,
+                                          uint32_t lig, uint32_t one, uint64_t& digest, uint32_t& tok)
 {
-    const pk_table* __restrict__ tbl = P.table;
-    const uint32_t noff = __ldg(P.name_off + req);
-    const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
-    const uint8_t* __restrict__ nm = P.names + noff;
-
-    // name bytes: lane j holds bytes j and j+32 for the table match; every byte adds its
-    // position-tagged term to the hash sum
-    uint32_t c0 = 0, c1 = 0;
-    for (uint32_t j = lane; j < nlen; j += 32) {
-        const uint32_t b = __ldg(nm + j);
-        sum_lane += name_term(j, b);
-        if (j < 32) c0 = b; else if (j < 64) c1 = b;
+    const uint32_t nblk = (len >> 4) + ((len & 15u) ? 1u : 0u);       // <= G
+    uint32_t tok128 = 0;
+    digest = 0ull;
+    if (lig < nblk) {
+        const uint4 x = ldg_stream(reinterpret_cast<const uint4*>(pay) + lig);
+        Words4 w = {{x.x, x.y, x.z, x.w}};
+        const uint32_t valid = len - lig * kBlockBytes;
+        if (valid < kBlockBytes) mask_tail(w, valid);
+        Stripe st;
+        stripe_init(st, lig);
+        stripe_round(st, w);
+        digest = stripe_digest(st);
+        scan_block(w, one, tok128);
     }
-
-    // tool class: exact whole-name byte equality, first match wins (mock.go:32-59);
-    // no match is the default branch (mock.go:60-64) — a class, not an error
-    uint32_t cls = __ldg(&tbl->default_class);
-    bool unknown = true;
-    const uint32_t nt = __ldg(&tbl->n_tools);
-    for (uint32_t t = 0; t < nt; ++t) {
-        const uint32_t tl = __ldg(&tbl->tools[t].name_len);
-        if (tl != nlen) continue;                                   // warp-uniform
-        bool ok = true;
-        if (lane < tl)       ok = (__ldg(&tbl->tools[t].name[lane]) == c0);
-        if (lane + 32u < tl) ok = ok && (__ldg(&tbl->tools[t].name[lane + 32u]) == c1);
-        if (__all_sync(kFull, ok)) {
-            cls = __ldg(&tbl->tools[t].class_id);
-            unknown = false;
-            break;
-        }
-    }
-
-    const uint64_t total = warp_sum64(sum_lane);
-    const uint64_t h = route_hash_final(total, len, nlen);
-
-    // provider selection: lane p scores provider p; max score, ties to the lowest index
-    const uint32_t np = __ldg(&tbl->n_providers);
-    bool elig = false;
-    uint64_t score = 0;
-    if (lane < np) {
-        const uint4 row = __ldg(reinterpret_cast<const uint4*>(&tbl->providers[lane]));
-        const uint32_t max_tokens = row.x, weight = row.y, tool_mask = row.z, salt = row.w;
-        elig  = weight != 0u && ((tool_mask >> cls) & 1u) != 0u && tok <= max_tokens;
-        score = provider_score(h, salt, weight);
-    }
-    uint32_t prov = PK_PROVIDER_NONE;
-    if (__ballot_sync(kFull, elig) != 0u) {
-        const uint32_t hi = elig ? (uint32_t)(score >> 32) : 0u;
-        const uint32_t mh = __reduce_max_sync(kFull, hi);
-        const bool     c  = elig && hi == mh;
-        const uint32_t lo = c ? (uint32_t)score : 0u;
-        const uint32_t ml = __reduce_max_sync(kFull, lo);
-        prov = (uint32_t)__ffs((int)__ballot_sync(kFull, c && lo == ml)) - 1u;
-    }
-
-    const uint32_t flags = ((orb & 0x80808080u) ? PK_FLAG_NONASCII : 0u) |
-                           (prov == PK_PROVIDER_NONE ? PK_FLAG_NO_PROVIDER : 0u) |
-                           (len == 0u ? PK_FLAG_EMPTY_PAYLOAD : 0u) |
-                           (unknown ? PK_FLAG_UNKNOWN_TOOL : 0u);
-
-    // 24-byte record as three u64 words, one per lane: a single coalesced store
-    if (lane < 3) {
-        uint64_t word;
-        if (lane == 0)      word = (uint64_t)len | ((uint64_t)tok << 32);
-        else if (lane == 1) word = h;
-        else                word = (uint64_t)(cls & 0xFFu) | ((uint64_t)(prov & 0xFFu) << 8) |
-                                   ((uint64_t)flags << 16) | (200ull << 32);   // Status.Code 200, mock.go:26
-        reinterpret_cast<uint64_t*>(P.out)[(size_t)req * 3 + lane] = word;
-    }
+    tok = tok128 >> 7;
 }
 
+// Fold one segment of a long request into its scratch entry; the warp that arrives last reads
+// the totals (resetting the entry to zero for the next launch) and lane 0 finalises.
+__device__ __forceinline__ void fold_long_segment(const RouteParams& P, uint32_t req, uint32_t len,
+                                                  uint64_t digest, uint32_t tok, uint32_t lane)
+{
+    const uint32_t nseg = (len + kSegBytes - 1u) / kSegBytes;
+    const uint64_t sum  = warp_sum64(digest);
+    const uint32_t tsum = __reduce_add_sync(kFull, tok);
+    if (lane != 0) return;
+    SegScratch* s = P.scratch + req;
+    atomicAdd(&s->hash_sum, (unsigned long long)sum);
+    atomicAdd(&s->tok, tsum);
+    __threadfence();
+    if (atomicAdd(&s->arrived, 1u) != nseg - 1u) return;
+    __threadfence();
+    const uint64_t total = atomicExch(&s->hash_sum, 0ull);
+    const uint32_t ttok  = atomicExch(&s->tok, 0u);
+    atomicExch(&s->arrived, 0u);
+    const uint32_t noff = P.name_off[req];
+    decide(P.table, P.names + noff, P.name_off[req + 1] - noff, len, total, ttok, P.out + req);
+}
+
+template <int G>
 __global__ void __launch_bounds__(kThreads, 4) route_kernel(const RouteParams P)
 {
-    const uint32_t lane   = threadIdx.x & 31u;
-    const uint32_t warp   = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
-    const uint32_t stride = gridDim.x * kWarpsPerCta;
-    const uint32_t ntasks = P.n + P.n_extra;
+    __shared__ uint64_t psum[kPartialSlots];     // [k][R+1]: lane-in-group k's digest for request i
+    __shared__ uint32_t ptok[kPartialSlots];
 
-    for (uint32_t task = warp; task < ntasks; task += stride) {
-        uint32_t req, seg;
-        if (task < P.n) {
-            req = task;
-            seg = 0;
-        } else {
-            const uint2 e = __ldg(P.extra + (task - P.n));
-            req = e.x;
-            seg = e.y;
-        }
-        const uint32_t len  = __ldg(P.pay_len + req);
-        const uint64_t off  = __ldg(P.pay_off + req);
-        const uint32_t nseg = len <= kSegBytes ? 1u : (len + kSegBytes - 1u) / kSegBytes;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t wid  = threadIdx.x >> 5;
+    const uint32_t R    = P.reqs_per_cta;
+    const uint32_t n_req_ctas = (P.n + R - 1u) / R;
 
-        const Partial part = scan_segment(P.payload + off, len, seg, lane);
-        const uint32_t tok = __reduce_add_sync(kFull, part.tok);
-        const uint32_t orb = __reduce_or_sync(kFull, part.orbits);
-
-        if (nseg == 1u) {
-            finalize_request(P, req, len, part.sum, tok, orb, lane);
-            continue;
-        }
-
-        // long request: fold this segment into the request's scratch entry; the warp
-        // that arrives last reads the totals (resetting the entry to zero) and finalises
-        const uint64_t sum = warp_sum64(part.sum);
-        SegScratch* s = P.scratch + req;
-        uint32_t last = 0;
-        if (lane == 0) {
-            atomicAdd(&s->hash_sum, (unsigned long long)sum);
-            atomicAdd(&s->tok, tok);
-            atomicOr(&s->orbits, orb);
-            __threadfence();
-            last = (atomicAdd(&s->arrived, 1u) == nseg - 1u) ? 1u : 0u;
-        }
-        last = __shfl_sync(kFull, last, 0);
-        if (last) {
-            uint64_t tsum = 0;
-            uint32_t ttok = 0, torb = 0;
-            if (lane == 0) {
-                __threadfence();
-                tsum = atomicExch(&s->hash_sum, 0ull);
-                ttok = atomicExch(&s->tok, 0u);
-                torb = atomicExch(&s->orbits, 0u);
-                atomicExch(&s->arrived, 0u);
-            }
-            ttok = __shfl_sync(kFull, ttok, 0);
-            torb = __shfl_sync(kFull, torb, 0);
-            finalize_request(P, req, len, tsum, ttok, torb, lane);   // tsum is 0 on lanes != 0
-        }
+    if (blockIdx.x >= n_req_ctas) {
+        // ---- extra segments (>= 1) of long requests: one warp per (request, segment) ----
+        const uint32_t task = (blockIdx.x - n_req_ctas) * kWarpsPerCta + wid;
+        if (task >= P.n_extra) return;
+        const uint2 e = __ldg(P.extra + task);
+        const uint32_t len = __ldg(P.pay_len + e.x);
+        uint64_t digest;
+        uint32_t tok;
+        scan_segment(P.payload + __ldg(P.pay_off + e.x), len, e.y, lane, P.one, digest, tok);
+        fold_long_segment(P, e.x, len, digest, tok, lane);
+        return;
     }
+
+    const uint32_t base_req = blockIdx.x * R;
+    const uint32_t r_here   = min(R, P.n - base_req);
+    const uint32_t ld       = R + 1u;            // odd leading dimension: conflict-free columns
+    constexpr uint32_t kGroups = 32u / G;
+    const uint32_t grp = lane / G, lig = lane % G;
+
+    // ---- phase 1: scan (first segment of) each request ----
+    for (uint32_t i = wid * kGroups + grp; i < r_here; i += kWarpsPerCta * kGroups) {
+        const uint32_t req = base_req + i;
+        const uint32_t len = __ldg(P.pay_len + req);
+        const uint8_t* pay = P.payload + __ldg(P.pay_off + req);
+        uint64_t digest;
+        uint32_t tok;
+        if (G == 32) {
+            scan_segment(pay, len, 0u, lane, P.one, digest, tok);
+            if (len > kSegBytes) {               // warp-uniform: the whole warp owns this request
+                fold_long_segment(P, req, len, digest, tok, lane);
+                continue;
+            }
+        } else {
+            scan_tiny<G>(pay, len, lig, P.one, digest, tok);
+        }
+        psum[lig * ld + i] = digest;
+        ptok[lig * ld + i] = tok;
+    }
+    __syncthreads();
+
+    // ---- phase 2: one thread per request ----
+    for (uint32_t t = threadIdx.x; t < r_here; t += kThreads) {
+        const uint32_t req = base_req + t;
+        const uint32_t len = __ldg(P.pay_len + req);
+        if (G == 32 && len > kSegBytes) continue;        // finalised by its last segment
+        uint64_t sum = 0;
+        uint32_t tok = 0;
+#pragma unroll
+        for (int k = 0; k < G; ++k) {
+            sum += psum[k * ld + t];
+            tok += ptok[k * ld + t];
+        }
+        const uint32_t noff = __ldg(P.name_off + req);
+        decide(P.table, P.names + noff, __ldg(P.name_off + req + 1) - noff, len, sum, tok, P.out + req);
+    }
+}
+
+uint32_t pow2_floor(uint32_t x)
+{
+    uint32_t p = 1;
+    while (p * 2u <= x) p *= 2u;
+    return p;
 }
 
 }  // namespace
 
-cudaError_t launch_route(const RouteParams& p, int num_sms, cudaStream_t stream)
+cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStream_t stream)
 {
-    const uint64_t ntasks = (uint64_t)p.n + p.n_extra;
-    if (ntasks == 0) return cudaSuccess;
-    uint64_t ctas = (ntasks + kWarpsPerCta - 1) / kWarpsPerCta;
-    const uint64_t cap = (uint64_t)num_sms * 8;      // persistent beyond two full waves of 4 CTAs/SM
-    if (ctas > cap) ctas = cap;
-    route_kernel<<<(unsigned)ctas, kThreads, 0, stream>>>(p);
+    if (p.n == 0) return cudaSuccess;
+    // lanes per request: a full warp, or a half / quarter warp when every payload fits one step
+    const int G = max_len <= 8u * kBlockBytes ? 8 : max_len <= 16u * kBlockBytes ? 16 : 32;
+    const uint32_t r_min = kWarpsPerCta * (32u / G);          // one request per lane group per pass
+    const uint32_t r_max = G == 32 ? 64u : G == 16 ? 128u : 256u;   // G * (R + 1) <= kPartialSlots
+    // enough CTAs to fill the machine (4 per SM resident), then as many requests per CTA as
+    // possible so that phase 2 runs with full warps
+    uint32_t R = pow2_floor(p.n / (uint32_t)(num_sms * 4) + 1u);
+    static const char* const r_env = std::getenv("PK_REQS_PER_CTA");     // tuning aid (power of two)
+    if (r_env && std::atoi(r_env) > 0) R = pow2_floor((uint32_t)std::atoi(r_env));
+    R = R < r_min ? r_min : R > r_max ? r_max : R;
+    p.reqs_per_cta = R;
+    p.one = 1u;
+    const uint32_t ctas = (p.n + R - 1u) / R + (p.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
+    switch (G) {
+    case 8:  route_kernel<8><<<ctas, kThreads, 0, stream>>>(p); break;
+    case 16: route_kernel<16><<<ctas, kThreads, 0, stream>>>(p); break;
+    default: route_kernel<32><<<ctas, kThreads, 0, stream>>>(p); break;
+    }
     return cudaGetLastError();
 }
 

@@ -11,11 +11,10 @@ namespace pk {
 // segments are scanned by different warps.  All-zero between launches: the warp that
 // finalises a request reads its entry with atomicExch(…, 0).
 struct __align__(32) SegScratch {
-    unsigned long long hash_sum;
-    uint32_t tok;        // est_tokens partial sum
-    uint32_t orbits;     // OR of all payload words
-    uint32_t arrived;    // segments done
-    uint32_t pad[3];
+    unsigned long long hash_sum;   // sum of stripe digests so far
+    uint32_t tok;                  // est_tokens partial sum
+    uint32_t arrived;              // segments done
+    uint32_t pad[4];
 };
 static_assert(sizeof(SegScratch) == 32, "SegScratch is 32 bytes");
 
@@ -31,9 +30,12 @@ struct RouteParams {
     pk_decision*    out;         // n
     uint32_t        n;
     uint32_t        n_extra;
+    uint32_t        reqs_per_cta;   // R: set by launch_route
+    uint32_t        one;            // the integer 1 (see pk_spec.cuh: keeps adds on the FMA pipe)
 };
 
-// Chooses grid/block and launches the fused scan+hash+select kernel on `stream`.
-cudaError_t launch_route(const RouteParams& p, int num_sms, cudaStream_t stream);
+// Chooses the lane-group width, requests per CTA and grid, and launches the fused
+// scan+hash+select kernel on `stream`.  max_len: the longest payload of the batch.
+cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStream_t stream);
 
 }  // namespace pk

@@ -1,12 +1,15 @@
 // pk_spec.cuh — constants and per-block arithmetic of the routing SPEC (DESIGN.md "SPEC"),
 // shared by every kernel.  The functions here are __host__ __device__ so that
-// tests/test_swar_host.py can compile this header with g++ and check the SWAR byte
-// classifier and the stripe round against the byte-at-a-time oracle without a GPU.
+// tests/test_swar_host.py can compile this header with g++ and check the SIMD-in-word byte
+// classifier, the stripe round and the selection rule against the byte-at-a-time oracle
+// without a GPU.
 //
-// Reference-pinned: only the tool-name switch (internal/service/mock.go:32-64), which
-// lives in pk_kernels.cu.  Everything in this header is build-defined.
+// Reference-pinned: only the tool-name switch (internal/service/mock.go:32-64).
+// Everything else in this header is build-defined.
 #pragma once
 #include <stdint.h>
+
+#include "../../include/pk_route.h"
 
 #if defined(__CUDACC__)
 #define PK_HD __host__ __device__ __forceinline__
@@ -20,7 +23,7 @@ constexpr uint32_t kBlockBytes   = 16;      // one 16-byte block = one lane's ve
 constexpr uint32_t kStripes      = 32;      // stripes per segment = warp width
 constexpr uint32_t kSegBlocks    = 1024;    // blocks per segment (16 KiB)
 constexpr uint32_t kSegBytes     = kSegBlocks * kBlockBytes;
-constexpr uint32_t kP1 = 0x9E3779B1u, kP2 = 0x85EBCA77u, kP3 = 0xC2B2AE3Du, kP5 = 0x165667B1u;
+constexpr uint32_t kP1 = 0x9E3779B1u, kP2 = 0x85EBCA77u, kP5 = 0x165667B1u;
 constexpr uint64_t kNameMul = 0xD6E8FEB86659FD93ull;
 constexpr uint64_t kFmixC1 = 0xFF51AFD7ED558CCDull, kFmixC2 = 0xC4CEB9FE1A85EC53ull;
 
@@ -65,53 +68,43 @@ PK_HD uint64_t fmix64(uint64_t x)
 }
 
 // ---- SPEC §B, four bytes at a time ------------------------------------------------
-// Returns the letter mask of this word (bit 7 of byte i set iff byte i is an ASCII
-// letter; other bits are don't-care) and adds 128 per token-starting byte to tok128.
-//   x          4 payload bytes, little endian (byte i = payload[o+i]); bytes past the
-//              payload end must already be zero (zero is a separator: counts nothing)
-//   prev_lm    letter mask of the previous word (only its bit 31 is used)
-//   brk        0x00000080 if o % 8 == 0 (a letter run is cut at every 8th offset), else 0
-// Letter mask of a word: bit 7 of byte i set iff byte i is an ASCII letter (other bits
-// are don't-care).  Depends on the word alone, so a lane can hand the mask of its last
-// word to its neighbour before scanning.
-PK_HD uint32_t letter_mask(uint32_t x)
+// Every quantity is a "flag word": bit 7 of byte i carries the predicate for payload byte
+// i of the word, the other bits are don't-care until the final mask.
+//
+// `one` is the integer 1 passed at run time.  a*one + c is an IMAD on the FMA pipe where
+// a + c would be an IADD on the ALU pipe; the classifier is otherwise all LOP3/SHF, so
+// this is what balances the two integer pipes of an SM (see DESIGN.md "Kernels").
+
+// ASCII letter?  folded = byte with bits 5 and 7 cleared: 'A'..'Z' and 'a'..'z' -> 0x41..0x5A
+PK_HD uint32_t letter_mask(uint32_t x, uint32_t one)
 {
-    const uint32_t y  = (x & 0x7F7F7F7Fu) | 0x20202020u;
-    const uint32_t a1 = y + 0x1F1F1F1Fu;          // bit7: folded byte >= 'a'
-    const uint32_t a2 = y + 0x05050505u;          // bit7: folded byte >  'z'
-    return a1 & ~a2 & ~x;
+    const uint32_t t  = x & 0x5F5F5F5Fu;
+    const uint32_t a1 = t * one + 0x3F3F3F3Fu;     // bit7: folded >= 0x41
+    const uint32_t a2 = t * one + 0x25252525u;     // bit7: folded >= 0x5B
+    return a1 & ~a2 & ~x;                          // ... and the byte is ASCII
 }
 
-PK_HD uint32_t scan_word(uint32_t x, uint32_t prev_lm, uint32_t brk, uint32_t& tok128)
+// Token-start flags of one word.  pl: letter flags of the PREVIOUS byte of each byte
+// (bit 7 of byte i = "byte i-1 is a letter"), already cleared where a run is cut.
+PK_HD uint32_t token_flags(uint32_t x, uint32_t lm, uint32_t pl, uint32_t one)
 {
-    const uint32_t g  = (x & 0x7F7F7F7Fu) + 0x5F5F5F5Fu;   // bit7: low 7 bits >= 0x21
-    const uint32_t lm = letter_mask(x);
-    const uint32_t pl = shift_in_prev_byte(prev_lm, lm);
-    const uint32_t c  = lm & pl & ~brk;           // letter continuing a run
-    const uint32_t s  = x << 1;                   // bit7: bit 6 of the byte
-    const uint32_t m  = ((g & ~x & ~c) | (x & s)) & 0x80808080u;   // graphic ASCII not continuing, or UTF-8 lead
-    tok128 = add_flag_bytes(m, tok128);
-    return lm;
+    const uint32_t g = (x & 0x7F7F7F7Fu) * one + 0x5F5F5F5Fu;   // bit7: low 7 bits >= 0x21
+    const uint32_t s = x * 2u;                                  // bit7: bit 6 of the byte
+    const uint32_t u = g & ~(lm & pl);             // graphic, and not a letter continuing a run
+    return ((x & s) | (~x & u)) & 0x80808080u;     // byte >= 0xC0 (UTF-8 lead), or ASCII and u
 }
 
-// One 16-byte block.  prev_lm: letter mask of the word before this block (bit 31).
-// Returns the letter mask of the block's last word.
-PK_HD uint32_t scan_block(const Words4& b, uint32_t prev_lm, uint32_t& tok128, uint32_t& orbits)
+// One 16-byte block at payload offset 16k.  A letter run is cut at every offset that is a
+// multiple of 8, i.e. at byte 0 of words 0 and 2 — so a block never needs its neighbour.
+// Bytes past the payload end must already be zero (zero is a separator: counts nothing).
+PK_HD void scan_block(const Words4& b, uint32_t one, uint32_t& tok128)
 {
-    uint32_t l0 = scan_word(b.w[0], prev_lm, 0x80u, tok128);
-    uint32_t l1 = scan_word(b.w[1], l0, 0u, tok128);
-    uint32_t l2 = scan_word(b.w[2], l1, 0x80u, tok128);
-    uint32_t l3 = scan_word(b.w[3], l2, 0u, tok128);
-    orbits |= (b.w[0] | b.w[1]) | (b.w[2] | b.w[3]);
-    return l3;
-}
-
-// Is byte b an ASCII letter?  Returned in "letter mask" form (bit 31), for the byte that
-// precedes a task's first block.
-PK_HD uint32_t letter_mask_of_byte(uint32_t b)
-{
-    const uint32_t y = (b & 0x7Fu) | 0x20u;
-    return (b < 0x80u && y >= 0x61u && y <= 0x7Au) ? 0x80000000u : 0u;
+    const uint32_t l0 = letter_mask(b.w[0], one), l1 = letter_mask(b.w[1], one);
+    const uint32_t l2 = letter_mask(b.w[2], one), l3 = letter_mask(b.w[3], one);
+    tok128 = add_flag_bytes(token_flags(b.w[0], l0, l0 << 8, one), tok128);
+    tok128 = add_flag_bytes(token_flags(b.w[1], l1, shift_in_prev_byte(l0, l1), one), tok128);
+    tok128 = add_flag_bytes(token_flags(b.w[2], l2, l2 << 8, one), tok128);
+    tok128 = add_flag_bytes(token_flags(b.w[3], l3, shift_in_prev_byte(l2, l3), one), tok128);
 }
 
 // Zero the bytes of a block that lie at or past `valid` (0..16) bytes.
@@ -165,14 +158,73 @@ PK_HD uint64_t route_hash_final(uint64_t sum, uint32_t pay_len, uint32_t name_le
     return fmix64(sum + ((uint64_t)name_len << 32) + (uint64_t)pay_len);
 }
 
-// ---- SPEC §D ----------------------------------------------------------------------
-PK_HD uint64_t provider_score(uint64_t route_hash, uint32_t salt, uint32_t weight)
+// ---- SPEC §A + §D: one request's decision from its scan results ---------------------
+// Sequential (one thread per request): name terms of the hash, the tool switch
+// (internal/service/mock.go:32-64: whole-name, case-sensitive byte equality, first match
+// wins, no match = the default branch — a class, not an error), final hash, provider.
+//   payload_sum   sum of the payload's stripe digests (SPEC §C)
+//   tok           est_tokens (SPEC §B)
+// Provider rule: among eligible providers (weight != 0, serves the tool class,
+// tok <= max_tokens) pick with probability weight / total weight, deterministically from
+// the top 32 bits of the route hash: x = (hi32(hash) * W) >> 32, first provider whose
+// cumulative weight exceeds x.
+PK_HD void decide(const pk_table* __restrict__ tbl, const uint8_t* __restrict__ name,
+                  uint32_t name_len, uint32_t pay_len, uint64_t payload_sum, uint32_t tok,
+                  pk_decision* __restrict__ out)
 {
-    uint32_t r = ((uint32_t)route_hash ^ salt) * kP2 + (uint32_t)(route_hash >> 32);
-    r ^= r >> 15;
-    r *= kP3;
-    r ^= r >> 13;
-    return (uint64_t)r * (uint64_t)weight;
+    uint64_t sum = payload_sum;
+    for (uint32_t j = 0; j < name_len; ++j) sum += name_term(j, name[j]);
+
+    uint32_t cls = tbl->default_class;
+    uint32_t unknown = 1;
+    const uint32_t nt = tbl->n_tools;
+    for (uint32_t t = 0; t < nt; ++t) {
+        if (tbl->tools[t].name_len != name_len) continue;
+        uint32_t j = 0;
+        while (j < name_len && tbl->tools[t].name[j] == name[j]) ++j;
+        if (j == name_len) { cls = tbl->tools[t].class_id; unknown = 0; break; }
+    }
+
+    const uint64_t h = route_hash_final(sum, pay_len, name_len);
+
+    const uint32_t np = tbl->n_providers;
+    uint32_t total = 0;
+    for (uint32_t p = 0; p < np; ++p) {
+        const pk_provider& e = tbl->providers[p];
+        const bool elig = e.weight != 0u && ((e.tool_mask >> cls) & 1u) != 0u && tok <= e.max_tokens;
+        total += elig ? e.weight : 0u;
+    }
+    uint32_t prov = PK_PROVIDER_NONE;
+    if (total != 0u) {
+        const uint32_t x = (uint32_t)(((uint64_t)(uint32_t)(h >> 32) * (uint64_t)total) >> 32);
+        uint32_t cum = 0;
+        for (uint32_t p = 0; p < np; ++p) {
+            const pk_provider& e = tbl->providers[p];
+            const bool elig = e.weight != 0u && ((e.tool_mask >> cls) & 1u) != 0u && tok <= e.max_tokens;
+            cum += elig ? e.weight : 0u;
+            if (cum > x) { prov = p; break; }
+        }
+    }
+
+    const uint32_t flags = (prov == PK_PROVIDER_NONE ? PK_FLAG_NO_PROVIDER : 0u) |
+                           (pay_len == 0u ? PK_FLAG_EMPTY_PAYLOAD : 0u) |
+                           (unknown ? PK_FLAG_UNKNOWN_TOOL : 0u);
+#if defined(__CUDA_ARCH__)
+    // the 24-byte record as three 8-byte stores
+    uint64_t* o = reinterpret_cast<uint64_t*>(out);
+    o[0] = (uint64_t)pay_len | ((uint64_t)tok << 32);
+    o[1] = h;
+    o[2] = (uint64_t)(cls & 0xFFu) | ((uint64_t)(prov & 0xFFu) << 8) | ((uint64_t)flags << 16) |
+           (200ull << 32);                          // Status.Code 200, mock.go:26
+#else
+    out->byte_len = pay_len;
+    out->est_tokens = tok;
+    out->route_hash = h;
+    out->tool_class = (uint8_t)cls;
+    out->provider = (uint8_t)prov;
+    out->flags = (uint16_t)flags;
+    out->status = 200;                              // Status.Code 200, mock.go:26
+#endif
 }
 
 }  // namespace pk

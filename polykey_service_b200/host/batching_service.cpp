@@ -1,0 +1,237 @@
+// batching_service.cpp — see batching_service.hpp.
+#include "batching_service.hpp"
+
+#include <chrono>
+#include <cstring>
+
+namespace polykey {
+
+namespace {
+inline uint64_t round16(uint64_t x) { return (x + 15u) & ~uint64_t(15); }
+using Clock = std::chrono::steady_clock;
+}  // namespace
+
+// ---------------------------------------------------------------- CudaBackend ------------
+CudaBackend::CudaBackend(int device, const pk_table& table, uint32_t max_requests,
+                         uint64_t max_payload_bytes, uint32_t n_slots)
+    : n_slots_(n_slots)
+{
+    pk_config cfg{};
+    cfg.max_requests = max_requests;
+    cfg.n_slots = n_slots;
+    cfg.max_payload_bytes = max_payload_bytes;
+    cfg.max_name_bytes = (uint64_t)max_requests * 256u;
+    status_ = pk_init(device, &table, &cfg, &h_);
+    if (status_ != PK_OK) h_ = nullptr;
+}
+
+CudaBackend::~CudaBackend() { if (h_) pk_destroy(h_); }
+void* CudaBackend::alloc_host(size_t bytes) { return h_ ? pk_host_alloc(h_, bytes) : nullptr; }
+
+int CudaBackend::submit(uint32_t slot, const uint8_t* payload, const uint64_t* pay_off,
+                        const uint32_t* pay_len, const uint8_t* names, const uint32_t* name_off,
+                        uint32_t n, pk_decision* out)
+{
+    if (!h_) return PK_ERR_NO_DEVICE;
+    return pk_submit(h_, slot, payload, pay_off, pay_len, names, name_off, n, out);
+}
+
+int CudaBackend::wait(uint32_t slot) { return h_ ? pk_wait(h_, slot) : PK_ERR_NO_DEVICE; }
+
+std::string CudaBackend::error_string(int status)
+{
+    std::string s = pk_strerror(status);
+    if (status == PK_ERR_CUDA && h_) s += " [cudaError " + std::to_string(pk_last_cuda_error(h_)) + "]";
+    return s;
+}
+
+// ---------------------------------------------------------------- BatchingService --------
+BatchingService::BatchingService(Service* inner, std::vector<RouteBackend*> backends, BatchingConfig cfg)
+    : inner_(inner), cfg_(cfg)
+{
+    for (RouteBackend* be : backends) {
+        auto s = std::make_unique<Shard>();
+        s->be = be;
+        s->arenas.resize(be->slots());
+        for (Arena& a : s->arenas) {
+            a.payload = static_cast<uint8_t*>(be->alloc_host(cfg_.max_payload_bytes + 64));
+            a.out = static_cast<pk_decision*>(be->alloc_host((size_t)cfg_.max_batch * sizeof(pk_decision)));
+            a.pay_off.resize(cfg_.max_batch + 1);
+            a.pay_len.resize(cfg_.max_batch);
+            a.name_off.resize(cfg_.max_batch + 1);
+            a.reqs.reserve(cfg_.max_batch);
+            if (!a.payload || !a.out) healthy_.store(false);
+        }
+        shards_.push_back(std::move(s));
+    }
+    if (shards_.empty()) healthy_.store(false);
+    for (auto& s : shards_) s->th = std::thread(&BatchingService::flusher, this, s.get());
+}
+
+BatchingService::~BatchingService() { Shutdown(); }
+
+void BatchingService::Shutdown()
+{
+    if (stopping_.exchange(true)) {
+        for (auto& s : shards_) if (s->th.joinable()) s->th.join();
+        return;
+    }
+    for (auto& s : shards_) {
+        { std::lock_guard<std::mutex> g(s->mu); }
+        s->cv.notify_all();
+    }
+    for (auto& s : shards_) if (s->th.joinable()) s->th.join();
+}
+
+BatchingStats BatchingService::stats() const
+{
+    BatchingStats t;
+    for (const auto& s : shards_) {
+        std::lock_guard<std::mutex> g(s->mu);
+        t.requests += s->st.requests; t.batches += s->st.batches; t.flush_full += s->st.flush_full;
+        t.flush_deadline += s->st.flush_deadline; t.errors += s->st.errors;
+        if (s->st.max_batch_seen > t.max_batch_seen) t.max_batch_seen = s->st.max_batch_seen;
+    }
+    return t;
+}
+
+Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, const Struct* parameters,
+                                    const std::string* secretId, const Metadata* metadata)
+{
+    if (stopping_.load() || shards_.empty())
+        return Result{nullptr, std::string("routing stage is shut down")};
+    if (!healthy_.load())
+        return Result{nullptr, std::string("routing stage is unhealthy")};
+
+    Pending p;
+    p.name = &toolName;
+    if (parameters) p.payload = to_json(*parameters);       // the request's prompt payload bytes
+    if (round16(p.payload.size()) > cfg_.max_payload_bytes)
+        return Result{nullptr, std::string("request payload exceeds the routing stage's arena")};
+
+    const uint64_t id = next_id_.fetch_add(1);
+    Shard* s = shards_[id % shards_.size()].get();          // shard by request id, no exchange
+    {
+        std::lock_guard<std::mutex> g(s->mu);
+        if (stopping_.load()) return Result{nullptr, std::string("routing stage is shut down")};
+        s->q.push_back(&p);
+    }
+    s->cv.notify_one();
+    {
+        std::unique_lock<std::mutex> w(p.mu);               // block this RPC's thread only
+        p.cv.wait(w, [&] { return p.done; });
+    }
+
+    if (p.rc != 0) {
+        // plain error: server.go:37-40 returns it verbatim (gRPC Unknown)
+        return Result{nullptr, "routing failed: " + s->be->error_string(p.rc)};
+    }
+    Result r = inner_->ExecuteTool(ctx, toolName, parameters, secretId, metadata);
+    if (r.resp) r.resp->decision = p.decision;
+    return r;
+}
+
+void BatchingService::complete(Shard* s, Arena& a, int rc)
+{
+    if (rc == 0) rc = s->be->wait((uint32_t)(&a - s->arenas.data()));
+    if (rc != 0) {
+        healthy_.store(false);
+        std::lock_guard<std::mutex> g(s->mu);
+        ++s->st.errors;
+    }
+    for (size_t i = 0; i < a.reqs.size(); ++i) {
+        Pending* p = a.reqs[i];
+        std::lock_guard<std::mutex> w(p->mu);
+        p->rc = rc;
+        if (rc == 0) p->decision = a.out[i];
+        p->done = true;
+        p->cv.notify_one();
+    }
+    a.reqs.clear();
+    a.inflight = false;
+}
+
+void BatchingService::flusher(Shard* s)
+{
+    const size_t depth = s->arenas.size();
+    std::deque<size_t> inflight;                            // submitted slots, oldest first
+    std::vector<size_t> free_slots;
+    for (size_t i = depth; i-- > 0;) free_slots.push_back(i);
+
+    auto finish_oldest = [&] {
+        const size_t slot = inflight.front();
+        inflight.pop_front();
+        complete(s, s->arenas[slot], 0);
+        free_slots.push_back(slot);
+    };
+
+    for (;;) {
+        std::unique_lock<std::mutex> lk(s->mu);
+        if (s->q.empty()) {
+            if (!inflight.empty()) {                        // nothing new: finish the oldest batch now
+                lk.unlock();
+                finish_oldest();
+                continue;
+            }
+            if (stopping_.load()) return;
+            s->cv.wait(lk, [&] { return !s->q.empty() || stopping_.load(); });
+            if (s->q.empty()) return;
+        }
+        // a batch is open: wait for it to fill or for the deadline of its first request
+        const auto deadline = Clock::now() + std::chrono::microseconds(cfg_.max_wait_us);
+        bool full = s->q.size() >= cfg_.max_batch;
+        while (!full && !stopping_.load()) {
+            if (s->cv.wait_until(lk, deadline) == std::cv_status::timeout) break;
+            full = s->q.size() >= cfg_.max_batch;
+        }
+        if (free_slots.empty()) {                           // free the slot we are about to reuse
+            lk.unlock();
+            finish_oldest();
+            lk.lock();
+        }
+        const size_t slot = free_slots.back();
+        free_slots.pop_back();
+        Arena& a = s->arenas[slot];
+        uint64_t at = 0;
+        uint32_t n = 0;
+        while (!s->q.empty() && n < cfg_.max_batch) {
+            Pending* p = s->q.front();
+            const uint64_t sz = round16(p->payload.size());
+            if (at + sz > cfg_.max_payload_bytes) break;    // arena full: the rest goes to the next batch
+            s->q.pop_front();
+            a.pay_off[n] = at;
+            a.pay_len[n] = (uint32_t)p->payload.size();
+            a.reqs.push_back(p);
+            at += sz;
+            ++n;
+        }
+        ++s->st.batches;
+        s->st.requests += n;
+        if (full) ++s->st.flush_full; else ++s->st.flush_deadline;
+        if (n > s->st.max_batch_seen) s->st.max_batch_seen = n;
+        lk.unlock();
+
+        // pack outside the lock: one memcpy per request into the (pinned) arena — gRPC buffers
+        // live on the caller's heap and cannot be DMA sources
+        a.names.clear();
+        for (uint32_t i = 0; i < n; ++i) {
+            const Pending* p = a.reqs[i];
+            if (!p->payload.empty()) std::memcpy(a.payload + a.pay_off[i], p->payload.data(), p->payload.size());
+            a.name_off[i] = (uint32_t)a.names.size();
+            a.names.insert(a.names.end(), p->name->begin(), p->name->end());
+        }
+        a.pay_off[n] = at;
+        a.name_off[n] = (uint32_t)a.names.size();
+        const int rc = s->be->submit((uint32_t)slot, a.payload, a.pay_off.data(), a.pay_len.data(),
+                                     a.names.data(), a.name_off.data(), n, a.out);
+        if (rc != 0) {
+            complete(s, a, rc);                             // fail exactly this batch's requests
+            free_slots.push_back(slot);
+        } else {
+            a.inflight = true;
+            inflight.push_back(slot);
+        }
+    }
+}
+
+}  // namespace polykey

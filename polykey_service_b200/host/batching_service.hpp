@@ -1,0 +1,134 @@
+// batching_service.hpp — the batching front-end that sits at the reference's plugin seam.
+//
+// `BatchingService` implements the same one-method interface as the reference's
+// service.Service (internal/service/service.go:13-15) and is handed to the server exactly
+// where NewMockService() is today (cmd/polykey/main.go:85-86):
+//
+//     inner   := service.NewMockService()
+//     batched := NewBatchingService(inner, backends, cfg)      // <- new
+//     srv     := server.NewServer(batched)
+//
+// grpc-go calls ExecuteTool from one goroutine (here: thread) per in-flight RPC, concurrently
+// and without a limit (main.go:74-77), so this is a multi-producer / single-consumer design:
+// callers enqueue and block on their own request; ONE flusher thread per GPU coalesces the
+// queue into the flat arenas of include/pk_route.h (size- or deadline-triggered), crosses the
+// C ABI once per batch (pk_submit / pk_wait, `pipeline_depth` batches in flight), hands each
+// caller its 24-byte decision, and the caller then delegates to the inner service for the
+// response body — so the gRPC surface and mock.go stay unchanged.
+//
+// Requests shard across GPUs by request id (id % n_gpus); there is no exchange between GPUs.
+// A device error is returned to every request of the failed batch as a plain error (surfaced
+// verbatim by server.go:37-40, i.e. gRPC Unknown) and flips healthy() to false so main can
+// set health to NOT_SERVING (main.go:93-94).  Shutdown() drains the queues before
+// GracefulStop (main.go:118-119).
+#pragma once
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <thread>
+
+#include "service.hpp"
+
+namespace polykey {
+
+// One routing device.  CudaBackend binds libpkroute.so; tests inject a CPU stand-in.
+class RouteBackend {
+public:
+    virtual ~RouteBackend() = default;
+    virtual uint32_t slots() const = 0;
+    // memory the flusher packs batches into (pinned for the CUDA backend)
+    virtual void* alloc_host(size_t bytes) = 0;
+    virtual int submit(uint32_t slot, const uint8_t* payload, const uint64_t* pay_off,
+                       const uint32_t* pay_len, const uint8_t* names, const uint32_t* name_off,
+                       uint32_t n, pk_decision* out) = 0;
+    virtual int wait(uint32_t slot) = 0;
+    virtual std::string error_string(int status) = 0;
+};
+
+// libpkroute.so through its C ABI (include/pk_route.h).  No CPU fallback: construction
+// fails (ok() == false, status() != 0) when there is no CUDA device.
+class CudaBackend final : public RouteBackend {
+public:
+    CudaBackend(int device, const pk_table& table, uint32_t max_requests, uint64_t max_payload_bytes,
+                uint32_t n_slots);
+    ~CudaBackend() override;
+    bool ok() const { return h_ != nullptr; }
+    int status() const { return status_; }
+    uint32_t slots() const override { return n_slots_; }
+    void* alloc_host(size_t bytes) override;
+    int submit(uint32_t slot, const uint8_t* payload, const uint64_t* pay_off, const uint32_t* pay_len,
+               const uint8_t* names, const uint32_t* name_off, uint32_t n, pk_decision* out) override;
+    int wait(uint32_t slot) override;
+    std::string error_string(int status) override;
+private:
+    pk_handle* h_ = nullptr;
+    int status_ = 0;
+    uint32_t n_slots_ = 0;
+};
+
+struct BatchingConfig {
+    uint32_t max_batch = 4096;             // requests per flush
+    uint32_t max_wait_us = 200;            // deadline from the first queued request
+    uint64_t max_payload_bytes = 32u << 20;
+    uint32_t max_name_bytes_per_request = 64;
+};
+
+struct BatchingStats {
+    uint64_t requests = 0, batches = 0, flush_full = 0, flush_deadline = 0, max_batch_seen = 0, errors = 0;
+};
+
+class BatchingService final : public Service {
+public:
+    // backends: one per GPU; not owned.
+    BatchingService(Service* inner, std::vector<RouteBackend*> backends, BatchingConfig cfg);
+    ~BatchingService() override;
+
+    Result ExecuteTool(Context& ctx, const std::string& toolName, const Struct* parameters,
+                       const std::string* secretId, const Metadata* metadata) override;
+
+    void Shutdown();                        // drain + join; further calls fail with an error
+    bool healthy() const { return healthy_.load(); }
+    BatchingStats stats() const;
+
+private:
+    struct Pending {
+        const std::string* name;
+        std::string payload;
+        pk_decision decision{};
+        int rc = 0;
+        // completion is signalled under `mu`, so the waiter (whose stack owns this object)
+        // cannot return and destroy it while the flusher still touches it
+        std::mutex mu;
+        std::condition_variable cv;
+        bool done = false;
+    };
+    struct Arena {                          // one per backend slot
+        uint8_t* payload = nullptr;
+        pk_decision* out = nullptr;
+        std::vector<uint64_t> pay_off;
+        std::vector<uint32_t> pay_len, name_off;
+        std::vector<uint8_t> names;
+        std::vector<Pending*> reqs;
+        bool inflight = false;
+    };
+    struct Shard {
+        RouteBackend* be = nullptr;
+        std::mutex mu;
+        std::condition_variable cv;
+        std::deque<Pending*> q;
+        std::vector<Arena> arenas;
+        std::thread th;
+        BatchingStats st;
+    };
+    void flusher(Shard* s);
+    void complete(Shard* s, Arena& a, int rc);
+
+    Service* inner_;
+    BatchingConfig cfg_;
+    std::vector<std::unique_ptr<Shard>> shards_;
+    std::atomic<uint64_t> next_id_{0};
+    std::atomic<bool> stopping_{false}, healthy_{true};
+};
+
+}  // namespace polykey

@@ -21,8 +21,7 @@ from oracle import pk_spec_py as S  # noqa: E402
 TOOLS = [(b"example_tool", 0), (b"struct_tool", 1), (b"file_tool", 2)]       # mock.go:33,37,52
 DEFAULT_CLASS = 3                                                             # mock.go:60
 MAXTOK = [4096, 8192, 8192, 32768, 32768, 131072, 131072, 1048576]
-PROVIDERS = [(MAXTOK[p], p + 1, 0x7 if p % 4 == 3 else 0xF, ((p + 1) * 0x9E3779B9) & 0xFFFFFFFF)
-             for p in range(8)]
+PROVIDERS = [(MAXTOK[p], p + 1, 0x7 if p % 4 == 3 else 0xF, 0) for p in range(8)]
 
 # hand-written: (name, expected class, takes the default branch?)
 TOOL_CLASS_ROWS = [

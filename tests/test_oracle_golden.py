@@ -40,7 +40,7 @@ def test_golden_records(oracle):
 def test_default_table_matches_fixture(oracle):
     g = load_golden()
     t = oracle.default_table()
-    got = [[t.providers[p].max_tokens, t.providers[p].weight, t.providers[p].tool_mask, t.providers[p].salt]
+    got = [[t.providers[p].max_tokens, t.providers[p].weight, t.providers[p].tool_mask, t.providers[p].reserved]
            for p in range(t.n_providers)]
     assert got == g["providers"] and t.default_class == g["default_class"]
 
@@ -50,7 +50,7 @@ def test_oracle_vs_python_restatement(oracle, mode):
     from oracle import pk_spec_py as S
     t = oracle.default_table()
     tools = [(bytes(t.tools[k].name[:t.tools[k].name_len]), t.tools[k].class_id) for k in range(t.n_tools)]
-    provs = [(p.max_tokens, p.weight, p.tool_mask, p.salt) for p in list(t.providers)[:t.n_providers]]
+    provs = [(p.max_tokens, p.weight, p.tool_mask, p.reserved) for p in list(t.providers)[:t.n_providers]]
     b = oracle.gen_batch(oracle.SEED_BASE + 17 * mode, 48, 0, 1200, mode=mode)
     rc, out = oracle.route_batch(t, b)
     assert rc == 0
@@ -64,7 +64,7 @@ def test_oracle_multisegment_vs_python(oracle):
     from oracle import pk_spec_py as S
     t = oracle.default_table()
     tools = [(bytes(t.tools[k].name[:t.tools[k].name_len]), t.tools[k].class_id) for k in range(t.n_tools)]
-    provs = [(p.max_tokens, p.weight, p.tool_mask, p.salt) for p in list(t.providers)[:t.n_providers]]
+    provs = [(p.max_tokens, p.weight, p.tool_mask, p.reserved) for p in list(t.providers)[:t.n_providers]]
     b = oracle.gen_batch(99, 3, 16380, 50000, mode=0)
     rc, out = oracle.route_batch(t, b)
     assert rc == 0

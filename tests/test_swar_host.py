@@ -18,17 +18,17 @@ def emul(tmp_path_factory):
     subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so,
                            os.path.join(HERE, "host_emul.cpp")])
     L = C.CDLL(so)
-    L.emul_route_one.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p]
+    L.emul_route_one.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
     return L
 
 
-def run_emul(emul, oracle, table, b):
+def run_emul(emul, oracle, table, b, lanes=32):
     n = b["pay_len"].size
     got = np.zeros(n, dtype=oracle.DECISION_DTYPE)
     for i in range(n):
         emul.emul_route_one(C.byref(table), b["payload"].ctypes.data + int(b["pay_off"][i]),
                             int(b["pay_len"][i]), b["names"].ctypes.data + int(b["name_off"][i]),
-                            int(b["name_off"][i + 1] - b["name_off"][i]), got.ctypes.data + 24 * i)
+                            int(b["name_off"][i + 1] - b["name_off"][i]), lanes, got.ctypes.data + 24 * i)
     return got
 
 
@@ -50,3 +50,13 @@ def test_warp_emulation_golden(emul, oracle):
     got = run_emul(emul, oracle, t, b)
     for r, (nm, p, want) in zip(got, rows):
         assert {k: int(r[k]) for k in r.dtype.names} == want, (nm, len(p))
+
+
+@pytest.mark.parametrize("lanes,maxlen", [(16, 256), (8, 128)])
+def test_lane_group_emulation(emul, oracle, lanes, maxlen):
+    """The 16- and 8-lane groups used for batches of tiny payloads."""
+    t = oracle.default_table()
+    for mode in range(5):
+        b = oracle.gen_batch(77 + mode, 300, 0, maxlen, mode=mode)
+        want = oracle.route_batch(t, b)[1]
+        assert_records_equal(run_emul(emul, oracle, t, b, lanes), want, f"lanes {lanes} mode {mode}")
