@@ -33,11 +33,10 @@ static inline uint64_t fmix64(uint64_t x)
 #define K64(b) (0x0101010101010101ull * (uint64_t)(b))
 static inline uint32_t scan_word64(uint64_t x, uint64_t* orbits)
 {
-    const uint64_t v  = x & K64(0x7F);
-    const uint64_t y  = v | K64(0x20);
-    const uint64_t a1 = y + K64(0x1F);            /* bit7: folded byte >= 'a' */
-    const uint64_t a2 = y + K64(0x05);            /* bit7: folded byte >  'z' */
-    const uint64_t g  = v + K64(0x5F);            /* bit7: low 7 bits >= 0x21 */
+    const uint64_t t  = x & K64(0x5F);            /* folded: bits 5 and 7 cleared */
+    const uint64_t a1 = t + K64(0x3F);            /* bit7: folded >= 0x41 */
+    const uint64_t a2 = t + K64(0x25);            /* bit7: folded >= 0x5B */
+    const uint64_t g  = t + K64(0x7F);            /* bit7: folded != 0 (not NUL / space) */
     const uint64_t lm = a1 & ~a2 & ~x;            /* ASCII letter */
     const uint64_t c  = lm & (lm << 8);           /* letter preceded by a letter in this word */
     const uint64_t m  = ((g & ~x & ~c) | (x & (x << 1))) & K64(0x80);

@@ -79,11 +79,11 @@ enum { C_SEP, C_LETTER, C_LEAD, C_CONT, C_OTHER };
 
 static int byte_class(uint8_t b)
 {
-    if (b <= 0x20) return C_SEP;
+    if (b == 0x00 || b == 0x20) return C_SEP;        /* NUL and space; zero padding counts nothing */
     if ((b >= 'A' && b <= 'Z') || (b >= 'a' && b <= 'z')) return C_LETTER;
     if (b >= 0xC0) return C_LEAD;
     if (b >= 0x80) return C_CONT;
-    return C_OTHER;                       /* 0x21..0x7F that is not a letter */
+    return C_OTHER;                       /* any other ASCII byte: digits, punctuation, control, DEL */
 }
 
 uint32_t pk_ref_est_tokens(const uint8_t* p, uint64_t len, int* nonascii)

@@ -39,14 +39,14 @@ def is_letter(b):
 def est_tokens(p: bytes):
     tokens = 0
     for j, b in enumerate(p):
-        if b <= 0x20 or 0x80 <= b <= 0xBF:
-            continue                                  # separators and UTF-8 continuation bytes
+        if b == 0x00 or b == 0x20 or 0x80 <= b <= 0xBF:
+            continue                                  # NUL, space and UTF-8 continuation bytes
         if is_letter(b):
             if j > 0 and is_letter(p[j - 1]) and j % 8 != 0:
                 continue                              # letter run continues
             tokens += 1
         else:
-            tokens += 1                               # lead byte, digit, punctuation, DEL
+            tokens += 1                               # lead byte, digit, punctuation, control, DEL
     return tokens, any(b >= 0x80 for b in p)
 
 

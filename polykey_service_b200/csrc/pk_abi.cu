@@ -41,7 +41,7 @@ struct pk_handle {
     int        device = 0;
     int        num_sms = 0;
     pk_config  cfg{};
-    pk_table*  d_table = nullptr;
+    pk::DevTable* d_table = nullptr;
     size_t     meta_cap = 0;
     uint64_t   max_extra = 0;
     std::vector<Slot> slots;
@@ -263,8 +263,12 @@ int pk_init(int device, const pk_table* tbl, const pk_config* cfg, pk_handle** o
 
     PK_INIT_CUDA(cudaSetDevice(device));
     PK_INIT_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
-    PK_INIT_CUDA(cudaMalloc(&h->d_table, sizeof(pk_table)));
-    PK_INIT_CUDA(cudaMemcpy(h->d_table, tbl, sizeof(pk_table), cudaMemcpyHostToDevice));
+    {
+        pk::DevTable dt;
+        pk::make_dev_table(*tbl, dt);
+        PK_INIT_CUDA(cudaMalloc(&h->d_table, sizeof(pk::DevTable)));
+        PK_INIT_CUDA(cudaMemcpy(h->d_table, &dt, sizeof(pk::DevTable), cudaMemcpyHostToDevice));
+    }
     PK_INIT_CUDA(cudaEventCreate(&h->ev0));
     PK_INIT_CUDA(cudaEventCreate(&h->ev1));
 
@@ -319,7 +323,9 @@ int pk_update_table(pk_handle* h, const pk_table* tbl)
     if (rc) return rc;
     rc = pk_sync(h);
     if (rc) return rc;
-    PK_CUDA(h, cudaMemcpy(h->d_table, tbl, sizeof(pk_table), cudaMemcpyHostToDevice));
+    pk::DevTable dt;
+    pk::make_dev_table(*tbl, dt);
+    PK_CUDA(h, cudaMemcpy(h->d_table, &dt, sizeof(pk::DevTable), cudaMemcpyHostToDevice));
     return PK_OK;
 }
 

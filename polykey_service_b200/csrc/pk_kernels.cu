@@ -37,6 +37,7 @@ constexpr int      kThreads     = kWarpsPerCta * 32;
 constexpr int      kUnroll      = 4;          // 128-bit loads in flight per lane
 constexpr unsigned kFull        = 0xFFFFFFFFu;
 constexpr int      kPartialSlots = 32 * 65;   // >= G * (R + 1) for every (G, R) launch_route picks
+constexpr uint32_t kNameStage   = 4096;       // bytes of tool names a CTA stages in shared memory
 
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p)
 {
@@ -109,15 +110,14 @@ __device__ __forceinline__ void scan_segment(const uint8_t* __restrict__ pay, ui
 }
 
 // A payload of at most G blocks scanned by a group of G lanes: one block per lane, one step.
-template <int G>
-__device__ __forceinline__ void scan_tiny(const uint8_t* __restrict__ pay, uint32_t len,
-                                          uint32_t lig, uint32_t one, uint64_t& digest, uint32_t& tok)
+// x is the lane's (already loaded) block; lanes past the payload's last block hold zeros.
+__device__ __forceinline__ void scan_tiny(uint4 x, uint32_t len, uint32_t lig, uint32_t one,
+                                          uint64_t& digest, uint32_t& tok)
 {
     const uint32_t nblk = (len >> 4) + ((len & 15u) ? 1u : 0u);       // <= G
     uint32_t tok128 = 0;
     digest = 0ull;
     if (lig < nblk) {
-        const uint4 x = ldg_stream(reinterpret_cast<const uint4*>(pay) + lig);
         Words4 w = {{x.x, x.y, x.z, x.w}};
         const uint32_t valid = len - lig * kBlockBytes;
         if (valid < kBlockBytes) mask_tail(w, valid);
@@ -157,6 +157,8 @@ __global__ void __launch_bounds__(kThreads, 4) route_kernel(const RouteParams P)
 {
     __shared__ uint64_t psum[kPartialSlots];     // [k][R+1]: lane-in-group k's digest for request i
     __shared__ uint32_t ptok[kPartialSlots];
+    __shared__ DevTable s_tbl;                   // the routing table, staged once per CTA
+    __shared__ __align__(16) uint8_t s_names[kNameStage];   // this CTA's tool names, when they fit
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t wid  = threadIdx.x >> 5;
@@ -182,24 +184,63 @@ __global__ void __launch_bounds__(kThreads, 4) route_kernel(const RouteParams P)
     constexpr uint32_t kGroups = 32u / G;
     const uint32_t grp = lane / G, lig = lane % G;
 
+    // ---- stage what phase 2 reads, so that its dependent loads hit shared memory; these
+    //      global loads are in flight while phase 1 runs ----
+    static_assert(sizeof(DevTable) % 16 == 0, "DevTable is copied as uint4");
+    if (threadIdx.x < sizeof(DevTable) / 16)
+        reinterpret_cast<uint4*>(&s_tbl)[threadIdx.x] = __ldg(reinterpret_cast<const uint4*>(P.table) + threadIdx.x);
+    const uint32_t names_lo = __ldg(P.name_off + base_req);
+    const uint32_t names_sz = __ldg(P.name_off + base_req + r_here) - names_lo;
+    const bool names_staged = names_sz <= kNameStage;
+    if (names_staged)
+        for (uint32_t j = threadIdx.x; j < names_sz; j += kThreads) s_names[j] = __ldg(P.names + names_lo + j);
+
     // ---- phase 1: scan (first segment of) each request ----
-    for (uint32_t i = wid * kGroups + grp; i < r_here; i += kWarpsPerCta * kGroups) {
-        const uint32_t req = base_req + i;
-        const uint32_t len = __ldg(P.pay_len + req);
-        const uint8_t* pay = P.payload + __ldg(P.pay_off + req);
-        uint64_t digest;
-        uint32_t tok;
-        if (G == 32) {
-            scan_segment(pay, len, 0u, lane, P.one, digest, tok);
+    if (G == 32) {
+        for (uint32_t i = wid; i < r_here; i += kWarpsPerCta) {
+            const uint32_t req = base_req + i;
+            const uint32_t len = __ldg(P.pay_len + req);
+            uint64_t digest;
+            uint32_t tok;
+            scan_segment(P.payload + __ldg(P.pay_off + req), len, 0u, lane, P.one, digest, tok);
             if (len > kSegBytes) {               // warp-uniform: the whole warp owns this request
                 fold_long_segment(P, req, len, digest, tok, lane);
                 continue;
             }
-        } else {
-            scan_tiny<G>(pay, len, lig, P.one, digest, tok);
+            psum[lane * ld + i] = digest;
+            ptok[lane * ld + i] = tok;
         }
-        psum[lig * ld + i] = digest;
-        ptok[lig * ld + i] = tok;
+    } else {
+        // tiny payloads: one block per lane, kPre requests' loads in flight per lane group
+        constexpr uint32_t kPre = 4;
+        constexpr uint32_t kStride = kWarpsPerCta * kGroups;
+        for (uint32_t i0 = wid * kGroups + grp; i0 < r_here; i0 += kPre * kStride) {
+            uint32_t len[kPre];
+            uint4 x[kPre];
+#pragma unroll
+            for (uint32_t u = 0; u < kPre; ++u) {
+                const uint32_t i = i0 + u * kStride;
+                len[u] = 0u;
+                x[u] = make_uint4(0u, 0u, 0u, 0u);
+                if (i < r_here) {
+                    len[u] = __ldg(P.pay_len + base_req + i);
+                    const uint32_t nblk = (len[u] >> 4) + ((len[u] & 15u) ? 1u : 0u);
+                    if (lig < nblk)
+                        x[u] = ldg_stream(reinterpret_cast<const uint4*>(P.payload + __ldg(P.pay_off + base_req + i)) + lig);
+                }
+            }
+#pragma unroll
+            for (uint32_t u = 0; u < kPre; ++u) {
+                const uint32_t i = i0 + u * kStride;
+                if (i < r_here) {
+                    uint64_t digest;
+                    uint32_t tok;
+                    scan_tiny(x[u], len[u], lig, P.one, digest, tok);
+                    psum[lig * ld + i] = digest;
+                    ptok[lig * ld + i] = tok;
+                }
+            }
+        }
     }
     __syncthreads();
 
@@ -216,7 +257,9 @@ __global__ void __launch_bounds__(kThreads, 4) route_kernel(const RouteParams P)
             tok += ptok[k * ld + t];
         }
         const uint32_t noff = __ldg(P.name_off + req);
-        decide(P.table, P.names + noff, __ldg(P.name_off + req + 1) - noff, len, sum, tok, P.out + req);
+        const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
+        const uint8_t* name = names_staged ? s_names + (noff - names_lo) : P.names + noff;
+        decide(&s_tbl, name, nlen, len, sum, tok, P.out + req);
     }
 }
 

@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include "../../include/pk_route.h"
+#include "pk_spec.cuh"
 
 namespace pk {
 
@@ -25,7 +26,7 @@ struct RouteParams {
     const uint8_t*  names;
     const uint32_t* name_off;    // n+1
     const uint2*    extra;       // (request, segment) for segments >= 1 of long requests
-    const pk_table* table;       // device-resident routing table
+    const DevTable* table;       // device-resident routing table (+ tool-name sums)
     SegScratch*     scratch;     // n entries, zero
     pk_decision*    out;         // n
     uint32_t        n;

@@ -68,43 +68,81 @@ PK_HD uint64_t fmix64(uint64_t x)
 }
 
 // ---- SPEC §B, four bytes at a time ------------------------------------------------
-// Every quantity is a "flag word": bit 7 of byte i carries the predicate for payload byte
-// i of the word, the other bits are don't-care until the final mask.
+// Byte classes: SEP = {0x00, 0x20}; LETTER = A-Z a-z; LEAD = 0xC0..0xFF; CONT = 0x80..0xBF;
+// OTHER = every other ASCII byte (digits, punctuation, control characters, DEL).
+// A token starts at every OTHER byte, every LEAD byte, and every LETTER that does not continue
+// a letter run; runs are cut at every payload offset that is a multiple of 8.
 //
-// `one` is the integer 1 passed at run time.  a*one + c is an IMAD on the FMA pipe where
-// a + c would be an IADD on the ALU pipe; the classifier is otherwise all LOP3/SHF, so
-// this is what balances the two integer pipes of an SM (see DESIGN.md "Kernels").
-
-// ASCII letter?  folded = byte with bits 5 and 7 cleared: 'A'..'Z' and 'a'..'z' -> 0x41..0x5A
-PK_HD uint32_t letter_mask(uint32_t x, uint32_t one)
+// Every quantity is a "flag word": bit 7 of byte i carries the predicate for byte i of the
+// word, the other bits are don't-care until the final mask.  On the device the five logic ops
+// are explicit lop3 (the compiler otherwise re-associates them into seven) and the three range
+// tests are mad.lo with a run-time multiplier `one` == 1: a*one + c is an IMAD on the FMA pipe
+// where a + c would be an IADD on the ALU pipe, which is what balances the SM's two integer
+// pipes (DESIGN.md "Kernels").
+#if defined(__CUDA_ARCH__)
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c)
 {
-    const uint32_t t  = x & 0x5F5F5F5Fu;
-    const uint32_t a1 = t * one + 0x3F3F3F3Fu;     // bit7: folded >= 0x41
-    const uint32_t a2 = t * one + 0x25252525u;     // bit7: folded >= 0x5B
-    return a1 & ~a2 & ~x;                          // ... and the byte is ASCII
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(d) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+    return d;
+}
+__device__ __forceinline__ uint32_t mad_lo(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+#else
+template <int LUT>
+static inline uint32_t lop3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d = 0;                                  // truth table: bit (a<<2 | b<<1 | c) of LUT
+    for (int bit = 0; bit < 32; ++bit) {
+        const uint32_t idx = (((a >> bit) & 1u) << 2) | (((b >> bit) & 1u) << 1) | ((c >> bit) & 1u);
+        d |= ((uint32_t)(LUT >> idx) & 1u) << bit;
+    }
+    return d;
+}
+static inline uint32_t mad_lo(uint32_t a, uint32_t b, uint32_t c) { return a * b + c; }
+#endif
+
+struct WordScan { uint32_t t, lm; };
+
+// t: the word with bits 5 and 7 of every byte cleared ("folded": A-Z and a-z -> 0x41..0x5A,
+// NUL and space -> 0).  lm: ASCII-letter flags.
+PK_HD WordScan fold_word(uint32_t x, uint32_t one)
+{
+    WordScan r;
+    r.t = x & 0x5F5F5F5Fu;
+    const uint32_t a1 = mad_lo(r.t, one, 0x3F3F3F3Fu);    // bit7: folded >= 0x41
+    const uint32_t a2 = mad_lo(r.t, one, 0x25252525u);    // bit7: folded >= 0x5B
+    r.lm = lop3<0x10>(a1, a2, x);                         // a1 & ~a2 & ~x : letter, and ASCII
+    return r;
 }
 
-// Token-start flags of one word.  pl: letter flags of the PREVIOUS byte of each byte
-// (bit 7 of byte i = "byte i-1 is a letter"), already cleared where a run is cut.
-PK_HD uint32_t token_flags(uint32_t x, uint32_t lm, uint32_t pl, uint32_t one)
+// Token-start flags of one word, pre-masked to bit 7.  pl: letter flags of the PREVIOUS byte of
+// each byte, already cleared where a run is cut.
+PK_HD uint32_t token_flags(uint32_t x, const WordScan& ws, uint32_t pl, uint32_t one)
 {
-    const uint32_t g = (x & 0x7F7F7F7Fu) * one + 0x5F5F5F5Fu;   // bit7: low 7 bits >= 0x21
-    const uint32_t s = x * 2u;                                  // bit7: bit 6 of the byte
-    const uint32_t u = g & ~(lm & pl);             // graphic, and not a letter continuing a run
-    return ((x & s) | (~x & u)) & 0x80808080u;     // byte >= 0xC0 (UTF-8 lead), or ASCII and u
+    const uint32_t g = mad_lo(ws.t, one, 0x7F7F7F7Fu);    // bit7: folded != 0, i.e. not NUL / space
+    const uint32_t a = lop3<0x70>(g, ws.lm, pl);          // g & ~(lm & pl): not a separator, not a continuing letter
+    const uint32_t s = x + x;                             // bit7: bit 6 of the byte
+    const uint32_t m = lop3<0xCA>(x, s, a);               // x ? s : a  -> byte >= 0xC0, or ASCII and a
+    return m & 0x80808080u;
 }
 
 // One 16-byte block at payload offset 16k.  A letter run is cut at every offset that is a
 // multiple of 8, i.e. at byte 0 of words 0 and 2 — so a block never needs its neighbour.
-// Bytes past the payload end must already be zero (zero is a separator: counts nothing).
+// Bytes past the payload end must already be zero (NUL is a separator: counts nothing).
 PK_HD void scan_block(const Words4& b, uint32_t one, uint32_t& tok128)
 {
-    const uint32_t l0 = letter_mask(b.w[0], one), l1 = letter_mask(b.w[1], one);
-    const uint32_t l2 = letter_mask(b.w[2], one), l3 = letter_mask(b.w[3], one);
-    tok128 = add_flag_bytes(token_flags(b.w[0], l0, l0 << 8, one), tok128);
-    tok128 = add_flag_bytes(token_flags(b.w[1], l1, shift_in_prev_byte(l0, l1), one), tok128);
-    tok128 = add_flag_bytes(token_flags(b.w[2], l2, l2 << 8, one), tok128);
-    tok128 = add_flag_bytes(token_flags(b.w[3], l3, shift_in_prev_byte(l2, l3), one), tok128);
+    const WordScan s0 = fold_word(b.w[0], one), s1 = fold_word(b.w[1], one);
+    const WordScan s2 = fold_word(b.w[2], one), s3 = fold_word(b.w[3], one);
+    tok128 = add_flag_bytes(token_flags(b.w[0], s0, s0.lm << 8, one), tok128);
+    tok128 = add_flag_bytes(token_flags(b.w[1], s1, shift_in_prev_byte(s0.lm, s1.lm), one), tok128);
+    tok128 = add_flag_bytes(token_flags(b.w[2], s2, s2.lm << 8, one), tok128);
+    tok128 = add_flag_bytes(token_flags(b.w[3], s3, shift_in_prev_byte(s2.lm, s3.lm), one), tok128);
 }
 
 // Zero the bytes of a block that lie at or past `valid` (0..16) bytes.
@@ -159,6 +197,28 @@ PK_HD uint64_t route_hash_final(uint64_t sum, uint32_t pay_len, uint32_t name_le
 }
 
 // ---- SPEC §A + §D: one request's decision from its scan results ---------------------
+// The routing table as the kernels see it: the caller's pk_table plus, per tool, the sum of
+// its name's hash terms, so that the switch compares 12 bytes (length + sum) per entry and
+// touches name bytes only to confirm a hit.
+struct alignas(16) DevTable {
+    pk_table t;
+    uint64_t tool_name_sum[PK_MAX_TOOLS];
+};
+
+PK_HD uint64_t name_sum(const uint8_t* name, uint32_t len)
+{
+    uint64_t s = 0;
+    for (uint32_t j = 0; j < len; ++j) s += name_term(j, name[j]);
+    return s;
+}
+
+static inline void make_dev_table(const pk_table& t, DevTable& d)
+{
+    d.t = t;
+    for (uint32_t k = 0; k < PK_MAX_TOOLS; ++k)
+        d.tool_name_sum[k] = k < t.n_tools ? name_sum(t.tools[k].name, t.tools[k].name_len) : 0;
+}
+
 // Sequential (one thread per request): name terms of the hash, the tool switch
 // (internal/service/mock.go:32-64: whole-name, case-sensitive byte equality, first match
 // wins, no match = the default branch — a class, not an error), final hash, provider.
@@ -168,29 +228,28 @@ PK_HD uint64_t route_hash_final(uint64_t sum, uint32_t pay_len, uint32_t name_le
 // tok <= max_tokens) pick with probability weight / total weight, deterministically from
 // the top 32 bits of the route hash: x = (hi32(hash) * W) >> 32, first provider whose
 // cumulative weight exceeds x.
-PK_HD void decide(const pk_table* __restrict__ tbl, const uint8_t* __restrict__ name,
+PK_HD void decide(const DevTable* __restrict__ tbl, const uint8_t* __restrict__ name,
                   uint32_t name_len, uint32_t pay_len, uint64_t payload_sum, uint32_t tok,
                   pk_decision* __restrict__ out)
 {
-    uint64_t sum = payload_sum;
-    for (uint32_t j = 0; j < name_len; ++j) sum += name_term(j, name[j]);
+    const uint64_t nsum = name_sum(name, name_len);
 
-    uint32_t cls = tbl->default_class;
+    uint32_t cls = tbl->t.default_class;
     uint32_t unknown = 1;
-    const uint32_t nt = tbl->n_tools;
+    const uint32_t nt = tbl->t.n_tools;
     for (uint32_t t = 0; t < nt; ++t) {
-        if (tbl->tools[t].name_len != name_len) continue;
-        uint32_t j = 0;
-        while (j < name_len && tbl->tools[t].name[j] == name[j]) ++j;
-        if (j == name_len) { cls = tbl->tools[t].class_id; unknown = 0; break; }
+        if (tbl->t.tools[t].name_len != name_len || tbl->tool_name_sum[t] != nsum) continue;
+        uint32_t j = 0;                              // confirm: the switch is exact byte equality
+        while (j < name_len && tbl->t.tools[t].name[j] == name[j]) ++j;
+        if (j == name_len) { cls = tbl->t.tools[t].class_id; unknown = 0; break; }
     }
 
-    const uint64_t h = route_hash_final(sum, pay_len, name_len);
+    const uint64_t h = route_hash_final(payload_sum + nsum, pay_len, name_len);
 
-    const uint32_t np = tbl->n_providers;
+    const uint32_t np = tbl->t.n_providers;
     uint32_t total = 0;
     for (uint32_t p = 0; p < np; ++p) {
-        const pk_provider& e = tbl->providers[p];
+        const pk_provider& e = tbl->t.providers[p];
         const bool elig = e.weight != 0u && ((e.tool_mask >> cls) & 1u) != 0u && tok <= e.max_tokens;
         total += elig ? e.weight : 0u;
     }
@@ -199,7 +258,7 @@ PK_HD void decide(const pk_table* __restrict__ tbl, const uint8_t* __restrict__ 
         const uint32_t x = (uint32_t)(((uint64_t)(uint32_t)(h >> 32) * (uint64_t)total) >> 32);
         uint32_t cum = 0;
         for (uint32_t p = 0; p < np; ++p) {
-            const pk_provider& e = tbl->providers[p];
+            const pk_provider& e = tbl->t.providers[p];
             const bool elig = e.weight != 0u && ((e.tool_mask >> cls) & 1u) != 0u && tok <= e.max_tokens;
             cum += elig ? e.weight : 0u;
             if (cum > x) { prov = p; break; }

@@ -60,19 +60,5 @@ def record_as_dict(r):
 
 def permute_batch(batch, perm):
     """Reorders the requests of a flat batch (payload starts stay 16-byte aligned)."""
-    n = len(perm)
-    pay_len = batch["pay_len"][perm]
-    pay_off = np.zeros(n + 1, dtype=np.uint64)
-    np.cumsum((pay_len.astype(np.uint64) + np.uint64(15)) & np.uint64(0xFFFFFFFFFFFFFFF0), out=pay_off[1:])
-    payload = np.full(max(int(pay_off[-1]), 16), 0x5A, dtype=np.uint8)[:int(pay_off[-1])]
-    nlen = (batch["name_off"][1:] - batch["name_off"][:-1])[perm]
-    name_off = np.zeros(n + 1, dtype=np.uint32)
-    np.cumsum(nlen, out=name_off[1:])
-    names = np.empty(int(name_off[-1]), dtype=np.uint8)
-    for j, i in enumerate(perm):
-        o, l = int(batch["pay_off"][i]), int(batch["pay_len"][i])
-        payload[int(pay_off[j]):int(pay_off[j]) + l] = batch["payload"][o:o + l]
-        a, b = int(batch["name_off"][i]), int(batch["name_off"][i + 1])
-        names[int(name_off[j]):int(name_off[j + 1])] = batch["names"][a:b]
-    return {"payload": payload, "pay_off": pay_off, "pay_len": pay_len.copy(), "names": names,
-            "name_off": name_off}
+    from polykey_service_b200.shard import select_requests
+    return select_requests(batch, perm)

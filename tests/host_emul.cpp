@@ -61,5 +61,7 @@ extern "C" void emul_route_one(const pk_table* t, const uint8_t* pay, uint32_t l
         sum += p.sum; tok += p.tok;
     }
     std::memset(d, 0, sizeof *d);
-    decide(t, name, nlen, len, sum, tok, d);
+    DevTable dt;
+    make_dev_table(*t, dt);
+    decide(&dt, name, nlen, len, sum, tok, d);
 }
