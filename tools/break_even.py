@@ -1,0 +1,92 @@
+#!/usr/bin/env python
+"""Batch-size sweep for the break-even statement `north_star` asks for.
+
+For n = 1 .. 65,536 requests of 2 KB it measures, on the same box and in the same run:
+  gpu_sync_us   median wall time of one pk_route_batch call (pinned host arena -> records on host)
+  gpu_pipe_us   per-batch time with 3 batches in flight (pk_submit / pk_wait)
+  cpu_b_us      the work-equivalent CPU port (oracle/pk_cpu_fast.c), all cores and 1 core
+  cpu_a_us      the reference-faithful CPU work (the tool switch only, mock.go:32-64), 1 core
+and prints one JSON object.  Test/measurement tooling: uses the oracle as the CPU arm only.
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import polykey_service_b200 as pk            # noqa: E402
+from oracle import pk_oracle as O            # noqa: E402
+
+
+def med(f, reps):
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        f()
+        ts.append(time.perf_counter() - t0)
+    ts.sort()
+    return ts[len(ts) // 2] * 1e6
+
+
+def main():
+    plen = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
+    sizes = [1, 4, 16, 64, 256, 1024, 4096, 16384, 65536]
+    cores = os.cpu_count() or 1
+    table = O.default_table()
+    cap = max(sizes) * ((plen + 15) & ~15)
+    r = pk.Router(device=0, max_requests=max(sizes), max_payload_bytes=cap, n_slots=3)
+    rows = []
+    bufs = [r.host_alloc(cap + 64) for _ in range(3)]
+    outs = [np.frombuffer(r.host_alloc(24 * max(sizes)), dtype=pk.DECISION_DTYPE) for _ in range(3)]
+    for n in sizes:
+        batches = [O.gen_batch(O.SEED_BASE + 9, n, plen, mode=0, first_id=j * n, payload_out=bufs[j]) for j in range(3)]
+        want = O.route_batch(table, batches[0], threads=min(cores, 8))[1]
+        got = r.route_batch(batches[0], out=outs[0][:n])
+        assert (got == want).all()
+        reps = 200 if n <= 4096 else 40
+        gpu_sync = med(lambda: r.route_batch(batches[0], out=outs[0][:n]), reps)
+
+        def pipe(k=reps):
+            infl = [False] * 3
+            for s in range(k):
+                d = s % 3
+                if infl[d]:
+                    r.wait(d)
+                r.submit(d, batches[d], outs[d][:n])
+                infl[d] = True
+            for d in range(3):
+                if infl[d]:
+                    r.wait(d)
+        pipe(6)
+        t0 = time.perf_counter()
+        pipe(reps)
+        gpu_pipe = (time.perf_counter() - t0) / reps * 1e6
+        cpu_b_all = med(lambda: O.route_batch(table, batches[0], threads=cores, fast=True), max(5, reps // 4))
+        cpu_b_1 = med(lambda: O.route_batch(table, batches[0], threads=1, fast=True), max(5, reps // 8))
+        cpu_a_1 = med(lambda: O.route_batch(table, batches[0], threads=1, switch_only=True), max(5, reps // 4))
+        rows.append({"n": n, "gpu_sync_us": gpu_sync, "gpu_pipe_us": gpu_pipe, "cpu_b_all_us": cpu_b_all,
+                     "cpu_b_1core_us": cpu_b_1, "cpu_a_1core_us": cpu_a_1})
+        print(rows[-1], file=sys.stderr, flush=True)
+    r.close()
+
+    def first(pred):
+        for row in rows:
+            if pred(row):
+                return row["n"]
+        return None
+    out = {"payload_bytes": plen, "cores": cores, "rows": rows,
+           "break_even_n": {
+               "gpu_sync_vs_cpu_b_1core": first(lambda x: x["gpu_sync_us"] < x["cpu_b_1core_us"]),
+               "gpu_sync_vs_cpu_b_all": first(lambda x: x["gpu_sync_us"] < x["cpu_b_all_us"]),
+               "gpu_pipe_vs_cpu_b_all": first(lambda x: x["gpu_pipe_us"] < x["cpu_b_all_us"]),
+               "gpu_pipe_vs_cpu_a_1core": first(lambda x: x["gpu_pipe_us"] < x["cpu_a_1core_us"])},
+           "note": "ctypes call overhead (~2-4 us) is inside every number; cpu_a is the tool switch only "
+                   "(what the Go reference does); None = the GPU never wins in this sweep"}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
