@@ -65,6 +65,7 @@ extern "C" {
 #define PK_MAX_NAME_LEN       0xFFFFFFu /* a request's tool name, bytes              */
 #define PK_PROVIDER_NONE      0xFFu
 #define PK_MAX_WEIGHT         (1u << 20) /* provider weight upper bound              */
+#define PK_NOALLOC_MAX_REQUESTS 65536u  /* batch limit of pk_route_device_noalloc    */
 
 /* decision flags */
                                        /* 0x0001u is reserved (always 0)            */
@@ -198,6 +199,51 @@ PK_API uint64_t pk_launch_count(const pk_handle* h);
  * here (SURVEY.md §7 "Pinned host memory from Go").                              */
 PK_API void* pk_host_alloc(pk_handle* h, size_t bytes);
 PK_API void  pk_host_free(pk_handle* h, void* p);
+
+/* pk_route_device_noalloc — routing for callers that cannot allocate GPU memory.
+ * (No counterpart in the reference: it has no device code at all.)
+ *
+ * Everything above runs on buffers pk_init() allocates.  That does not work for a host
+ * process whose GPU memory already belongs to something else (an inference engine that
+ * reserved all of HBM at start-up, a fixed-budget pool), nor on a thread that must never
+ * hit the device-wide synchronisation cudaMalloc / cudaFree imply.  This entry point makes
+ * no allocation of any kind, on the device or on the host, and needs no handle: the caller
+ * passes DEVICE pointers to a batch it has already placed in its own memory and to the
+ * record array to fill; the only other device memory the kernel needs — one 32-byte scratch
+ * entry per request, used by requests longer than 16 KiB, and the routing table — lives in
+ * static storage inside the library: PK_NOALLOC_MAX_REQUESTS * 32 bytes = 2 MiB per GPU
+ * that loads the library, held until the process exits.
+ *
+ *   table            HOST pointer; copied into the library's static device copy each call
+ *   d_payload .. d_name_off   DEVICE pointers, same layout and alignment rules as
+ *                    pk_route_batch (pay_off[i] % 16 == 0, offsets relative to d_payload /
+ *                    d_names); d_payload must be 16-byte aligned and readable up to the
+ *                    end of the last request's final 16-byte block
+ *   d_extra, n_extra DEVICE array of n_extra (request, segment) uint32 pairs: one pair for
+ *                    every segment s >= 1 of every request longer than 16384 bytes
+ *                    (segment s covers bytes [16384*s, 16384*(s+1)) ); NULL / 0 if no request
+ *                    is that long.  The list must match d_pay_len exactly — it is not
+ *                    checked, the lengths being on the device.
+ *   n                requests; more than PK_NOALLOC_MAX_REQUESTS is refused with
+ *                    PK_ERR_CAPACITY (the static scratch has no room for them)
+ *   max_payload_len  an upper bound of the payload lengths (0xFFFFFFFF if unknown)
+ *   d_out            DEVICE pointer to n records
+ *   stream           cudaStream_t (as void*) of the CURRENT device; the work is enqueued
+ *                    there and the call returns without waiting — synchronise the stream
+ *                    before reading d_out
+ *
+ * The first call on each device resolves the static storage's device address
+ * (cudaGetSymbolAddress); make that first call outside any stream capture.
+ * All calls share the one static scratch array and table copy: two calls whose GPU work
+ * can overlap (different streams, different threads) race on them — serialise them on one
+ * stream.  The part of the scratch a call can touch is cleared by that call before its
+ * kernel runs, so a call is not affected by what earlier calls left behind.             */
+PK_API int pk_route_device_noalloc(const pk_table* table,
+                                   const uint8_t* d_payload, const uint64_t* d_pay_off,
+                                   const uint32_t* d_pay_len, const uint8_t* d_names,
+                                   const uint32_t* d_name_off, const uint32_t* d_extra,
+                                   uint32_t n_extra, uint32_t n, uint32_t max_payload_len,
+                                   pk_decision* d_out, void* stream);
 
 PK_API const char* pk_strerror(int status);
 PK_API int         pk_last_cuda_error(const pk_handle* h);   /* cudaError_t of last failure */

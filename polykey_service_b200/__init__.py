@@ -99,6 +99,7 @@ def lib() -> C.CDLL:
         L.pk_host_alloc.argtypes, L.pk_host_alloc.restype = [vp, C.c_size_t], vp
         L.pk_host_free.argtypes, L.pk_host_free.restype = [vp, vp], None
         L.pk_last_cuda_error.argtypes = [vp]
+        L.pk_route_device_noalloc.argtypes = [C.POINTER(PkTable), vp, vp, vp, vp, vp, vp, u32, u32, u32, vp, vp]
         _lib = L
     return _lib
 

@@ -14,7 +14,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpkroute.so")
-SOURCES = ["pk_kernels.cu", "pk_abi.cu"]
+SOURCES = ["pk_kernels.cu", "pk_abi.cu", "pk_noalloc.cu"]
 HEADERS = ["pk_kernels.cuh", "pk_spec.cuh", os.path.join("..", "..", "include", "pk_route.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-shared"]
