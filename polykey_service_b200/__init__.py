@@ -18,7 +18,8 @@ import numpy as np
 __all__ = ["Router", "PkError", "PkTable", "PkTool", "PkProvider", "DECISION_DTYPE", "default_table",
            "make_table", "pack_requests", "round16", "lib", "LIB_PATH", "STATUS", "FLAG_NO_PROVIDER", "FLAG_EMPTY_PAYLOAD", "FLAG_UNKNOWN_TOOL", "PROVIDER_NONE"]
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libpkroute.so")
+# POLYKEY_PKROUTE_LIB: developer aid — load a tuning variant built with build.build(defines=..., out=...)
+LIB_PATH = os.environ.get("POLYKEY_PKROUTE_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libpkroute.so")
 
 PK_MAX_TOOLS, PK_MAX_TOOL_NAME, PK_MAX_PROVIDERS = 16, 64, 32
 FLAG_NO_PROVIDER, FLAG_EMPTY_PAYLOAD, FLAG_UNKNOWN_TOOL = 2, 4, 8

@@ -35,14 +35,16 @@ def stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not stale():
+def build(force: bool = False, verbose: bool = False, defines=(), out: str | None = None) -> str:
+    """defines/out: build a tuning variant (e.g. defines=["PK_PIPE=0"]) to another path."""
+    if out is None and not force and not stale():
         return LIB
-    cmd = [nvcc(), *NVCC_FLAGS, "-o", LIB] + [os.path.join(CSRC, f) for f in SOURCES]
+    out = out or LIB
+    cmd = [nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-o", out] + [os.path.join(CSRC, f) for f in SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     subprocess.check_call(cmd)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":

@@ -29,12 +29,26 @@
 #include "pk_kernels.cuh"
 #include "pk_spec.cuh"
 
+// Build-time tuning knobs (python -m polykey_service_b200.build passes the chosen values).
+#ifndef PK_PIPE
+#define PK_PIPE 0        // 1: the main loop keeps a second group of loads in flight (register double buffer)
+#endif
+#ifndef PK_MIN_CTAS
+#define PK_MIN_CTAS 5    // __launch_bounds__ minimum resident CTAs per SM, full-warp kernels (G == 32)
+#endif
+#ifndef PK_MIN_CTAS_TINY
+#define PK_MIN_CTAS_TINY 8   // ... lane-group kernels (G < 32): latency-bound, more resident warps win
+#endif
+#ifndef PK_UNROLL
+#define PK_UNROLL 4      // 128-bit loads in flight per lane
+#endif
+
 namespace pk {
 namespace {
 
 constexpr int      kWarpsPerCta = 8;
 constexpr int      kThreads     = kWarpsPerCta * 32;
-constexpr int      kUnroll      = 4;          // 128-bit loads in flight per lane
+constexpr int      kUnroll      = PK_UNROLL;  // 128-bit loads in flight per lane
 constexpr unsigned kFull        = 0xFFFFFFFFu;
 constexpr int      kPartialSlots = 32 * 65;   // >= G * (R + 1) for every (G, R) launch_route picks
 constexpr uint32_t kNameStage   = 4096;       // bytes of tool names a CTA stages in shared memory
@@ -72,18 +86,42 @@ __device__ __forceinline__ void scan_segment(const uint8_t* __restrict__ pay, ui
     uint32_t tok128 = 0;
     uint32_t b0 = 0;
 
-    // main loop: four whole warp-steps (2 KiB) per iteration, no predicates
-    for (; b0 + 32u * kUnroll <= nwhole; b0 += 32u * kUnroll) {
-        uint4 x[kUnroll];
+    // main loop: groups of four whole warp-steps (2 KiB), no predicates
+    const uint32_t ngroups = nwhole / (32u * kUnroll);
+    auto load_group = [&](uint4 (&x)[kUnroll], uint32_t g) {
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) x[u] = ldg_stream(base + b0 + u * 32);
+        for (int u = 0; u < kUnroll; ++u) x[u] = ldg_stream(base + g * (32u * kUnroll) + u * 32);
+    };
+    auto consume_group = [&](const uint4 (&x)[kUnroll]) {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
             const Words4 w = {{x[u].x, x[u].y, x[u].z, x[u].w}};
             stripe_round(st, w);
             scan_block(w, one, tok128);
         }
+    };
+#if PK_PIPE
+    {   // register double buffer: the next group's loads are issued before this group is consumed
+        uint4 xa[kUnroll], xb[kUnroll];
+        uint32_t g = 0;
+        if (ngroups > 0) load_group(xa, 0);
+        while (g < ngroups) {
+            if (g + 1 < ngroups) load_group(xb, g + 1);
+            consume_group(xa);
+            if (++g >= ngroups) break;
+            if (g + 1 < ngroups) load_group(xa, g + 1);
+            consume_group(xb);
+            ++g;
+        }
     }
+#else
+    for (uint32_t g = 0; g < ngroups; ++g) {
+        uint4 x[kUnroll];
+        load_group(x, g);
+        consume_group(x);
+    }
+#endif
+    b0 = ngroups * (32u * kUnroll);
     // remainder: ragged steps, the payload's last (partial) block
     for (; b0 < nb; b0 += 32u * kUnroll) {
         uint4 x[kUnroll];
@@ -130,6 +168,81 @@ __device__ __forceinline__ void scan_tiny(uint4 x, uint32_t len, uint32_t lig, u
     tok = tok128 >> 7;
 }
 
+// One copy of the sequential decision code per kernel (it is long; inlining it at every call
+// site only bloats the instruction cache footprint).
+__device__ __noinline__ void decide_call(const DevTable* tbl, const uint8_t* name, uint32_t name_len,
+                                         uint32_t pay_len, uint64_t payload_sum, uint32_t tok,
+                                         pk_decision* out)
+{
+    decide(tbl, name, name_len, pay_len, payload_sum, tok, out);
+}
+
+// Latency mode (small batches): the warp that scanned a request finalises it on the spot,
+// lane-parallel — name bytes one per lane, the tool switch as a warp vote, the provider rule as
+// a warp prefix sum — with no shared memory and no CTA barrier on the path.  Same results as
+// decide(): the hash sum is commutative, so name terms can join the lanes' digests before the
+// reduction, and the first lane whose running weight exceeds x is the first such provider.
+__device__ __forceinline__ void finalize_warp(const RouteParams& P, uint32_t req, uint32_t len,
+                                              uint64_t digest, uint32_t tok_lane, uint32_t lane)
+{
+    const DevTable* __restrict__ tbl = P.table;
+    const uint32_t noff = __ldg(P.name_off + req);
+    const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
+    const uint8_t* __restrict__ nm = P.names + noff;
+
+    uint32_t c0 = 0, c1 = 0;                      // this lane's name bytes lane and lane+32
+    for (uint32_t j = lane; j < nlen; j += 32) {
+        const uint32_t b = __ldg(nm + j);
+        digest += name_term(j, b);
+        if (j < 32) c0 = b; else if (j < 64) c1 = b;
+    }
+    // tool switch (mock.go:32-64): whole-name byte equality, first match wins
+    uint32_t cls = __ldg(&tbl->t.default_class);
+    uint32_t unknown = 1;
+    const uint32_t nt = __ldg(&tbl->t.n_tools);
+    for (uint32_t t = 0; t < nt; ++t) {
+        const uint32_t tl = __ldg(&tbl->t.tools[t].name_len);
+        if (tl != nlen) continue;                                     // warp-uniform
+        bool ok = true;
+        if (lane < tl)       ok = (__ldg(&tbl->t.tools[t].name[lane]) == c0);
+        if (lane + 32u < tl) ok = ok && (__ldg(&tbl->t.tools[t].name[lane + 32u]) == c1);
+        if (__all_sync(kFull, ok)) { cls = __ldg(&tbl->t.tools[t].class_id); unknown = 0; break; }
+    }
+    const uint64_t total = warp_sum64(digest);
+    const uint32_t tok = __reduce_add_sync(kFull, tok_lane);
+    const uint64_t h = route_hash_final(total, len, nlen);
+
+    // provider: lane p holds provider p's eligible weight; inclusive prefix sum over the warp
+    const uint32_t np = __ldg(&tbl->t.n_providers);
+    uint32_t cum = 0;
+    if (lane < np) {
+        const uint4 row = __ldg(reinterpret_cast<const uint4*>(&tbl->t.providers[lane]));
+        const bool elig = row.y != 0u && ((row.z >> cls) & 1u) != 0u && tok <= row.x;
+        cum = elig ? row.y : 0u;
+    }
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t up = __shfl_up_sync(kFull, cum, d);
+        if (lane >= (uint32_t)d) cum += up;
+    }
+    const uint32_t wtotal = __shfl_sync(kFull, cum, 31);
+    uint32_t prov = PK_PROVIDER_NONE;
+    if (wtotal != 0u) {
+        const uint32_t x = __umulhi((uint32_t)(h >> 32), wtotal);
+        prov = (uint32_t)__ffs((int)__ballot_sync(kFull, cum > x)) - 1u;
+    }
+    const uint32_t flags = (prov == PK_PROVIDER_NONE ? PK_FLAG_NO_PROVIDER : 0u) |
+                           (len == 0u ? PK_FLAG_EMPTY_PAYLOAD : 0u) | (unknown ? PK_FLAG_UNKNOWN_TOOL : 0u);
+    if (lane < 3) {                                // the 24-byte record: one coalesced store
+        uint64_t word;
+        if (lane == 0)      word = (uint64_t)len | ((uint64_t)tok << 32);
+        else if (lane == 1) word = h;
+        else                word = (uint64_t)(cls & 0xFFu) | ((uint64_t)(prov & 0xFFu) << 8) |
+                                   ((uint64_t)flags << 16) | (200ull << 32);   // Status.Code 200, mock.go:26
+        reinterpret_cast<uint64_t*>(P.out)[(size_t)req * 3 + lane] = word;
+    }
+}
+
 // Fold one segment of a long request into its scratch entry; the warp that arrives last reads
 // the totals (resetting the entry to zero for the next launch) and lane 0 finalises.
 __device__ __forceinline__ void fold_long_segment(const RouteParams& P, uint32_t req, uint32_t len,
@@ -149,12 +262,13 @@ __device__ __forceinline__ void fold_long_segment(const RouteParams& P, uint32_t
     const uint32_t ttok  = atomicExch(&s->tok, 0u);
     atomicExch(&s->arrived, 0u);
     const uint32_t noff = P.name_off[req];
-    decide(P.table, P.names + noff, P.name_off[req + 1] - noff, len, total, ttok, P.out + req);
+    decide_call(P.table, P.names + noff, P.name_off[req + 1] - noff, len, total, ttok, P.out + req);
 }
 
-template <int G>
-__global__ void __launch_bounds__(kThreads, 4) route_kernel(const RouteParams P)
+template <int G, bool kWarpFinal>
+__global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : PK_MIN_CTAS_TINY) route_kernel(const RouteParams P)
 {
+    static_assert(!kWarpFinal || G == 32, "latency mode finalises with the full warp");
     __shared__ uint64_t psum[kPartialSlots];     // [k][R+1]: lane-in-group k's digest for request i
     __shared__ uint32_t ptok[kPartialSlots];
     __shared__ DevTable s_tbl;                   // the routing table, staged once per CTA
@@ -180,20 +294,49 @@ __global__ void __launch_bounds__(kThreads, 4) route_kernel(const RouteParams P)
 
     const uint32_t base_req = blockIdx.x * R;
     const uint32_t r_here   = min(R, P.n - base_req);
+
+    if (kWarpFinal) {
+        // ---- latency mode: scan and finalise per warp; nothing shared, no barrier ----
+        for (uint32_t i = wid; i < r_here; i += kWarpsPerCta) {
+            const uint32_t req = base_req + i;
+            const uint32_t len = __ldg(P.pay_len + req);
+            uint64_t digest;
+            uint32_t tok;
+            scan_segment(P.payload + __ldg(P.pay_off + req), len, 0u, lane, P.one, digest, tok);
+            if (len > kSegBytes) fold_long_segment(P, req, len, digest, tok, lane);
+            else                 finalize_warp(P, req, len, digest, tok, lane);
+        }
+        return;
+    }
+
     const uint32_t ld       = R + 1u;            // odd leading dimension: conflict-free columns
     constexpr uint32_t kGroups = 32u / G;
     const uint32_t grp = lane / G, lig = lane % G;
 
-    // ---- stage what phase 2 reads, so that its dependent loads hit shared memory; these
-    //      global loads are in flight while phase 1 runs ----
+    // ---- prologue.  Phase 2 reads the table and the tool names; they are staged in shared
+    //      memory so that its dependent loads are LDS.  Order matters for latency: all
+    //      independent metadata loads are issued first; then (G == 32) each warp pulls the head
+    //      of its first payload towards L2, so that HBM fetch runs while the name bytes — which
+    //      need name_off first — are staged; only then does the scan start. ----
     static_assert(sizeof(DevTable) % 16 == 0, "DevTable is copied as uint4");
-    if (threadIdx.x < sizeof(DevTable) / 16)
-        reinterpret_cast<uint4*>(&s_tbl)[threadIdx.x] = __ldg(reinterpret_cast<const uint4*>(P.table) + threadIdx.x);
     const uint32_t names_lo = __ldg(P.name_off + base_req);
     const uint32_t names_sz = __ldg(P.name_off + base_req + r_here) - names_lo;
-    const bool names_staged = names_sz <= kNameStage;
-    if (names_staged)
-        for (uint32_t j = threadIdx.x; j < names_sz; j += kThreads) s_names[j] = __ldg(P.names + names_lo + j);
+    uint4 tbl_part = make_uint4(0u, 0u, 0u, 0u);
+    if (threadIdx.x < sizeof(DevTable) / 16)
+        tbl_part = __ldg(reinterpret_cast<const uint4*>(P.table) + threadIdx.x);
+    bool names_staged = false;
+    if (G == 32) {
+        if (wid < r_here) {
+            const uint32_t len0 = __ldg(P.pay_len + base_req + wid);
+            const uint8_t* pay0 = P.payload + __ldg(P.pay_off + base_req + wid);
+            if (lane < 16u && lane * 128u < len0)
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(pay0 + lane * 128u));
+        }
+        names_staged = names_sz <= kNameStage;
+        if (names_staged)
+            for (uint32_t j = threadIdx.x; j < names_sz; j += kThreads) s_names[j] = __ldg(P.names + names_lo + j);
+    }
+    if (threadIdx.x < sizeof(DevTable) / 16) reinterpret_cast<uint4*>(&s_tbl)[threadIdx.x] = tbl_part;
 
     // ---- phase 1: scan (first segment of) each request ----
     if (G == 32) {
@@ -259,7 +402,7 @@ __global__ void __launch_bounds__(kThreads, 4) route_kernel(const RouteParams P)
         const uint32_t noff = __ldg(P.name_off + req);
         const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
         const uint8_t* name = names_staged ? s_names + (noff - names_lo) : P.names + noff;
-        decide(&s_tbl, name, nlen, len, sum, tok, P.out + req);
+        decide_call(&s_tbl, name, nlen, len, sum, tok, P.out + req);
     }
 }
 
@@ -288,10 +431,17 @@ cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStrea
     p.reqs_per_cta = R;
     p.one = 1u;
     const uint32_t ctas = (p.n + R - 1u) / R + (p.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
+    // latency mode while one request per warp already fills the machine's resident CTA slots
+    static const char* const m_env = std::getenv("PK_LATENCY_MODE");     // tuning aid: 0 / 1 forces
+    bool warp_final = G == 32 && R == r_min;
+    if (m_env && G == 32) warp_final = std::atoi(m_env) != 0;
     switch (G) {
-    case 8:  route_kernel<8><<<ctas, kThreads, 0, stream>>>(p); break;
-    case 16: route_kernel<16><<<ctas, kThreads, 0, stream>>>(p); break;
-    default: route_kernel<32><<<ctas, kThreads, 0, stream>>>(p); break;
+    case 8:  route_kernel<8, false><<<ctas, kThreads, 0, stream>>>(p); break;
+    case 16: route_kernel<16, false><<<ctas, kThreads, 0, stream>>>(p); break;
+    default:
+        if (warp_final) route_kernel<32, true><<<ctas, kThreads, 0, stream>>>(p);
+        else            route_kernel<32, false><<<ctas, kThreads, 0, stream>>>(p);
+        break;
     }
     return cudaGetLastError();
 }

@@ -212,11 +212,28 @@ PK_HD uint64_t name_sum(const uint8_t* name, uint32_t len)
     return s;
 }
 
+// Host side: the device copy is normalised — name bytes past name_len, tool rows past n_tools
+// and provider rows past n_providers are zero — so that decide() may compare names as words
+// and read whole groups of provider rows.
 static inline void make_dev_table(const pk_table& t, DevTable& d)
 {
-    d.t = t;
-    for (uint32_t k = 0; k < PK_MAX_TOOLS; ++k)
-        d.tool_name_sum[k] = k < t.n_tools ? name_sum(t.tools[k].name, t.tools[k].name_len) : 0;
+    d = DevTable{};
+    d.t.n_tools = t.n_tools;
+    d.t.default_class = t.default_class;
+    d.t.n_providers = t.n_providers;
+    for (uint32_t k = 0; k < t.n_tools && k < PK_MAX_TOOLS; ++k) {
+        const uint32_t len = t.tools[k].name_len <= PK_MAX_TOOL_NAME ? t.tools[k].name_len : PK_MAX_TOOL_NAME;
+        for (uint32_t j = 0; j < len; ++j) d.t.tools[k].name[j] = t.tools[k].name[j];
+        d.t.tools[k].name_len = t.tools[k].name_len;
+        d.t.tools[k].class_id = t.tools[k].class_id;
+        d.tool_name_sum[k] = name_sum(d.t.tools[k].name, len);
+    }
+    for (uint32_t p = 0; p < t.n_providers && p < PK_MAX_PROVIDERS; ++p) d.t.providers[p] = t.providers[p];
+}
+
+PK_HD bool provider_eligible(const pk_provider& e, uint32_t cls, uint32_t tok)
+{
+    return e.weight != 0u && ((e.tool_mask >> cls) & 1u) != 0u && tok <= e.max_tokens;
 }
 
 // Sequential (one thread per request): name terms of the hash, the tool switch
@@ -228,40 +245,65 @@ static inline void make_dev_table(const pk_table& t, DevTable& d)
 // tok <= max_tokens) pick with probability weight / total weight, deterministically from
 // the top 32 bits of the route hash: x = (hi32(hash) * W) >> 32, first provider whose
 // cumulative weight exceeds x.
+//
+// Written for latency, since one thread walks it alone: the first 16 name bytes are read once,
+// in one batch of independent loads, and kept packed in four registers — they feed the hash
+// terms and the comparison against the table (whose names are word-aligned) four bytes at a
+// time; longer names fall back to byte loops for the remainder.  The provider loops are
+// unrolled by four so that their table loads are in flight together.
 PK_HD void decide(const DevTable* __restrict__ tbl, const uint8_t* __restrict__ name,
                   uint32_t name_len, uint32_t pay_len, uint64_t payload_sum, uint32_t tok,
                   pk_decision* __restrict__ out)
 {
-    const uint64_t nsum = name_sum(name, name_len);
+    uint32_t nw[4] = {0u, 0u, 0u, 0u};               // name bytes 0..15, little endian, zero padded
+    uint64_t nsum = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < 16; ++j) {
+        if (j < name_len) {
+            const uint32_t b = name[j];
+            nw[j >> 2] |= b << (8u * (j & 3u));
+            nsum += name_term(j, b);
+        }
+    }
+    for (uint32_t j = 16; j < name_len; ++j) nsum += name_term(j, name[j]);
 
     uint32_t cls = tbl->t.default_class;
     uint32_t unknown = 1;
     const uint32_t nt = tbl->t.n_tools;
     for (uint32_t t = 0; t < nt; ++t) {
-        if (tbl->t.tools[t].name_len != name_len || tbl->tool_name_sum[t] != nsum) continue;
-        uint32_t j = 0;                              // confirm: the switch is exact byte equality
-        while (j < name_len && tbl->t.tools[t].name[j] == name[j]) ++j;
-        if (j == name_len) { cls = tbl->t.tools[t].class_id; unknown = 0; break; }
+        const pk_tool& e = tbl->t.tools[t];
+        if (e.name_len != name_len || tbl->tool_name_sum[t] != nsum) continue;
+        // confirm: the switch is exact byte equality.  pk_tool::name is 4-byte aligned and zero
+        // padded past name_len (pk_init / pk_update_table check that), so the head compares as words.
+        const uint32_t* tw = reinterpret_cast<const uint32_t*>(e.name);
+        bool same = (tw[0] == nw[0]) & (tw[1] == nw[1]) & (tw[2] == nw[2]) & (tw[3] == nw[3]);
+        for (uint32_t j = 16; same && j < name_len; ++j) same = e.name[j] == name[j];
+        if (same) { cls = e.class_id; unknown = 0; break; }
     }
 
     const uint64_t h = route_hash_final(payload_sum + nsum, pay_len, name_len);
 
     const uint32_t np = tbl->t.n_providers;
     uint32_t total = 0;
-    for (uint32_t p = 0; p < np; ++p) {
-        const pk_provider& e = tbl->t.providers[p];
-        const bool elig = e.weight != 0u && ((e.tool_mask >> cls) & 1u) != 0u && tok <= e.max_tokens;
-        total += elig ? e.weight : 0u;
+    for (uint32_t p0 = 0; p0 < np; p0 += 4) {
+#pragma unroll
+        for (uint32_t u = 0; u < 4; ++u) {
+            // rows past n_providers are zero (weight 0 = not eligible): safe to read, add nothing
+            const pk_provider& e = tbl->t.providers[(p0 + u) & (PK_MAX_PROVIDERS - 1u)];
+            total += (p0 + u < np && provider_eligible(e, cls, tok)) ? e.weight : 0u;
+        }
     }
     uint32_t prov = PK_PROVIDER_NONE;
     if (total != 0u) {
         const uint32_t x = (uint32_t)(((uint64_t)(uint32_t)(h >> 32) * (uint64_t)total) >> 32);
         uint32_t cum = 0;
-        for (uint32_t p = 0; p < np; ++p) {
-            const pk_provider& e = tbl->t.providers[p];
-            const bool elig = e.weight != 0u && ((e.tool_mask >> cls) & 1u) != 0u && tok <= e.max_tokens;
-            cum += elig ? e.weight : 0u;
-            if (cum > x) { prov = p; break; }
+        for (uint32_t p0 = 0; p0 < np && prov == PK_PROVIDER_NONE; p0 += 4) {
+#pragma unroll
+            for (uint32_t u = 0; u < 4; ++u) {
+                const pk_provider& e = tbl->t.providers[(p0 + u) & (PK_MAX_PROVIDERS - 1u)];
+                cum += (p0 + u < np && provider_eligible(e, cls, tok)) ? e.weight : 0u;
+                if (cum > x && prov == PK_PROVIDER_NONE) prov = p0 + u;
+            }
         }
     }
 

@@ -69,6 +69,13 @@ def test_seeded_batches(router, oracle, mode, shape):
     check(router, oracle, b, f"mode {mode} shape {shape}")
 
 
+def test_large_ragged_batch_throughput_mode(router, oracle):
+    """Enough requests that a CTA owns 32+ of them: the thread-per-request decision phase
+    (smaller batches take the per-warp latency mode)."""
+    b = oracle.gen_batch(78, 24000, 0, 1500, mode=-1)
+    check(router, oracle, b, "24000 ragged requests")
+
+
 def test_ragged_mixed_stream(router, oracle):
     b = oracle.gen_batch(77, 5000, 0, 9000, mode=-1)
     check(router, oracle, b, "mixed modes, ragged")
