@@ -175,9 +175,11 @@ PK_API int  pk_wait(pk_handle* h, uint32_t slot);
  * pk_launch runs the kernels over the staged batch (no copies, asynchronous on the
  * slot's stream); pk_launch_many issues `count` launches back to back, launch k
  * using slot slots[k % n_slots_in_list], all on ONE stream (slot slots[0]'s), either
- * as `count` plain launches or (use_graph != 0) as one CUDA graph of `count` kernel
- * nodes; it brackets them with CUDA events on that stream, waits, and reports the
- * device time in *elapsed_ms; pk_fetch copies the slot's records out (synchronous). */
+ * as `count` plain launches or (use_graph == 1) as one CUDA graph of `count` kernel
+ * nodes in a chain, or (use_graph = k >= 2) as a graph of k parallel chains, launch j in
+ * chain j % k, so that independent batches may overlap on the GPU; it brackets them with
+ * CUDA events on that stream, waits, and reports the device time in *elapsed_ms;
+ * pk_fetch copies the slot's records out (synchronous).                               */
 PK_API int  pk_stage(pk_handle* h, uint32_t slot,
               const uint8_t* payload, const uint64_t* pay_off, const uint32_t* pay_len,
               const uint8_t* names, const uint32_t* name_off, uint32_t n);

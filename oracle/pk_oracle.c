@@ -295,6 +295,11 @@ int pk_ref_route_batch_mt(const pk_table* t, const uint8_t* payload, const uint6
     if (nthreads < 1) nthreads = 1;
     if (nthreads > 1024) nthreads = 1024;
     if (nthreads > n) nthreads = n;
+    if (nthreads == 1) {                       /* no thread spawn for the single-core arm */
+        mt_job one = {t, payload, pay_off, pay_len, names, name_off, out, 0, n, switch_only};
+        mt_worker(&one);
+        return PK_OK;
+    }
     pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * nthreads);
     mt_job* jobs = (mt_job*)malloc(sizeof(mt_job) * nthreads);
     if (!th || !jobs) { free(th); free(jobs); return PK_ERR_ARG; }

@@ -227,7 +227,8 @@ class Router:
     def launch(self, slot: int):
         self._check(self._L.pk_launch(self._h, slot), "pk_launch")
 
-    def launch_many(self, slots, count: int, use_graph: bool = False) -> float:
+    def launch_many(self, slots, count: int, use_graph=False) -> float:
+        """use_graph: False = plain launches, True / 1 = one graph (a chain), k >= 2 = a graph of k parallel chains."""
         arr = np.asarray(slots, dtype=np.uint32)
         ms = C.c_float(0)
         self._check(self._L.pk_launch_many(self._h, arr.ctypes.data, arr.size, count, int(use_graph),

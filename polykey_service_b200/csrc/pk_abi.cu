@@ -432,8 +432,27 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
         cudaGraphExec_t exec = nullptr;
         PK_CUDA(h, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
         int rc = PK_OK;
-        for (uint32_t k = 0; k < count && rc == PK_OK; ++k)
-            rc = launch_slot(h, h->slots[slots[k % n_list]], st);
+        const uint32_t width = use_graph >= 2 ? (uint32_t)use_graph : 1u;
+        if (width == 1 || n_list < width) {
+            for (uint32_t k = 0; k < count && rc == PK_OK; ++k)
+                rc = launch_slot(h, h->slots[slots[k % n_list]], st);
+        } else {
+            // fork: chain b runs on the stream of listed slot b (b >= 1) or on st (b == 0)
+            cudaError_t fe = cudaEventRecord(h->ev0, st);
+            for (uint32_t b = 1; b < width && fe == cudaSuccess; ++b)
+                fe = cudaStreamWaitEvent(h->slots[slots[b]].stream, h->ev0, 0);
+            if (fe != cudaSuccess) rc = PK_ERR_CUDA;
+            for (uint32_t k = 0; k < count && rc == PK_OK; ++k) {
+                const uint32_t b = k % width;
+                rc = launch_slot(h, h->slots[slots[k % n_list]], b == 0 ? st : h->slots[slots[b]].stream);
+            }
+            // join
+            for (uint32_t b = 1; b < width && rc == PK_OK; ++b) {
+                Slot& sb = h->slots[slots[b]];
+                if (cudaEventRecord(sb.done, sb.stream) != cudaSuccess ||
+                    cudaStreamWaitEvent(st, sb.done, 0) != cudaSuccess) rc = PK_ERR_CUDA;
+            }
+        }
         cudaError_t ce = cudaStreamEndCapture(st, &graph);
         if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
         PK_CUDA(h, ce);

@@ -205,7 +205,8 @@ def test_async_slots_and_resident_form(pk, router, oracle):
     before = router.launch_count
     ms = router.launch_many([0, 1, 2], 9, use_graph=False)
     ms_g = router.launch_many([0, 1, 2], 9, use_graph=True)
-    assert ms > 0 and ms_g > 0 and router.launch_count == before + 18
+    ms_p = router.launch_many([0, 1, 2], 9, use_graph=3)                      # three parallel chains
+    assert ms > 0 and ms_g > 0 and ms_p > 0 and router.launch_count == before + 27
     for s in range(3):
         assert_records_equal(router.fetch(s, 3000),
                              oracle.route_batch(t, batches[(s + 1) % 3], threads=8)[1], f"resident {s}")
