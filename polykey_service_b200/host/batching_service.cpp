@@ -1,6 +1,7 @@
 // batching_service.cpp — see batching_service.hpp.
 #include "batching_service.hpp"
 
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 
@@ -89,7 +90,7 @@ BatchingStats BatchingService::stats() const
     for (const auto& s : shards_) {
         std::lock_guard<std::mutex> g(s->mu);
         t.requests += s->st.requests; t.batches += s->st.batches; t.flush_full += s->st.flush_full;
-        t.flush_deadline += s->st.flush_deadline; t.errors += s->st.errors;
+        t.flush_deadline += s->st.flush_deadline; t.flush_idle += s->st.flush_idle; t.errors += s->st.errors;
         if (s->st.max_batch_seen > t.max_batch_seen) t.max_batch_seen = s->st.max_batch_seen;
     }
     return t;
@@ -118,8 +119,8 @@ Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, c
     }
     s->cv.notify_one();
     {
-        std::unique_lock<std::mutex> w(p.mu);               // block this RPC's thread only
-        p.cv.wait(w, [&] { return p.done; });
+        std::unique_lock<std::mutex> w(s->done_mu);         // block this RPC's thread only
+        s->done_cv.wait(w, [&] { return p.done; });
     }
 
     if (p.rc != 0) {
@@ -139,14 +140,16 @@ void BatchingService::complete(Shard* s, Arena& a, int rc)
         std::lock_guard<std::mutex> g(s->mu);
         ++s->st.errors;
     }
-    for (size_t i = 0; i < a.reqs.size(); ++i) {
-        Pending* p = a.reqs[i];
-        std::lock_guard<std::mutex> w(p->mu);
-        p->rc = rc;
-        if (rc == 0) p->decision = a.out[i];
-        p->done = true;
-        p->cv.notify_one();
+    {
+        std::lock_guard<std::mutex> w(s->done_mu);
+        for (size_t i = 0; i < a.reqs.size(); ++i) {
+            Pending* p = a.reqs[i];
+            p->rc = rc;
+            if (rc == 0) p->decision = a.out[i];
+            p->done = true;
+        }
     }
+    s->done_cv.notify_all();
     a.reqs.clear();
     a.inflight = false;
 }
@@ -179,10 +182,17 @@ void BatchingService::flusher(Shard* s)
         }
         // a batch is open: wait for it to fill or for the deadline of its first request
         const auto deadline = Clock::now() + std::chrono::microseconds(cfg_.max_wait_us);
-        bool full = s->q.size() >= cfg_.max_batch;
+        const auto idle = std::chrono::microseconds(cfg_.idle_flush_us ? cfg_.idle_flush_us : cfg_.max_wait_us);
+        bool full = s->q.size() >= cfg_.max_batch, went_idle = false;
         while (!full && !stopping_.load()) {
-            if (s->cv.wait_until(lk, deadline) == std::cv_status::timeout) break;
+            const size_t before = s->q.size();
+            const auto until = std::min(deadline, Clock::now() + idle);
+            s->cv.wait_until(lk, until);
             full = s->q.size() >= cfg_.max_batch;
+            if (full) break;
+            const auto now = Clock::now();
+            if (now >= deadline) break;
+            if (s->q.size() == before && now >= until) { went_idle = true; break; }   // nothing new arrived
         }
         if (free_slots.empty()) {                           // free the slot we are about to reuse
             lk.unlock();
@@ -207,7 +217,7 @@ void BatchingService::flusher(Shard* s)
         }
         ++s->st.batches;
         s->st.requests += n;
-        if (full) ++s->st.flush_full; else ++s->st.flush_deadline;
+        if (full) ++s->st.flush_full; else if (went_idle) ++s->st.flush_idle; else ++s->st.flush_deadline;
         if (n > s->st.max_batch_seen) s->st.max_batch_seen = n;
         lk.unlock();
 

@@ -70,12 +70,15 @@ private:
 struct BatchingConfig {
     uint32_t max_batch = 4096;             // requests per flush
     uint32_t max_wait_us = 200;            // deadline from the first queued request
+    uint32_t idle_flush_us = 20;           // flush earlier once no request has arrived for this long
+                                           // (a closed population of callers is all queued by then)
     uint64_t max_payload_bytes = 32u << 20;
     uint32_t max_name_bytes_per_request = 64;
 };
 
 struct BatchingStats {
-    uint64_t requests = 0, batches = 0, flush_full = 0, flush_deadline = 0, max_batch_seen = 0, errors = 0;
+    uint64_t requests = 0, batches = 0, flush_full = 0, flush_deadline = 0, flush_idle = 0,
+             max_batch_seen = 0, errors = 0;
 };
 
 class BatchingService final : public Service {
@@ -97,11 +100,7 @@ private:
         std::string payload;
         pk_decision decision{};
         int rc = 0;
-        // completion is signalled under `mu`, so the waiter (whose stack owns this object)
-        // cannot return and destroy it while the flusher still touches it
-        std::mutex mu;
-        std::condition_variable cv;
-        bool done = false;
+        bool done = false;                  // guarded by Shard::done_mu
     };
     struct Arena {                          // one per backend slot
         uint8_t* payload = nullptr;
@@ -120,6 +119,12 @@ private:
         std::vector<Arena> arenas;
         std::thread th;
         BatchingStats st;
+        // Completion: a whole batch is marked done under done_mu and announced with ONE
+        // notify_all (a futex broadcast) instead of one wake-up call per request.  The waiter,
+        // whose stack owns the Pending, re-checks under done_mu, so it cannot return and destroy
+        // the object while the flusher still touches it.
+        std::mutex done_mu;
+        std::condition_variable done_cv;
     };
     void flusher(Shard* s);
     void complete(Shard* s, Arena& a, int rc);

@@ -157,10 +157,10 @@ static void test_batching(uint32_t n_gpus, uint32_t threads, uint32_t per_thread
     Context ctx;
     Result r = svc.ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr);
     CHECK(r.error && !r.resp);                                                       // after Shutdown: error, not a hang
-    std::printf("batching %s gpus=%u threads=%u: %llu requests in %llu batches (full %llu, deadline %llu, max %llu)\n",
+    std::printf("batching %s gpus=%u threads=%u: %llu requests in %llu batches (full %llu, deadline %llu, idle %llu, max %llu)\n",
                 cuda ? "cuda" : "cpu-stand-in", n_gpus, threads, (unsigned long long)st.requests, (unsigned long long)st.batches,
                 (unsigned long long)st.flush_full, (unsigned long long)st.flush_deadline,
-                (unsigned long long)st.max_batch_seen);
+                (unsigned long long)st.flush_idle, (unsigned long long)st.max_batch_seen);
 }
 
 static void test_device_error_path()

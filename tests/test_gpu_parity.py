@@ -262,6 +262,40 @@ def test_config_c3_full(pk, oracle):
         r.close()
 
 
+def test_config_c4_one_full_shard(pk, oracle):
+    """BASELINE configs[4] at full size for one rank: 1,000,000 requests x 2 KB sharded over 8 GPUs
+    is 125,000 requests (256 MB) per GPU; rank 3's shard, ids 3, 11, 19, ... generated directly."""
+    n, length = 125000, 2048
+    r = pk.Router(device=0, max_requests=n, max_payload_bytes=n * length, n_slots=1)
+    try:
+        # the generator is seeded per request id, so a rank can generate its own ids; here the
+        # shard's ids are contiguous in the rank-local numbering used by bench.py
+        b = oracle.gen_batch(oracle.SEED_BASE + 4, n, length, mode=0, first_id=3 * n, threads=16)
+        rc, want = oracle.route_batch(oracle.default_table(), b, threads=32, fast=True)
+        assert rc == 0
+        assert_records_equal(r.route_batch(b), want, "C4 shard")
+    finally:
+        r.close()
+
+
+def test_maximum_sizes(pk, oracle):
+    """The largest request the reference's transport accepts is 4 MiB (grpc-go default,
+    cmd/polykey/main.go:74-77); also one request far beyond it, and a 1,000-byte tool name."""
+    table = oracle.default_table()
+    reqs = [(b"example_tool", bytes(np.random.default_rng(5).integers(32, 127, 4 << 20, dtype=np.uint8))),
+            (b"n" * 1000, b"short payload with a very long name"),
+            (b"file_tool", bytes(np.random.default_rng(6).integers(0, 256, (33 << 20) + 7, dtype=np.uint8)))]
+    b = pk.pack_requests(reqs)
+    r = pk.Router(device=0, max_requests=8, max_payload_bytes=int(b["pay_off"][-1]), max_name_bytes=4096, n_slots=1)
+    try:
+        rc, want = oracle.route_batch(table, b, threads=3, fast=True)
+        assert rc == 0
+        assert_records_equal(r.route_batch(b), want, "maximum sizes")
+        assert (oracle.route_batch(table, b, threads=3)[1] == want).all()      # fast port == plain oracle here too
+    finally:
+        r.close()
+
+
 def test_config_c4_shards(pk, router, oracle):
     """BASELINE configs[4]: the stream is sharded by request id (req_id % G) with no exchange;
     each shard's records equal the corresponding rows of the unsharded result."""
