@@ -14,8 +14,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpkroute.so")
-SOURCES = ["pk_kernels.cu", "pk_abi.cu", "pk_noalloc.cu"]
-HEADERS = ["pk_kernels.cuh", "pk_spec.cuh", os.path.join("..", "..", "include", "pk_route.h")]
+SOURCES = ["pk_kernels.cu", "pk_abi.cu", "pk_noalloc.cu", "pk_gcm.cu"]
+HEADERS = ["pk_kernels.cuh", "pk_spec.cuh", "pk_gcm.cuh", os.path.join("..", "..", "include", "pk_route.h"),
+           os.path.join("..", "..", "include", "pk_gcm.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-shared"]
 

@@ -1,0 +1,220 @@
+// pk_gcm.cu — batched AES-256-GCM on the GPU and its C ABI (declared in include/pk_gcm.h).
+//
+// The batched form of BatchEncrypt / BatchDecrypt, internal/adapters/security/cipher.go:110-141:
+// the reference walks the batch sequentially and rebuilds the AES key schedule and the GCM state
+// for every message (cipher.go:35-43 inside the loops at :116-122 and :133-139).  Here the key
+// schedule, the T-table and the GHASH table are built once per key on the host; one GPU thread
+// then seals or opens one message (messages here are secrets: tens of bytes to a few KB), with
+// the T-table and the key context staged in shared memory.  Integer/LDS-bound work — no tensor
+// cores, and not HBM-bound: ~60 instructions per byte.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <new>
+
+#include "../../include/pk_gcm.h"
+#include "pk_gcm.cuh"
+
+namespace {
+
+using pkgcm::KeyContext;
+constexpr int kThreads = 128;
+
+// mode 0: seal   in = plaintext arena,  out = sealed arena (nonce || ct || tag per message)
+// mode 1: open   in = sealed arena,     out = plaintext arena; status[i] = 0 ok / 1 auth / 2 short
+__global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restrict__ kc_g,
+                                                       const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
+                                                       const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
+                                                       uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
+                                                       uint32_t* __restrict__ status, uint32_t n, int mode)
+{
+    __shared__ KeyContext kc;
+    static_assert(sizeof(KeyContext) % 16 == 0, "KeyContext is staged as uint4");
+    for (uint32_t i = threadIdx.x; i < sizeof(KeyContext) / 16; i += kThreads)
+        reinterpret_cast<uint4*>(&kc)[i] = __ldg(reinterpret_cast<const uint4*>(kc_g) + i);
+    __syncthreads();
+
+    const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t* src = in + in_off[i];
+    uint8_t* dst = out + out_off[i];
+    const uint32_t len = in_len[i];
+    uint8_t tag[16];
+    if (mode == 0) {
+        const uint8_t* nonce = nonces + (size_t)i * pkgcm::kNonceBytes;
+        for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];           // cipher.go:51-52
+        pkgcm::gcm_crypt_message(&kc, kc.te0, nonce, src, dst + pkgcm::kNonceBytes, len, false, tag);
+        for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) dst[pkgcm::kNonceBytes + len + b] = tag[b];
+    } else {
+        if (len < pkgcm::kOverhead) {                     // shorter than nonce + tag: cipher.go:69-71 / Open fails
+            status[i] = len < pkgcm::kNonceBytes ? 2u : 1u;
+            return;
+        }
+        const uint32_t clen = len - pkgcm::kOverhead;
+        pkgcm::gcm_crypt_message(&kc, kc.te0, src, src + pkgcm::kNonceBytes, dst, clen, true, tag);
+        uint32_t diff = 0;
+        for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) diff |= (uint32_t)(tag[b] ^ src[pkgcm::kNonceBytes + clen + b]);
+        if (diff != 0) {                                  // authentication failed: release no plaintext
+            for (uint32_t b = 0; b < clen; ++b) dst[b] = 0;
+            status[i] = 1u;
+        } else {
+            status[i] = 0u;
+        }
+    }
+}
+
+}  // namespace
+
+struct pk_gcm {
+    int device = 0;
+    uint32_t max_messages = 0;
+    uint64_t max_bytes = 0;
+    KeyContext* d_kc = nullptr;
+    uint8_t *d_in = nullptr, *d_out = nullptr, *d_nonce = nullptr;
+    uint64_t *d_in_off = nullptr, *d_out_off = nullptr;
+    uint32_t *d_len = nullptr, *d_status = nullptr;
+    cudaStream_t stream = nullptr;
+    int last_cuda = 0;
+    uint64_t launches = 0;
+};
+
+namespace {
+
+#define PKG_CUDA(h, call)                                   \
+    do {                                                    \
+        cudaError_t e__ = (call);                           \
+        if (e__ != cudaSuccess) {                           \
+            if (h) (h)->last_cuda = (int)e__;               \
+            (void)cudaGetLastError();                       \
+            return PK_GCM_ERR_CUDA;                         \
+        }                                                   \
+    } while (0)
+
+int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const uint32_t* in_len,
+        const uint8_t* nonces, uint32_t n, uint8_t* out, const uint64_t* out_off, uint32_t* status)
+{
+    if (!h) return PK_GCM_ERR_ARG;
+    if (n == 0) return PK_GCM_OK;
+    if (!in_off || !in_len || !out_off || !out || (mode == 0 && !nonces) || (mode == 1 && !status)) return PK_GCM_ERR_ARG;
+    if (n > h->max_messages) return PK_GCM_ERR_CAPACITY;
+    // validate layout: 16-byte aligned, non-overlapping slots in order; compute extents
+    uint64_t in_end = 0, out_end = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint64_t need_out = mode == 0 ? (uint64_t)in_len[i] + pkgcm::kOverhead
+                                            : (in_len[i] >= pkgcm::kOverhead ? in_len[i] - pkgcm::kOverhead : 0);
+        if (in_off[i] % 16 || out_off[i] % 16) return PK_GCM_ERR_ALIGN;
+        if (in_off[i] < in_end || out_off[i] < out_end) return PK_GCM_ERR_OFFSETS;
+        in_end = in_off[i] + in_len[i];
+        out_end = out_off[i] + need_out;
+    }
+    if (in_end > h->max_bytes || out_end > h->max_bytes) return PK_GCM_ERR_CAPACITY;
+    if (in_end && !in) return PK_GCM_ERR_ARG;
+
+    PKG_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    if (in_end) PKG_CUDA(h, cudaMemcpyAsync(h->d_in, in, in_end, cudaMemcpyHostToDevice, st));
+    PKG_CUDA(h, cudaMemcpyAsync(h->d_in_off, in_off, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    PKG_CUDA(h, cudaMemcpyAsync(h->d_out_off, out_off, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    PKG_CUDA(h, cudaMemcpyAsync(h->d_len, in_len, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    if (mode == 0) PKG_CUDA(h, cudaMemcpyAsync(h->d_nonce, nonces, (size_t)n * pkgcm::kNonceBytes, cudaMemcpyHostToDevice, st));
+    gcm_kernel<<<(n + kThreads - 1) / kThreads, kThreads, 0, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
+                                                                   h->d_out, h->d_out_off, h->d_status, n, mode);
+    PKG_CUDA(h, cudaGetLastError());
+    ++h->launches;
+    if (out_end) PKG_CUDA(h, cudaMemcpyAsync(out, h->d_out, out_end, cudaMemcpyDeviceToHost, st));
+    if (mode == 1) PKG_CUDA(h, cudaMemcpyAsync(status, h->d_status, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    PKG_CUDA(h, cudaStreamSynchronize(st));
+    if (mode == 1)
+        for (uint32_t i = 0; i < n; ++i)
+            if (status[i] != 0) return PK_GCM_ERR_AUTH;       // BatchDecrypt fails as a whole, cipher.go:135-137
+    return PK_GCM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* pk_gcm_strerror(int status)
+{
+    switch (status) {
+    case PK_GCM_OK:           return "ok";
+    case PK_GCM_ERR_ARG:      return "invalid argument";
+    case PK_GCM_ERR_ALIGN:    return "message offset is not a multiple of 16";
+    case PK_GCM_ERR_OFFSETS:  return "message slots overlap or are out of order";
+    case PK_GCM_ERR_CAPACITY: return "batch exceeds the capacity given to pk_gcm_init";
+    case PK_GCM_ERR_CUDA:     return "CUDA runtime error";
+    case PK_GCM_ERR_NO_DEVICE:return "no usable CUDA device";
+    case PK_GCM_ERR_KEYLEN:   return "key length must be 32 bytes";
+    case PK_GCM_ERR_AUTH:     return "failed to decrypt: message authentication failed";
+    default:                  return "unknown pk_gcm status";
+    }
+}
+
+int pk_gcm_init(int device, const uint8_t* key, uint32_t key_len, uint32_t max_messages,
+                uint64_t max_bytes, pk_gcm** out)
+{
+    if (!out) return PK_GCM_ERR_ARG;
+    *out = nullptr;
+    if (!key || max_messages == 0) return PK_GCM_ERR_ARG;
+    if (key_len != 32) return PK_GCM_ERR_KEYLEN;          // validateKey, cipher.go:15-19
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { (void)cudaGetLastError(); return PK_GCM_ERR_NO_DEVICE; }
+    if (device < 0 || device >= count) return PK_GCM_ERR_NO_DEVICE;
+    pk_gcm* h = new (std::nothrow) pk_gcm();
+    if (!h) return PK_GCM_ERR_ARG;
+    h->device = device;
+    h->max_messages = max_messages;
+    h->max_bytes = max_bytes;
+    KeyContext kc;
+    pkgcm::make_key_context(key, kc);
+    const size_t n = max_messages;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_kc, sizeof kc);
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_kc, &kc, sizeof kc, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_in, max_bytes + 64);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_out, max_bytes + 64);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_nonce, n * pkgcm::kNonceBytes);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_in_off, n * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_out_off, n * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_len, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_status, n * 4);
+    std::memset(&kc, 0, sizeof kc);                       // do not leave key material on the stack
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        pk_gcm_destroy(h);
+        return PK_GCM_ERR_CUDA;
+    }
+    *out = h;
+    return PK_GCM_OK;
+}
+
+void pk_gcm_destroy(pk_gcm* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->d_kc) { cudaMemset(h->d_kc, 0, sizeof(KeyContext)); cudaFree(h->d_kc); }
+    void* bufs[] = {h->d_in, h->d_out, h->d_nonce, h->d_in_off, h->d_out_off, h->d_len, h->d_status};
+    for (void* b : bufs) if (b) cudaFree(b);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    (void)cudaGetLastError();
+    delete h;
+}
+
+int pk_gcm_seal_batch(pk_gcm* h, const uint8_t* plain, const uint64_t* plain_off, const uint32_t* plain_len,
+                      const uint8_t* nonces, uint32_t n, uint8_t* sealed, const uint64_t* sealed_off)
+{
+    return run(h, 0, plain, plain_off, plain_len, nonces, n, sealed, sealed_off, nullptr);
+}
+
+int pk_gcm_open_batch(pk_gcm* h, const uint8_t* sealed, const uint64_t* sealed_off, const uint32_t* sealed_len,
+                      uint32_t n, uint8_t* plain, const uint64_t* plain_off, uint32_t* status)
+{
+    return run(h, 1, sealed, sealed_off, sealed_len, nullptr, n, plain, plain_off, status);
+}
+
+uint64_t pk_gcm_launch_count(const pk_gcm* h) { return h ? h->launches : 0; }
+int pk_gcm_last_cuda_error(const pk_gcm* h) { return h ? h->last_cuda : 0; }
+
+}  // extern "C"

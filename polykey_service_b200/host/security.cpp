@@ -1,0 +1,151 @@
+// security.cpp — see security.hpp.
+#include "security.hpp"
+
+#include <sys/random.h>
+
+#include <cstring>
+
+namespace polykey::security {
+
+namespace {
+inline uint64_t round16(uint64_t x) { return (x + 15u) & ~uint64_t(15); }
+}
+
+Error validateKey(const Bytes& key)
+{
+    if (key.size() != 32)                               // cipher.go:16-17
+        return "key length must be 32 bytes, got " + std::to_string(key.size()) + " bytes";
+    return std::nullopt;
+}
+
+GpuCipher::GpuCipher(const Bytes& key, int device, uint32_t max_messages, uint64_t max_bytes)
+{
+    init_error_ = validateKey(key);
+    if (init_error_) return;
+    const int rc = pk_gcm_init(device, key.data(), (uint32_t)key.size(), max_messages, max_bytes, &h_);
+    if (rc != PK_GCM_OK) {
+        h_ = nullptr;
+        init_error_ = std::string("failed to create AES cipher: ") + pk_gcm_strerror(rc);   // cipher.go:37
+    }
+}
+
+GpuCipher::~GpuCipher() { if (h_) pk_gcm_destroy(h_); }
+
+BatchResult GpuCipher::BatchEncrypt(const std::vector<Bytes>& plaintexts, const std::vector<Bytes>* nonces)
+{
+    if (init_error_) return {{}, init_error_};
+    const uint32_t n = (uint32_t)plaintexts.size();
+    if (n == 0) return {{}, std::nullopt};
+    std::vector<uint64_t> poff(n), soff(n);
+    std::vector<uint32_t> plen(n);
+    uint64_t pat = 0, sat = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        plen[i] = (uint32_t)plaintexts[i].size();
+        poff[i] = pat; soff[i] = sat;
+        pat += round16(plen[i]);
+        sat += round16((uint64_t)plen[i] + PK_GCM_OVERHEAD);
+    }
+    Bytes plain(pat + 16), sealed(sat + 16), nonce_arr((size_t)n * PK_GCM_NONCE_BYTES);
+    for (uint32_t i = 0; i < n; ++i)
+        if (plen[i]) std::memcpy(plain.data() + poff[i], plaintexts[i].data(), plen[i]);
+    if (nonces) {
+        for (uint32_t i = 0; i < n; ++i) {
+            if ((*nonces)[i].size() != PK_GCM_NONCE_BYTES) return {{}, std::string("failed to encrypt plaintext: bad nonce length")};
+            std::memcpy(nonce_arr.data() + (size_t)i * PK_GCM_NONCE_BYTES, (*nonces)[i].data(), PK_GCM_NONCE_BYTES);
+        }
+    } else {
+        size_t got = 0;                                  // generateNonce, cipher.go:25-31
+        while (got < nonce_arr.size()) {
+            const ssize_t r = getrandom(nonce_arr.data() + got, nonce_arr.size() - got, 0);
+            if (r <= 0) return {{}, std::string("failed to encrypt plaintext: failed to generate nonce")};
+            got += (size_t)r;
+        }
+    }
+    const int rc = pk_gcm_seal_batch(h_, plain.data(), poff.data(), plen.data(), nonce_arr.data(), n, sealed.data(), soff.data());
+    if (rc != PK_GCM_OK) return {{}, std::string("failed to encrypt plaintext: ") + pk_gcm_strerror(rc)};   // cipher.go:119
+    BatchResult out;
+    out.values.reserve(n);
+    for (uint32_t i = 0; i < n; ++i)
+        out.values.emplace_back(sealed.begin() + (ptrdiff_t)soff[i], sealed.begin() + (ptrdiff_t)(soff[i] + plen[i] + PK_GCM_OVERHEAD));
+    return out;
+}
+
+BatchResult GpuCipher::BatchDecrypt(const std::vector<Bytes>& ciphertexts)
+{
+    if (init_error_) return {{}, init_error_};
+    const uint32_t n = (uint32_t)ciphertexts.size();
+    if (n == 0) return {{}, std::nullopt};
+    std::vector<uint64_t> soff(n), poff(n);
+    std::vector<uint32_t> slen(n), status(n, 0);
+    uint64_t sat = 0, pat = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        slen[i] = (uint32_t)ciphertexts[i].size();
+        soff[i] = sat; poff[i] = pat;
+        sat += round16(slen[i]);
+        pat += round16(slen[i] >= PK_GCM_OVERHEAD ? slen[i] - PK_GCM_OVERHEAD : 0);
+    }
+    Bytes sealed(sat + 16), plain(pat + 16);
+    for (uint32_t i = 0; i < n; ++i)
+        if (slen[i]) std::memcpy(sealed.data() + soff[i], ciphertexts[i].data(), slen[i]);
+    const int rc = pk_gcm_open_batch(h_, sealed.data(), soff.data(), slen.data(), n, plain.data(), poff.data(), status.data());
+    if (rc == PK_GCM_ERR_AUTH) {
+        for (uint32_t i = 0; i < n; ++i) {               // the first failing item decides the message, cipher.go:133-137
+            if (status[i] == 2)
+                return {{}, "failed to decrypt ciphertext: ciphertext too short: " + std::to_string(slen[i]) +
+                                " bytes, expected at least " + std::to_string(PK_GCM_NONCE_BYTES) + " bytes"};   // cipher.go:70
+            if (status[i] == 1)
+                return {{}, std::string("failed to decrypt ciphertext: failed to decrypt: cipher: message authentication failed")};   // cipher.go:80
+        }
+    }
+    if (rc != PK_GCM_OK) return {{}, std::string("failed to decrypt ciphertext: ") + pk_gcm_strerror(rc)};
+    BatchResult out;
+    out.values.reserve(n);
+    for (uint32_t i = 0; i < n; ++i)
+        out.values.emplace_back(plain.begin() + (ptrdiff_t)poff[i], plain.begin() + (ptrdiff_t)(poff[i] + slen[i] - PK_GCM_OVERHEAD));
+    return out;
+}
+
+// ---- the reference's four exported functions (cipher.go:92-141) ----
+BatchResult BatchEncrypt(const Bytes& key, const std::vector<Bytes>& plaintexts)
+{
+    if (Error e = validateKey(key)) return {{}, e};       // cipher.go:111-113
+    uint64_t bytes = 64;
+    for (const Bytes& p : plaintexts) bytes += round16(p.size() + PK_GCM_OVERHEAD);
+    GpuCipher c(key, 0, (uint32_t)plaintexts.size() + 1, bytes);
+    return c.BatchEncrypt(plaintexts);
+}
+
+BatchResult BatchDecrypt(const Bytes& key, const std::vector<Bytes>& ciphertexts)
+{
+    if (Error e = validateKey(key)) return {{}, e};       // cipher.go:127-129
+    uint64_t bytes = 64;
+    for (const Bytes& c : ciphertexts) bytes += round16(c.size());
+    GpuCipher c(key, 0, (uint32_t)ciphertexts.size() + 1, bytes);
+    return c.BatchDecrypt(ciphertexts);
+}
+
+namespace {
+// a single Encrypt / Decrypt returns encryptKey's / decryptKey's error without the batch wrapper
+std::string unwrap(const std::string& msg, const std::string& prefix)
+{
+    return msg.rfind(prefix, 0) == 0 ? msg.substr(prefix.size()) : msg;
+}
+}  // namespace
+
+BytesResult Encrypt(const Bytes& key, const Bytes& plaintext)
+{
+    if (Error e = validateKey(key)) return {{}, e};       // cipher.go:93-95
+    BatchResult r = BatchEncrypt(key, {plaintext});
+    if (r.error) return {{}, unwrap(*r.error, "failed to encrypt plaintext: ")};
+    return {std::move(r.values[0]), std::nullopt};
+}
+
+BytesResult Decrypt(const Bytes& key, const Bytes& ciphertext)
+{
+    if (Error e = validateKey(key)) return {{}, e};       // cipher.go:100-102
+    BatchResult r = BatchDecrypt(key, {ciphertext});
+    if (r.error) return {{}, unwrap(*r.error, "failed to decrypt ciphertext: ")};   // cipher.go:103, 69-81
+    return {std::move(r.values[0]), std::nullopt};
+}
+
+}  // namespace polykey::security

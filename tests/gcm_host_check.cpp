@@ -1,0 +1,57 @@
+// gcm_host_check.cpp — the AES-256-GCM building blocks of csrc/pk_gcm.cuh compiled for the host,
+// so tests/test_gcm_cpu.py can check them against OpenSSL (Python `cryptography`) and the NIST
+// known-answer tests without a GPU.  Test-only code.
+#include <cstdint>
+#include <cstring>
+
+#include "../polykey_service_b200/csrc/pk_gcm.cuh"
+
+using namespace pkgcm;
+
+extern "C" void gcmh_seal(const uint8_t* key, const uint8_t* nonce, const uint8_t* pt, uint32_t len, uint8_t* out)
+{
+    KeyContext kc;
+    make_key_context(key, kc);
+    std::memcpy(out, nonce, 12);
+    uint8_t tag[16];
+    gcm_crypt_message(&kc, kc.te0, nonce, pt, out + 12, len, false, tag);
+    std::memcpy(out + 12 + len, tag, 16);
+}
+
+// returns 0 ok, 1 auth failure, 2 too short
+extern "C" int gcmh_open(const uint8_t* key, const uint8_t* sealed, uint32_t len, uint8_t* pt)
+{
+    if (len < 12) return 2;
+    if (len < 28) return 1;
+    KeyContext kc;
+    make_key_context(key, kc);
+    uint8_t tag[16];
+    gcm_crypt_message(&kc, kc.te0, sealed, sealed + 12, pt, len - 28, true, tag);
+    return std::memcmp(tag, sealed + len - 16, 16) == 0 ? 0 : 1;
+}
+
+extern "C" void gcmh_encrypt_block(const uint8_t* key, const uint8_t in[16], uint8_t out[16])
+{
+    KeyContext kc;
+    make_key_context(key, kc);
+    uint32_t s[4] = {load_be32(in), load_be32(in + 4), load_be32(in + 8), load_be32(in + 12)};
+    aes256_encrypt_block(kc.te0, kc.rk, s);
+    for (int j = 0; j < 4; ++j) { out[4*j] = s[j] >> 24; out[4*j+1] = s[j] >> 16; out[4*j+2] = s[j] >> 8; out[4*j+3] = s[j]; }
+}
+
+// table-driven multiply vs the bit-by-bit textbook one; returns the number of mismatches
+extern "C" int gcmh_check_ghash(const uint8_t* key, uint64_t seed, int trials)
+{
+    KeyContext kc;
+    make_key_context(key, kc);
+    int bad = 0;
+    for (int t = 0; t < trials; ++t) {
+        seed = seed * 6364136223846793005ull + 1442695040888963407ull; uint64_t a = seed;
+        seed = seed * 6364136223846793005ull + 1442695040888963407ull; uint64_t b = seed;
+        uint64_t xh = a, xl = b, yh = a, yl = b;
+        ghash_mul(kc.hh, kc.hl, xh, xl);
+        ghash_mul_bitwise(kc.hh[8], kc.hl[8], yh, yl);
+        if (xh != yh || xl != yl) ++bad;
+    }
+    return bad;
+}

@@ -11,8 +11,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def declared_symbols():
-    src = open(os.path.join(ROOT, "include", "pk_route.h")).read()
-    return sorted(set(re.findall(r"^PK_API[^;(]*?\b(pk_\w+)\s*\(", src, flags=re.M)))
+    names = set()
+    for hdr in ("pk_route.h", "pk_gcm.h"):
+        src = open(os.path.join(ROOT, "include", hdr)).read()
+        names |= set(re.findall(r"^(?:PK_API|PK_GCM_API)[^;(]*?\b(pk_\w+)\s*\(", src, flags=re.M))
+    return sorted(names)
 
 
 def test_every_declared_symbol_is_exported(pk):

@@ -1,0 +1,112 @@
+"""GPU: batched AES-256-GCM through the C ABI (include/pk_gcm.h) against OpenSSL (Python
+`cryptography`) and the standard's known-answer tests — bit-exact.
+
+Reference: BatchEncrypt / BatchDecrypt, internal/adapters/security/cipher.go:110-141; output format
+nonce || ciphertext || tag (cipher.go:51-52); key must be 32 bytes (cipher.go:15-19); a ciphertext
+shorter than a nonce and any authentication failure are errors (cipher.go:69-71, 78-81)."""
+import numpy as np
+import pytest
+from cryptography.hazmat.primitives.ciphers.aead import AESGCM
+
+from test_gcm_cpu import KATS
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def G(pk):
+    from polykey_service_b200 import gcm
+    return gcm
+
+
+def test_known_answer_tests_on_gpu(G):
+    for key, iv, pt, ct, tag in KATS:
+        with G.Gcm(bytes.fromhex(key), max_messages=4, max_bytes=4096) as g:
+            out = g.batch_encrypt([bytes.fromhex(pt)], [bytes.fromhex(iv)])
+            assert out[0].hex() == iv + ct + tag
+            assert g.batch_decrypt(out) == [bytes.fromhex(pt)]
+
+
+def test_batch_matches_openssl(G):
+    rng = np.random.default_rng(11)
+    key = rng.bytes(32)
+    lengths = list(range(0, 80)) + [127, 128, 129, 255, 256, 257, 1000, 4096, 4099, 20000] + \
+        rng.integers(0, 600, 3000).tolist()
+    pts = [rng.bytes(int(l)) for l in lengths]
+    nonces = [rng.bytes(12) for _ in lengths]
+    ref = AESGCM(key)
+    with G.Gcm(key, max_messages=8192, max_bytes=8 << 20) as g:
+        before = g.launch_count
+        sealed = g.batch_encrypt(pts, nonces)
+        assert g.launch_count == before + 1                        # one launch for the whole batch
+        for s, p, nce in zip(sealed, pts, nonces):
+            assert s == nce + ref.encrypt(nce, p, None)
+        assert g.batch_decrypt(sealed) == pts                      # round trip on the GPU
+        # and the GPU opens what OpenSSL sealed
+        theirs = [nce + ref.encrypt(nce, p, None) for p, nce in zip(pts[:200], nonces[:200])]
+        assert g.batch_decrypt(theirs) == pts[:200]
+
+
+def test_tampering_and_short_ciphertexts(G):
+    rng = np.random.default_rng(12)
+    key = rng.bytes(32)
+    pts = [rng.bytes(50) for _ in range(64)]
+    nonces = [rng.bytes(12) for _ in range(64)]
+    with G.Gcm(key, max_messages=128, max_bytes=1 << 20) as g:
+        sealed = g.batch_encrypt(pts, nonces)
+        bad = list(sealed)
+        bad[3] = bytes([bad[3][0] ^ 1]) + bad[3][1:]                # nonce bit
+        bad[17] = bad[17][:20] + bytes([bad[17][20] ^ 0x80]) + bad[17][21:]     # ciphertext bit
+        bad[40] = bad[40][:-1] + bytes([bad[40][-1] ^ 2])           # tag bit
+        bad[50] = b"short"                                          # cipher.go:69-71
+        bad[51] = bytes(20)                                         # nonce but no room for a tag
+        with pytest.raises(G.GcmError) as e:                        # BatchDecrypt fails as a whole
+            g.batch_decrypt(bad)
+        assert e.value.code == -10
+        st = e.value.status
+        assert [int(i) for i in np.nonzero(st)[0]] == [3, 17, 40, 50, 51]
+        assert st[50] == 2 and st[51] == 1 and st[3] == 1
+        assert g.batch_decrypt(sealed) == pts                       # the handle is still healthy
+    with G.Gcm(rng.bytes(32), max_messages=128, max_bytes=1 << 20) as other:   # wrong key
+        with pytest.raises(G.GcmError):
+            other.batch_decrypt(sealed[:4])
+
+
+def test_key_length_and_argument_errors(G):
+    for bad_len in (0, 16, 24, 31, 33):
+        with pytest.raises(G.GcmError) as e:                        # validateKey, cipher.go:15-19
+            G.Gcm(bytes(bad_len) or b"", max_messages=4, max_bytes=4096)
+        assert e.value.code in (-9, -1)
+    with G.Gcm(bytes(32), max_messages=4, max_bytes=256) as g:
+        assert g.batch_encrypt([], []) == []
+        with pytest.raises(G.GcmError) as e:
+            g.batch_encrypt([b"x"] * 5, [bytes(12)] * 5)
+        assert e.value.code == -4
+        with pytest.raises(G.GcmError) as e:
+            g.batch_encrypt([bytes(400)], [bytes(12)])
+        assert e.value.code == -4
+        plen = np.array([4, 4], dtype=np.uint32)
+        off = np.array([0, 8], dtype=np.uint64)                    # not 16-byte aligned
+        with pytest.raises(G.GcmError) as e:
+            g.seal_arena(np.zeros(64, np.uint8), off, plen, np.zeros(24, np.uint8), np.zeros(256, np.uint8),
+                         np.array([0, 48], dtype=np.uint64))
+        assert e.value.code == -2
+
+
+def test_large_batch_of_secrets(G):
+    """65,536 secrets of 32-256 bytes: the shape this helper exists for."""
+    rng = np.random.default_rng(13)
+    key = rng.bytes(32)
+    n = 65536
+    lens = rng.integers(32, 257, n)
+    blob = rng.bytes(int(lens.sum()))
+    cuts = np.concatenate([[0], np.cumsum(lens)])
+    pts = [blob[int(cuts[i]):int(cuts[i + 1])] for i in range(n)]
+    nonce_blob = rng.bytes(12 * n)
+    nonces = [nonce_blob[12 * i:12 * i + 12] for i in range(n)]
+    with G.Gcm(key, max_messages=n, max_bytes=32 << 20) as g:
+        sealed = g.batch_encrypt(pts, nonces)
+        ref = AESGCM(key)
+        for i in rng.integers(0, n, 2000).tolist() + [0, n - 1]:
+            assert sealed[i] == nonces[i] + ref.encrypt(nonces[i], pts[i], None)
+        assert g.batch_decrypt(sealed) == pts

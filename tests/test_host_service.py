@@ -36,3 +36,28 @@ def test_host_mirror_cpu(host_test_exe):
 def test_host_mirror_cuda_backend(host_test_exe):
     out = subprocess.run([host_test_exe, "cuda"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "HOST CUDA TESTS OK" in out.stdout, out.stdout + out.stderr
+
+
+@pytest.fixture(scope="module")
+def security_test_exe(tmp_path_factory, pk):
+    exe = str(tmp_path_factory.mktemp("sec") / "host_security_test")
+    host = os.path.join(ROOT, "polykey_service_b200", "host")
+    subprocess.check_call([
+        "g++", "-std=c++20", "-O2", "-Wall", "-Wextra", "-o", exe,
+        os.path.join(ROOT, "tests", "host_security_test.cpp"), os.path.join(host, "security.cpp"),
+        "-L" + os.path.join(ROOT, "polykey_service_b200"), "-lpkroute",
+        "-Wl,-rpath," + os.path.join(ROOT, "polykey_service_b200")])
+    return exe
+
+
+def test_security_mirror_cpu(security_test_exe):
+    """Key validation and its message (cipher.go:15-19) need no GPU."""
+    out = subprocess.run([security_test_exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "SECURITY TESTS OK" in out.stdout, out.stdout + out.stderr
+
+
+@pytest.mark.gpu
+def test_security_mirror_cuda(security_test_exe):
+    """Encrypt / Decrypt / BatchEncrypt / BatchDecrypt (cipher.go:92-141) on the device."""
+    out = subprocess.run([security_test_exe, "cuda"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "SECURITY TESTS OK" in out.stdout, out.stdout + out.stderr
