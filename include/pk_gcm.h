@@ -72,6 +72,8 @@ PK_GCM_API int  pk_gcm_open_batch(pk_gcm* h, const uint8_t* sealed, const uint64
 
 PK_GCM_API const char* pk_gcm_strerror(int status);
 PK_GCM_API uint64_t    pk_gcm_launch_count(const pk_gcm* h);
+/* Device time of the kernel of the last seal/open call (CUDA events on its stream), ms; < 0 if none. */
+PK_GCM_API float       pk_gcm_last_kernel_ms(pk_gcm* h);
 PK_GCM_API int         pk_gcm_last_cuda_error(const pk_gcm* h);
 
 #ifdef __cplusplus

@@ -74,6 +74,7 @@ struct pk_gcm {
     uint64_t *d_in_off = nullptr, *d_out_off = nullptr;
     uint32_t *d_len = nullptr, *d_status = nullptr;
     cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // bracket the kernel of the last call
     int last_cuda = 0;
     uint64_t launches = 0;
 };
@@ -117,9 +118,11 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
     PKG_CUDA(h, cudaMemcpyAsync(h->d_out_off, out_off, (size_t)n * 8, cudaMemcpyHostToDevice, st));
     PKG_CUDA(h, cudaMemcpyAsync(h->d_len, in_len, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     if (mode == 0) PKG_CUDA(h, cudaMemcpyAsync(h->d_nonce, nonces, (size_t)n * pkgcm::kNonceBytes, cudaMemcpyHostToDevice, st));
+    PKG_CUDA(h, cudaEventRecord(h->ev0, st));
     gcm_kernel<<<(n + kThreads - 1) / kThreads, kThreads, 0, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
                                                                    h->d_out, h->d_out_off, h->d_status, n, mode);
     PKG_CUDA(h, cudaGetLastError());
+    PKG_CUDA(h, cudaEventRecord(h->ev1, st));
     ++h->launches;
     if (out_end) PKG_CUDA(h, cudaMemcpyAsync(out, h->d_out, out_end, cudaMemcpyDeviceToHost, st));
     if (mode == 1) PKG_CUDA(h, cudaMemcpyAsync(status, h->d_status, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
@@ -170,6 +173,8 @@ int pk_gcm_init(int device, const uint8_t* key, uint32_t key_len, uint32_t max_m
     const size_t n = max_messages;
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_kc, sizeof kc);
     if (e == cudaSuccess) e = cudaMemcpy(h->d_kc, &kc, sizeof kc, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_in, max_bytes + 64);
@@ -197,6 +202,8 @@ void pk_gcm_destroy(pk_gcm* h)
     if (h->d_kc) { cudaMemset(h->d_kc, 0, sizeof(KeyContext)); cudaFree(h->d_kc); }
     void* bufs[] = {h->d_in, h->d_out, h->d_nonce, h->d_in_off, h->d_out_off, h->d_len, h->d_status};
     for (void* b : bufs) if (b) cudaFree(b);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->stream) cudaStreamDestroy(h->stream);
     (void)cudaGetLastError();
     delete h;
@@ -215,6 +222,15 @@ int pk_gcm_open_batch(pk_gcm* h, const uint8_t* sealed, const uint64_t* sealed_o
 }
 
 uint64_t pk_gcm_launch_count(const pk_gcm* h) { return h ? h->launches : 0; }
+
+float pk_gcm_last_kernel_ms(pk_gcm* h)
+{
+    float ms = -1.f;
+    if (!h || h->launches == 0) return ms;
+    cudaSetDevice(h->device);
+    if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) { (void)cudaGetLastError(); return -1.f; }
+    return ms;
+}
 int pk_gcm_last_cuda_error(const pk_gcm* h) { return h ? h->last_cuda : 0; }
 
 }  // extern "C"

@@ -38,6 +38,7 @@ def lib() -> C.CDLL:
         L.pk_gcm_strerror.argtypes, L.pk_gcm_strerror.restype = [C.c_int], C.c_char_p
         L.pk_gcm_launch_count.argtypes, L.pk_gcm_launch_count.restype = [vp], C.c_uint64
         L.pk_gcm_last_cuda_error.argtypes = [vp]
+        L.pk_gcm_last_kernel_ms.argtypes, L.pk_gcm_last_kernel_ms.restype = [vp], C.c_float
         _bound = True
     return L
 
@@ -82,6 +83,10 @@ class Gcm:
     @property
     def launch_count(self) -> int:
         return int(self._L.pk_gcm_launch_count(self._h))
+
+    @property
+    def last_kernel_ms(self) -> float:
+        return float(self._L.pk_gcm_last_kernel_ms(self._h))
 
     # flat-arena forms (what the ABI takes) ------------------------------------------------
     def seal_arena(self, plain, plain_off, plain_len, nonces, sealed, sealed_off):
