@@ -1,0 +1,59 @@
+"""bench.py's output contract: exactly ONE JSON line on stdout with the agreed keys.
+CPU: the reference arm (`--impl reference`, the oracle port on the host cores).
+GPU: the product arm with a few steps."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BASE_KEYS = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
+             "scaling", "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"}
+
+
+def run_bench(*args, timeout=600):
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *args], capture_output=True,
+                         text=True, timeout=timeout, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, out.stdout[:500]                 # one line, nothing else on stdout
+    return json.loads(lines[0])
+
+
+def test_reference_arm_line(oracle):
+    d = run_bench("--impl", "reference", "--steps", "3", "--warmup", "1")
+    assert BASE_KEYS <= set(d) and d["impl"] == "reference"
+    assert d["metric"] == "routed_requests_per_sec" and d["unit"] == "requests/s" and d["value"] > 0
+    assert d["steps"] == 3 and d["warmup"] == 1 and d["higher_is_better"] is True and d["vs_baseline"] is None
+    assert "workload" in d["config"] and "model" not in d["config"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+
+
+def test_reference_arm_other_ranks_print_nothing(oracle):
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
+                          "--steps", "2", "--warmup", "1"], capture_output=True, text=True, timeout=120, cwd=ROOT, env=env)
+    assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+@pytest.mark.gpu
+def test_product_arm_line(oracle, pk):
+    d = run_bench("--steps", "200", "--warmup", "5")
+    assert BASE_KEYS <= set(d) and "impl" not in d
+    assert d["n_gpus"] == 1 and d["steps"] == 200 and d["warmup"] >= 3 and d["scaling"] == "weak"
+    assert d["gpu_launches"] == 200                                   # our kernel, once per step
+    r = d["roofline"]
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and 0 < r["frac"] < 1.2 and r["peak"] > 1000
+    assert abs(r["achieved"] / r["peak"] - r["frac"]) < 1e-9
+    e = d["e2e"]
+    assert e["value"] > 0 and e["h2d_bytes_per_step"] > 8_000_000 and e["d2h_bytes_per_step"] == 24 * 4096
+    assert e["value"] < d["value"]                                   # copies cost something
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["value"] > 0 and cb["cores"] >= 1
+    c = d["clocks"]
+    assert c["sm_max_mhz"] and c["sm_mhz"] and isinstance(c["reasons"], list)
+    assert "l2" in d["config"] and "workload" in d["config"]
