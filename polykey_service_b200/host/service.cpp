@@ -1,6 +1,7 @@
 // service.cpp — MockService / Server mirrors (see service.hpp for the Go ↔ C++ map).
 #include "service.hpp"
 
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <ctime>
@@ -82,6 +83,34 @@ std::string rfc3339_utc(int64_t unix_seconds)
     char b[40];
     std::strftime(b, sizeof b, "%Y-%m-%dT%H:%M:%SZ", &tmv);
     return b;
+}
+
+int64_t LoggingInterceptor::now_ns()
+{
+    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// time.Duration.String(): "1.5s", "2.25ms", "340µs", "17ns" — the largest unit that keeps the value >= 1
+std::string LoggingInterceptor::format_duration(int64_t ns)
+{
+    char b[48];
+    if (ns < 1000) std::snprintf(b, sizeof b, "%lldns", (long long)ns);
+    else {
+        const char* unit = ns < 1000000 ? "µs" : ns < 1000000000 ? "ms" : "s";
+        const double v = ns < 1000000 ? ns / 1e3 : ns < 1000000000 ? ns / 1e6 : ns / 1e9;
+        std::snprintf(b, sizeof b, "%.9g%s", v, unit);
+    }
+    return b;
+}
+
+void LoggingInterceptor::log(const char* level, const char* msg, const std::string& method,
+                             const std::string* duration, const char* code)
+{
+    if (!sink_) return;
+    std::string line = std::string("{\"level\":\"") + level + "\",\"msg\":\"" + msg + "\",\"method\":\"" + method + "\"";
+    if (duration) line += ",\"duration\":\"" + *duration + "\"";
+    if (code) line += std::string(",\"code\":\"") + code + "\"";
+    sink_->push_back(line + "}");
 }
 
 std::unique_ptr<MockService> NewMockService() { return std::make_unique<MockService>(); }

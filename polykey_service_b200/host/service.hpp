@@ -112,6 +112,34 @@ private:
 };
 inline Server NewServer(Service* s) { return Server(s); }   // server.go:19-24
 
+// loggingInterceptor — cmd/polykey/main.go:25-52.  Wraps one unary call: health checks pass
+// through unlogged (:29-31); otherwise "gRPC call received" before (:33) and "gRPC call finished"
+// with duration and status code after (:44-48) — level ERROR and code "Unknown" when the handler
+// returned a plain error (status.Code of a non-status error), "OK" otherwise.  The response and
+// the error are returned untouched (:50).  Log records go to `sink` as the reference's JSON lines
+// minus the timestamp.
+class LoggingInterceptor {
+public:
+    explicit LoggingInterceptor(std::vector<std::string>* sink) : sink_(sink) {}
+    template <typename Handler>
+    Result Intercept(const std::string& fullMethod, Handler&& handler)
+    {
+        if (fullMethod == "/grpc.health.v1.Health/Check") return handler();
+        const int64_t t0 = now_ns();
+        log("INFO", "gRPC call received", fullMethod, nullptr, nullptr);
+        Result r = handler();
+        const std::string dur = format_duration(now_ns() - t0);
+        const char* code = r.error ? "Unknown" : "OK";
+        log(r.error ? "ERROR" : "INFO", "gRPC call finished", fullMethod, &dur, code);
+        return r;
+    }
+    static std::string format_duration(int64_t ns);      // Go's time.Duration.String() for sub-minute spans
+private:
+    static int64_t now_ns();
+    void log(const char* level, const char* msg, const std::string& method, const std::string* duration, const char* code);
+    std::vector<std::string>* sink_;
+};
+
 std::string rfc3339_utc(int64_t unix_seconds);
 
 }  // namespace polykey

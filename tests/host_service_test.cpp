@@ -101,6 +101,31 @@ static void test_server()
     CHECK(log.back() == "Service ExecuteTool failed error=boom");
 }
 
+static void test_logging_interceptor()
+{
+    // cmd/polykey/main.go:25-52
+    std::vector<std::string> log;
+    LoggingInterceptor li(&log);
+    auto svc = NewMockService();
+    Context ctx; ctx.now_unix = 1;
+    Result ok = li.Intercept("/polykey.v2.PolykeyService/ExecuteTool",
+                             [&] { return svc->ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr); });
+    CHECK(!ok.error && ok.resp && log.size() == 2);
+    CHECK(log[0] == "{\"level\":\"INFO\",\"msg\":\"gRPC call received\",\"method\":\"/polykey.v2.PolykeyService/ExecuteTool\"}");
+    CHECK(log[1].rfind("{\"level\":\"INFO\",\"msg\":\"gRPC call finished\",\"method\":\"/polykey.v2.PolykeyService/ExecuteTool\",\"duration\":\"", 0) == 0);
+    CHECK(log[1].find("\"code\":\"OK\"}") != std::string::npos);
+    FailingService bad;
+    Result err = li.Intercept("/polykey.v2.PolykeyService/ExecuteTool",
+                              [&] { return bad.ExecuteTool(ctx, "x", nullptr, nullptr, nullptr); });
+    CHECK(err.error && *err.error == "boom" && log.size() == 4);                       // error passes through (:50)
+    CHECK(log[3].find("\"level\":\"ERROR\"") != std::string::npos && log[3].find("\"code\":\"Unknown\"") != std::string::npos);
+    Result health = li.Intercept("/grpc.health.v1.Health/Check",
+                                 [&] { return svc->ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr); });
+    CHECK(!health.error && log.size() == 4);                                          // health checks are not logged (:29-31)
+    CHECK(LoggingInterceptor::format_duration(17) == "17ns" && LoggingInterceptor::format_duration(340000) == "340µs");
+    CHECK(LoggingInterceptor::format_duration(2250000) == "2.25ms" && LoggingInterceptor::format_duration(1500000000) == "1.5s");
+}
+
 static void test_batching(uint32_t n_gpus, uint32_t threads, uint32_t per_thread, uint32_t max_batch,
                           bool cuda = false)
 {
@@ -199,6 +224,7 @@ int main(int argc, char** argv)
     }
     test_mock_service();
     test_server();
+    test_logging_interceptor();
     test_batching(1, 1, 40, 64);
     test_batching(1, 16, 60, 4);
     test_batching(1, 16, 120, 32);
