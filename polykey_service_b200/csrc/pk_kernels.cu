@@ -183,19 +183,17 @@ __device__ __noinline__ void decide_call(const DevTable* tbl, const uint8_t* nam
 // decide(): the hash sum is commutative, so name terms can join the lanes' digests before the
 // reduction, and the first lane whose running weight exceeds x is the first such provider.
 __device__ __forceinline__ void finalize_warp(const RouteParams& P, uint32_t req, uint32_t len,
-                                              uint64_t digest, uint32_t tok_lane, uint32_t lane)
+                                              uint64_t digest, uint32_t tok_lane, uint32_t lane,
+                                              uint32_t noff, uint32_t nlen, uint32_t c0, uint32_t c1)
 {
     const DevTable* __restrict__ tbl = P.table;
-    const uint32_t noff = __ldg(P.name_off + req);
-    const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
     const uint8_t* __restrict__ nm = P.names + noff;
 
-    uint32_t c0 = 0, c1 = 0;                      // this lane's name bytes lane and lane+32
-    for (uint32_t j = lane; j < nlen; j += 32) {
-        const uint32_t b = __ldg(nm + j);
-        digest += name_term(j, b);
-        if (j < 32) c0 = b; else if (j < 64) c1 = b;
-    }
+    // c0 / c1: this lane's name bytes `lane` and `lane + 32`, fetched by the caller before the
+    // scan so that their HBM latency hides behind the payload's; longer names read on here
+    if (lane < nlen)       digest += name_term(lane, c0);
+    if (lane + 32u < nlen) digest += name_term(lane + 32u, c1);
+    for (uint32_t j = lane + 64u; j < nlen; j += 32) digest += name_term(j, __ldg(nm + j));
     // tool switch (mock.go:32-64): whole-name byte equality, first match wins
     uint32_t cls = __ldg(&tbl->t.default_class);
     uint32_t unknown = 1;
@@ -300,11 +298,18 @@ __global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : PK_MIN_CTAS_
         for (uint32_t i = wid; i < r_here; i += kWarpsPerCta) {
             const uint32_t req = base_req + i;
             const uint32_t len = __ldg(P.pay_len + req);
+            const uint64_t off = __ldg(P.pay_off + req);
+            // the name is needed only after the scan, but its bytes are two dependent loads away
+            // (offset, then bytes): start them now, next to the payload's
+            const uint32_t noff = __ldg(P.name_off + req);
+            const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
+            const uint32_t c0 = lane < nlen ? (uint32_t)__ldg(P.names + noff + lane) : 0u;
+            const uint32_t c1 = lane + 32u < nlen ? (uint32_t)__ldg(P.names + noff + lane + 32u) : 0u;
             uint64_t digest;
             uint32_t tok;
-            scan_segment(P.payload + __ldg(P.pay_off + req), len, 0u, lane, P.one, digest, tok);
+            scan_segment(P.payload + off, len, 0u, lane, P.one, digest, tok);
             if (len > kSegBytes) fold_long_segment(P, req, len, digest, tok, lane);
-            else                 finalize_warp(P, req, len, digest, tok, lane);
+            else                 finalize_warp(P, req, len, digest, tok, lane, noff, nlen, c0, c1);
         }
         return;
     }
