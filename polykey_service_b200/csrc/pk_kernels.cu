@@ -182,42 +182,70 @@ __device__ __noinline__ void decide_call(const DevTable* tbl, const uint8_t* nam
 // a warp prefix sum — with no shared memory and no CTA barrier on the path.  Same results as
 // decide(): the hash sum is commutative, so name terms can join the lanes' digests before the
 // reduction, and the first lane whose running weight exceeds x is the first such provider.
-__device__ __forceinline__ void finalize_warp(const RouteParams& P, uint32_t req, uint32_t len,
-                                              uint64_t digest, uint32_t tok_lane, uint32_t lane,
-                                              uint32_t noff, uint32_t nlen, uint32_t c0, uint32_t c1)
+//
+// Everything that does not depend on the payload is done BEFORE the scan (warp_prologue), while
+// the payload's first 2 KiB are on their way to L2: the name bytes are two dependent loads away,
+// the table rows one each, and after the scan nothing but arithmetic and one store is left.
+struct WarpPrologue {
+    uint64_t name_digest;     // this lane's share of the name terms of the hash
+    uint32_t nlen;
+    uint32_t cls;             // tool class; bit 31 set = unknown tool (default branch)
+    uint32_t max_tokens, weight, tool_mask;   // provider row `lane` (weight 0 past n_providers)
+};
+
+__device__ __forceinline__ WarpPrologue warp_prologue(const RouteParams& P, uint32_t noff, uint32_t nlen,
+                                                      uint32_t lane)
 {
     const DevTable* __restrict__ tbl = P.table;
     const uint8_t* __restrict__ nm = P.names + noff;
-
-    // c0 / c1: this lane's name bytes `lane` and `lane + 32`, fetched by the caller before the
-    // scan so that their HBM latency hides behind the payload's; longer names read on here
-    if (lane < nlen)       digest += name_term(lane, c0);
-    if (lane + 32u < nlen) digest += name_term(lane + 32u, c1);
-    for (uint32_t j = lane + 64u; j < nlen; j += 32) digest += name_term(j, __ldg(nm + j));
-    // tool switch (mock.go:32-64): whole-name byte equality, first match wins
-    uint32_t cls = __ldg(&tbl->t.default_class);
-    uint32_t unknown = 1;
+    WarpPrologue w;
+    w.nlen = nlen;
+    // independent table loads first, so they are in flight together with the name bytes
     const uint32_t nt = __ldg(&tbl->t.n_tools);
-    for (uint32_t t = 0; t < nt; ++t) {
-        const uint32_t tl = __ldg(&tbl->t.tools[t].name_len);
-        if (tl != nlen) continue;                                     // warp-uniform
+    const uint32_t np = __ldg(&tbl->t.n_providers);
+    uint32_t cls = __ldg(&tbl->t.default_class);
+    uint4 row = make_uint4(0u, 0u, 0u, 0u);
+    if (lane < np) row = __ldg(reinterpret_cast<const uint4*>(&tbl->t.providers[lane]));
+    const uint32_t my_tool_len = lane < nt ? __ldg(&tbl->t.tools[lane].name_len) : 0xFFFFFFFFu;
+    const uint32_t c0 = lane < nlen ? (uint32_t)__ldg(nm + lane) : 0u;
+    const uint32_t c1 = lane + 32u < nlen ? (uint32_t)__ldg(nm + lane + 32u) : 0u;
+    w.max_tokens = row.x; w.weight = row.y; w.tool_mask = row.z;
+
+    uint64_t d = 0;
+    if (lane < nlen)       d += name_term(lane, c0);
+    if (lane + 32u < nlen) d += name_term(lane + 32u, c1);
+    for (uint32_t j = lane + 64u; j < nlen; j += 32) d += name_term(j, __ldg(nm + j));
+    w.name_digest = d;
+
+    // tool switch (mock.go:32-64): whole-name byte equality, first match wins.  Lane t holds
+    // entry t's length; candidates are the entries of the request's length, in table order.
+    uint32_t unknown = 0x80000000u;
+    uint32_t cand = __ballot_sync(kFull, my_tool_len == nlen);
+    while (cand != 0u) {
+        const uint32_t t = (uint32_t)__ffs((int)cand) - 1u;
+        cand &= cand - 1u;
         bool ok = true;
-        if (lane < tl)       ok = (__ldg(&tbl->t.tools[t].name[lane]) == c0);
-        if (lane + 32u < tl) ok = ok && (__ldg(&tbl->t.tools[t].name[lane + 32u]) == c1);
-        if (__all_sync(kFull, ok)) { cls = __ldg(&tbl->t.tools[t].class_id); unknown = 0; break; }
+        if (lane < nlen)       ok = (__ldg(&tbl->t.tools[t].name[lane]) == c0);
+        if (lane + 32u < nlen) ok = ok && (__ldg(&tbl->t.tools[t].name[lane + 32u]) == c1);
+        if (__all_sync(kFull, ok)) { cls = __ldg(&tbl->t.tools[t].class_id); unknown = 0u; break; }
     }
-    const uint64_t total = warp_sum64(digest);
+    w.cls = cls | unknown;
+    return w;
+}
+
+__device__ __forceinline__ void finalize_warp(const RouteParams& P, uint32_t req, uint32_t len,
+                                              uint64_t digest, uint32_t tok_lane, uint32_t lane,
+                                              const WarpPrologue& w)
+{
+    const uint64_t total = warp_sum64(digest + w.name_digest);
     const uint32_t tok = __reduce_add_sync(kFull, tok_lane);
-    const uint64_t h = route_hash_final(total, len, nlen);
+    const uint64_t h = route_hash_final(total, len, w.nlen);
+    const uint32_t cls = w.cls & 0xFFu;
+    const uint32_t unknown = w.cls >> 31;
 
     // provider: lane p holds provider p's eligible weight; inclusive prefix sum over the warp
-    const uint32_t np = __ldg(&tbl->t.n_providers);
-    uint32_t cum = 0;
-    if (lane < np) {
-        const uint4 row = __ldg(reinterpret_cast<const uint4*>(&tbl->t.providers[lane]));
-        const bool elig = row.y != 0u && ((row.z >> cls) & 1u) != 0u && tok <= row.x;
-        cum = elig ? row.y : 0u;
-    }
+    const bool elig = w.weight != 0u && ((w.tool_mask >> cls) & 1u) != 0u && tok <= w.max_tokens;
+    uint32_t cum = elig ? w.weight : 0u;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const uint32_t up = __shfl_up_sync(kFull, cum, d);
@@ -299,17 +327,18 @@ __global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : PK_MIN_CTAS_
             const uint32_t req = base_req + i;
             const uint32_t len = __ldg(P.pay_len + req);
             const uint64_t off = __ldg(P.pay_off + req);
-            // the name is needed only after the scan, but its bytes are two dependent loads away
-            // (offset, then bytes): start them now, next to the payload's
             const uint32_t noff = __ldg(P.name_off + req);
             const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
-            const uint32_t c0 = lane < nlen ? (uint32_t)__ldg(P.names + noff + lane) : 0u;
-            const uint32_t c1 = lane + 32u < nlen ? (uint32_t)__ldg(P.names + noff + lane + 32u) : 0u;
+            // pull the head of the payload towards L2, then do all payload-independent work
+            // (name bytes, tool switch, provider row) while that HBM fetch is under way
+            if (lane < 16u && lane * 128u < len)
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(P.payload + off + lane * 128u));
+            const WarpPrologue w = warp_prologue(P, noff, nlen, lane);
             uint64_t digest;
             uint32_t tok;
             scan_segment(P.payload + off, len, 0u, lane, P.one, digest, tok);
             if (len > kSegBytes) fold_long_segment(P, req, len, digest, tok, lane);
-            else                 finalize_warp(P, req, len, digest, tok, lane, noff, nlen, c0, c1);
+            else                 finalize_warp(P, req, len, digest, tok, lane, w);
         }
         return;
     }
