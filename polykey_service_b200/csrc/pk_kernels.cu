@@ -30,9 +30,9 @@
 #include "pk_spec.cuh"
 
 // Build-time tuning knobs (python -m polykey_service_b200.build passes the chosen values).
-#ifndef PK_PIPE
-#define PK_PIPE 0        // 1: the main loop keeps a second group of loads in flight (register double buffer)
-#endif
+#ifndef PK_TMA
+#define PK_TMA 0         // 1: segments >= 1 of long requests are staged through shared memory with
+#endif                   //    cp.async.bulk + mbarrier (a 4-stage, 2 KiB ring per warp) instead of LDG.128
 #ifndef PK_MIN_CTAS
 #define PK_MIN_CTAS 5    // __launch_bounds__ minimum resident CTAs per SM, full-warp kernels (G == 32)
 #endif
@@ -71,9 +71,42 @@ __device__ __forceinline__ uint64_t warp_sum64(uint64_t v)
 // Scan one 16 KiB segment of one payload with a full warp.  pay points at the payload's first
 // byte (16-byte aligned).  Returns this lane's stripe digest (0 if it saw no block) and its
 // token count.
+// A warp's private staging ring for the cp.async.bulk variant: kTmaStages chunks of 2 KiB (one
+// chunk = four warp-steps) and one mbarrier per chunk.
+#ifndef PK_TMA_STAGES
+#define PK_TMA_STAGES 4
+#endif
+#ifndef PK_TMA_MIN_CTAS
+#define PK_TMA_MIN_CTAS 3
+#endif
+constexpr int      kTmaStages = PK_TMA_STAGES;
+constexpr uint32_t kTmaChunk  = 32u * kUnroll * kBlockBytes;       // 2 KiB
+struct TmaRing { uint8_t* stage; uint64_t* bar; };
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void tma_issue(const TmaRing& r, uint32_t s, const uint8_t* src)
+{
+    const uint32_t bar = smem_u32(r.bar + s), dst = smem_u32(r.stage + s * kTmaChunk);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(kTmaChunk) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst), "l"(src), "r"(kTmaChunk), "r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tma_wait(const TmaRing& r, uint32_t s, uint32_t parity)
+{
+    const uint32_t bar = smem_u32(r.bar + s);
+    uint32_t done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+
+template <bool kTma = false>
 __device__ __forceinline__ void scan_segment(const uint8_t* __restrict__ pay, uint32_t len,
                                              uint32_t seg, uint32_t lane, uint32_t one,
-                                             uint64_t& digest, uint32_t& tok)
+                                             uint64_t& digest, uint32_t& tok, TmaRing ring = TmaRing{nullptr, nullptr})
 {
     const uint32_t nblk   = (len >> 4) + ((len & 15u) ? 1u : 0u);
     const uint32_t first  = seg * kSegBlocks;
@@ -100,27 +133,33 @@ __device__ __forceinline__ void scan_segment(const uint8_t* __restrict__ pay, ui
             scan_block(w, one, tok128);
         }
     };
-#if PK_PIPE
-    {   // register double buffer: the next group's loads are issued before this group is consumed
-        uint4 xa[kUnroll], xb[kUnroll];
-        uint32_t g = 0;
-        if (ngroups > 0) load_group(xa, 0);
-        while (g < ngroups) {
-            if (g + 1 < ngroups) load_group(xb, g + 1);
-            consume_group(xa);
-            if (++g >= ngroups) break;
-            if (g + 1 < ngroups) load_group(xa, g + 1);
-            consume_group(xb);
-            ++g;
+    if (kTma) {
+        // chunks of 2 KiB land in the warp's ring by bulk async copy; lane 0 keeps kTmaStages of
+        // them in flight, every lane then reads its 16-byte block of each step with LDS.128
+        const uint8_t* src = pay + (size_t)first * kBlockBytes;
+        if (lane == 0)
+            for (uint32_t c = 0; c < ngroups && c < (uint32_t)kTmaStages; ++c) tma_issue(ring, c, src + (size_t)c * kTmaChunk);
+        for (uint32_t c = 0; c < ngroups; ++c) {
+            const uint32_t s = c % kTmaStages;
+            tma_wait(ring, s, (c / kTmaStages) & 1u);
+            uint4 x[kUnroll];
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u)
+                x[u] = *reinterpret_cast<const uint4*>(ring.stage + s * kTmaChunk + u * 512 + lane * 16);
+            consume_group(x);
+            __syncwarp();                                   // every lane has read stage s
+            if (lane == 0 && c + kTmaStages < ngroups) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic reads before async write
+                tma_issue(ring, s, src + (size_t)(c + kTmaStages) * kTmaChunk);
+            }
+        }
+    } else {
+        for (uint32_t g = 0; g < ngroups; ++g) {
+            uint4 x[kUnroll];
+            load_group(x, g);
+            consume_group(x);
         }
     }
-#else
-    for (uint32_t g = 0; g < ngroups; ++g) {
-        uint4 x[kUnroll];
-        load_group(x, g);
-        consume_group(x);
-    }
-#endif
     b0 = ngroups * (32u * kUnroll);
     // remainder: ragged steps, the payload's last (partial) block
     for (; b0 < nb; b0 += 32u * kUnroll) {
@@ -440,6 +479,37 @@ __global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : PK_MIN_CTAS_
     }
 }
 
+#if PK_TMA
+// Segments >= 1 of long requests, one warp per (request, segment), the bytes staged through a
+// per-warp shared-memory ring by cp.async.bulk (SASS: UBLKCP) and consumed with LDS.128.
+constexpr size_t kTmaSmemBytes = (size_t)kWarpsPerCta * kTmaStages * kTmaChunk + (size_t)kWarpsPerCta * kTmaStages * 8;
+
+__global__ void __launch_bounds__(kThreads, PK_TMA_MIN_CTAS) segment_kernel_tma(const RouteParams P)
+{
+    extern __shared__ __align__(128) uint8_t tma_smem[];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t wid  = threadIdx.x >> 5;
+    TmaRing ring;
+    ring.stage = tma_smem + (size_t)wid * kTmaStages * kTmaChunk;
+    ring.bar   = reinterpret_cast<uint64_t*>(tma_smem + (size_t)kWarpsPerCta * kTmaStages * kTmaChunk) + wid * kTmaStages;
+    if (lane == 0) {
+        for (int s = 0; s < kTmaStages; ++s)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_u32(ring.bar + s)) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+    const uint32_t task = blockIdx.x * kWarpsPerCta + wid;
+    if (task >= P.n_extra) return;
+    const uint2 e = __ldg(P.extra + task);
+    const uint32_t len = __ldg(P.pay_len + e.x);
+    uint64_t digest;
+    uint32_t tok;
+    scan_segment<true>(P.payload + __ldg(P.pay_off + e.x), len, e.y, lane, P.one, digest, tok, ring);
+    fold_long_segment(P, e.x, len, digest, tok, lane);
+}
+#endif
+
 uint32_t pow2_floor(uint32_t x)
 {
     uint32_t p = 1;
@@ -464,6 +534,10 @@ cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStrea
     R = R < r_min ? r_min : R > r_max ? r_max : R;
     p.reqs_per_cta = R;
     p.one = 1u;
+#if PK_TMA
+    const uint32_t n_extra_tma = p.n_extra;
+    p.n_extra = 0;                                  // the main kernel scans first segments only
+#endif
     const uint32_t ctas = (p.n + R - 1u) / R + (p.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
     // latency mode while one request per warp already fills the machine's resident CTA slots
     static const char* const m_env = std::getenv("PK_LATENCY_MODE");     // tuning aid: 0 / 1 forces
@@ -477,6 +551,14 @@ cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStrea
         else            route_kernel<32, false><<<ctas, kThreads, 0, stream>>>(p);
         break;
     }
+#if PK_TMA
+    if (n_extra_tma != 0) {
+        static const cudaError_t attr = cudaFuncSetAttribute(segment_kernel_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTmaSmemBytes);
+        if (attr != cudaSuccess) return attr;
+        p.n_extra = n_extra_tma;
+        segment_kernel_tma<<<(n_extra_tma + kWarpsPerCta - 1u) / kWarpsPerCta, kThreads, kTmaSmemBytes, stream>>>(p);
+    }
+#endif
     return cudaGetLastError();
 }
 
