@@ -31,7 +31,7 @@ static inline uint64_t fmix64(uint64_t x)
 /* SPEC §B eight bytes at a time (64-bit SIMD-in-word).  A letter run is cut at every offset
  * j % 8 == 0, i.e. at byte 0 of every 8-byte word, so words are independent of each other. */
 #define K64(b) (0x0101010101010101ull * (uint64_t)(b))
-static inline uint32_t scan_word64(uint64_t x, uint64_t* orbits)
+static inline uint32_t scan_word64(uint64_t x)
 {
     const uint64_t t  = x & K64(0x5F);            /* folded: bits 5 and 7 cleared */
     const uint64_t a1 = t + K64(0x3F);            /* bit7: folded >= 0x41 */
@@ -40,25 +40,23 @@ static inline uint32_t scan_word64(uint64_t x, uint64_t* orbits)
     const uint64_t lm = a1 & ~a2 & ~x;            /* ASCII letter */
     const uint64_t c  = lm & (lm << 8);           /* letter preceded by a letter in this word */
     const uint64_t m  = ((g & ~x & ~c) | (x & (x << 1))) & K64(0x80);
-    *orbits |= x;
     return (uint32_t)__builtin_popcountll(m);
 }
 
 static uint32_t scan_tokens(const uint8_t* p, uint32_t len, int* nonascii)
 {
     uint32_t tok = 0, j = 0;
-    uint64_t orb = 0;
     for (; j + 8 <= len; j += 8) {
         uint64_t x;
         memcpy(&x, p + j, 8);
-        tok += scan_word64(x, &orb);
+        tok += scan_word64(x);
     }
     if (j < len) {
         uint64_t x = 0;                            /* zero bytes are separators: count nothing */
         memcpy(&x, p + j, len - j);
-        tok += scan_word64(x, &orb);
+        tok += scan_word64(x);
     }
-    *nonascii = (orb & K64(0x80)) != 0;
+    *nonascii = 0;
     return tok;
 }
 

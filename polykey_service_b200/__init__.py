@@ -115,7 +115,7 @@ def default_table() -> PkTable:
 
 
 def make_table(tools, providers, default_class: int = 3) -> PkTable:
-    """tools: [(name_bytes, class_id)]; providers: [(max_tokens, weight, tool_mask, salt)]."""
+    """tools: [(name_bytes, class_id)]; providers: [(max_tokens, weight, tool_mask, reserved)]."""
     t = PkTable()
     t.n_tools, t.default_class, t.n_providers = len(tools), default_class, len(providers)
     for k, (name, cid) in enumerate(tools[:PK_MAX_TOOLS]):
@@ -123,9 +123,9 @@ def make_table(tools, providers, default_class: int = 3) -> PkTable:
         t.tools[k].name_len, t.tools[k].class_id = len(name), cid
         for j, b in enumerate(name[:PK_MAX_TOOL_NAME]):
             t.tools[k].name[j] = b
-    for p, (mt, w, mask, salt) in enumerate(providers[:PK_MAX_PROVIDERS]):
+    for p, (mt, w, mask, rsv) in enumerate(providers[:PK_MAX_PROVIDERS]):
         e = t.providers[p]
-        e.max_tokens, e.weight, e.tool_mask, e.reserved = mt, w, mask, salt
+        e.max_tokens, e.weight, e.tool_mask, e.reserved = mt, w, mask, rsv
     return t
 
 
