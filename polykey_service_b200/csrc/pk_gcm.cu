@@ -5,8 +5,8 @@
 // for every message (cipher.go:35-43 inside the loops at :116-122 and :133-139).  Here the key
 // schedule, the T-table and the GHASH table are built once per key on the host; one GPU thread
 // then seals or opens one message (messages here are secrets: tens of bytes to a few KB), with
-// the T-table and the key context staged in shared memory.  Integer/LDS-bound work — no tensor
-// cores, and not HBM-bound: ~60 instructions per byte.
+// the key's tables staged in shared memory (Te0 replicated per bank).  Integer/LDS-bound work —
+// no tensor cores, and not HBM-bound.
 #include <cuda_runtime.h>
 
 #include <cstring>
@@ -18,7 +18,7 @@
 namespace {
 
 using pkgcm::KeyContext;
-constexpr int kThreads = 128;
+constexpr int kThreads = 256;          // largest block; small batches use narrower blocks (see run())
 
 // mode 0: seal   in = plaintext arena,  out = sealed arena (nonce || ct || tag per message)
 // mode 1: open   in = sealed arena,     out = plaintext arena; status[i] = 0 ok / 1 auth / 2 short
@@ -28,13 +28,22 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
                                                        uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
                                                        uint32_t* __restrict__ status, uint32_t n, int mode)
 {
-    __shared__ KeyContext kc;
-    static_assert(sizeof(KeyContext) % 16 == 0, "KeyContext is staged as uint4");
-    for (uint32_t i = threadIdx.x; i < sizeof(KeyContext) / 16; i += kThreads)
-        reinterpret_cast<uint4*>(&kc)[i] = __ldg(reinterpret_cast<const uint4*>(kc_g) + i);
+    // shared memory: the key's round keys and GHASH tables (4.9 KB) and Te0 replicated once per
+    // bank (32 KB: entry x of lane l at word 32·x + l), so the AES lookups of a warp never collide
+    __shared__ pkgcm::GcmTables kc;
+    __shared__ uint32_t te_rep[256 * 32];
+    for (uint32_t i = threadIdx.x; i < sizeof(pkgcm::GcmTables) / 16; i += blockDim.x)
+        reinterpret_cast<uint4*>(&kc)[i] = __ldg(reinterpret_cast<const uint4*>(&kc_g->g) + i);
+    for (uint32_t x = threadIdx.x; x < 256; x += blockDim.x) {
+        const uint32_t t = __ldg(&kc_g->te[0][x]);
+        const uint4 t4 = make_uint4(t, t, t, t);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) reinterpret_cast<uint4*>(te_rep + x * 32)[q] = t4;
+    }
     __syncthreads();
+    const pkgcm::TeReplicated te{te_rep, threadIdx.x & 31u};
 
-    const uint32_t i = blockIdx.x * kThreads + threadIdx.x;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint8_t* src = in + in_off[i];
     uint8_t* dst = out + out_off[i];
@@ -43,7 +52,7 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
     if (mode == 0) {
         const uint8_t* nonce = nonces + (size_t)i * pkgcm::kNonceBytes;
         for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];           // cipher.go:51-52
-        pkgcm::gcm_crypt_message(&kc, kc.te0, nonce, src, dst + pkgcm::kNonceBytes, len, false, tag);
+        pkgcm::gcm_crypt_message(&kc, te, nonce, src, dst + pkgcm::kNonceBytes, len, false, tag);
         for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) dst[pkgcm::kNonceBytes + len + b] = tag[b];
     } else {
         if (len < pkgcm::kOverhead) {                     // shorter than nonce + tag: cipher.go:69-71 / Open fails
@@ -51,7 +60,7 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
             return;
         }
         const uint32_t clen = len - pkgcm::kOverhead;
-        pkgcm::gcm_crypt_message(&kc, kc.te0, src, src + pkgcm::kNonceBytes, dst, clen, true, tag);
+        pkgcm::gcm_crypt_message(&kc, te, src, src + pkgcm::kNonceBytes, dst, clen, true, tag);
         uint32_t diff = 0;
         for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) diff |= (uint32_t)(tag[b] ^ src[pkgcm::kNonceBytes + clen + b]);
         if (diff != 0) {                                  // authentication failed: release no plaintext
@@ -119,7 +128,9 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
     PKG_CUDA(h, cudaMemcpyAsync(h->d_len, in_len, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     if (mode == 0) PKG_CUDA(h, cudaMemcpyAsync(h->d_nonce, nonces, (size_t)n * pkgcm::kNonceBytes, cudaMemcpyHostToDevice, st));
     PKG_CUDA(h, cudaEventRecord(h->ev0, st));
-    gcm_kernel<<<(n + kThreads - 1) / kThreads, kThreads, 0, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
+    // one thread per message: spread a small batch over more SMs with narrower blocks
+    const uint32_t threads = n >= 148u * 2u * kThreads ? kThreads : n >= 148u * 64u ? 64u : 32u;
+    gcm_kernel<<<(n + threads - 1) / threads, threads, 0, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
                                                                    h->d_out, h->d_out_off, h->d_status, n, mode);
     PKG_CUDA(h, cudaGetLastError());
     PKG_CUDA(h, cudaEventRecord(h->ev1, st));

@@ -14,7 +14,7 @@ extern "C" void gcmh_seal(const uint8_t* key, const uint8_t* nonce, const uint8_
     make_key_context(key, kc);
     std::memcpy(out, nonce, 12);
     uint8_t tag[16];
-    gcm_crypt_message(&kc, kc.te0, nonce, pt, out + 12, len, false, tag);
+    gcm_crypt_message(&kc.g, TeTables{kc.te}, nonce, pt, out + 12, len, false, tag);
     std::memcpy(out + 12 + len, tag, 16);
 }
 
@@ -26,7 +26,7 @@ extern "C" int gcmh_open(const uint8_t* key, const uint8_t* sealed, uint32_t len
     KeyContext kc;
     make_key_context(key, kc);
     uint8_t tag[16];
-    gcm_crypt_message(&kc, kc.te0, sealed, sealed + 12, pt, len - 28, true, tag);
+    gcm_crypt_message(&kc.g, TeTables{kc.te}, sealed, sealed + 12, pt, len - 28, true, tag);
     return std::memcmp(tag, sealed + len - 16, 16) == 0 ? 0 : 1;
 }
 
@@ -35,7 +35,7 @@ extern "C" void gcmh_encrypt_block(const uint8_t* key, const uint8_t in[16], uin
     KeyContext kc;
     make_key_context(key, kc);
     uint32_t s[4] = {load_be32(in), load_be32(in + 4), load_be32(in + 8), load_be32(in + 12)};
-    aes256_encrypt_block(kc.te0, kc.rk, s);
+    aes256_encrypt_block(TeTables{kc.te}, kc.g.rk, s);
     for (int j = 0; j < 4; ++j) { out[4*j] = s[j] >> 24; out[4*j+1] = s[j] >> 16; out[4*j+2] = s[j] >> 8; out[4*j+3] = s[j]; }
 }
 
@@ -49,8 +49,8 @@ extern "C" int gcmh_check_ghash(const uint8_t* key, uint64_t seed, int trials)
         seed = seed * 6364136223846793005ull + 1442695040888963407ull; uint64_t a = seed;
         seed = seed * 6364136223846793005ull + 1442695040888963407ull; uint64_t b = seed;
         uint64_t xh = a, xl = b, yh = a, yl = b;
-        ghash_mul(kc.hh, kc.hl, xh, xl);
-        ghash_mul_bitwise(kc.hh[8], kc.hl[8], yh, yl);
+        ghash_mul(&kc.g, xh, xl);
+        ghash_mul_bitwise(kc.g.hh[0x80], kc.g.hl[0x80], yh, yl);
         if (xh != yh || xl != yl) ++bad;
     }
     return bad;
