@@ -70,6 +70,12 @@ PK_GCM_API int  pk_gcm_open_batch(pk_gcm* h, const uint8_t* sealed, const uint64
                                   const uint32_t* sealed_len, uint32_t n, uint8_t* plain,
                                   const uint64_t* plain_off, uint32_t* status);
 
+/* Page-locked host memory for the arenas (plain, sealed, offsets, nonces): copies to and from
+ * pinned memory run at PCIe rate; pageable memory is staged by the driver at about a third of it.
+ * Any host pointer is accepted by the calls above; these are the fast ones.  NULL on failure.     */
+PK_GCM_API void* pk_gcm_host_alloc(pk_gcm* h, size_t bytes);
+PK_GCM_API void  pk_gcm_host_free(pk_gcm* h, void* p);
+
 PK_GCM_API const char* pk_gcm_strerror(int status);
 PK_GCM_API uint64_t    pk_gcm_launch_count(const pk_gcm* h);
 /* Device time of the kernel of the last seal/open call (CUDA events on its stream), ms; < 0 if none. */

@@ -4,11 +4,13 @@
 // the reference walks the batch sequentially and rebuilds the AES key schedule and the GCM state
 // for every message (cipher.go:35-43 inside the loops at :116-122 and :133-139).  Here the key
 // schedule, the T-table and the GHASH table are built once per key on the host; one GPU thread
-// then seals or opens one message (messages here are secrets: tens of bytes to a few KB), with
-// the key's tables staged in shared memory (Te0 replicated per bank).  Integer/LDS-bound work —
+// then seals or opens one message (messages here are secrets: tens of bytes to a few KB; the
+// longer ones get a warp each, gcm_long_kernel), with
+// the key's tables staged in shared memory (Te0 and Te2 replicated per bank).  Integer/LDS-bound work —
 // no tensor cores, and not HBM-bound.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -20,20 +22,27 @@ namespace {
 using pkgcm::KeyContext;
 constexpr int kThreads = 256;          // largest block; small batches use narrower blocks (see run())
 
-// mode 0: seal   in = plaintext arena,  out = sealed arena (nonce || ct || tag per message)
-// mode 1: open   in = sealed arena,     out = plaintext arena; status[i] = 0 ok / 1 auth / 2 short
-__global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restrict__ kc_g,
-                                                       const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
-                                                       const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
-                                                       uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
-                                                       uint32_t* __restrict__ status, uint32_t n, int mode)
+// Shared memory.  gcm_kernel (one thread per message; latency-bound, wants occupancy): static,
+// 41 KB -> 5 CTAs of 256 threads per SM
+//   the key's round keys and GHASH tables (pkgcm::GcmTables, 8.8 KB) and Te0 replicated once per
+//   bank (32 KB: entry x of lane l at word 32·x + l), so the AES lookups of a warp never collide.
+// gcm_long_kernel (one warp per message; ALU-pipe-bound, wants fewer instructions): dynamic,
+// 72.5 KB -> 3 CTAs per SM
+//   [0, 64 KB)   Te0 | Te2 replicated per bank, pkgcm::TeDual's layout
+//   then         pkgcm::GcmTables
+//   then         the round keys rotated left by 8 (TeDual::rkr)
+constexpr uint32_t kTabBytes = 256u * 256u;
+constexpr uint32_t kSmemBytes = kTabBytes + (uint32_t)sizeof(pkgcm::GcmTables) + 256u;
+
+__device__ __forceinline__ void stage_key(pkgcm::GcmTables* kc, const KeyContext* __restrict__ kc_g)
 {
-    // shared memory: the key's round keys and GHASH tables (4.9 KB) and Te0 replicated once per
-    // bank (32 KB: entry x of lane l at word 32·x + l), so the AES lookups of a warp never collide
-    __shared__ pkgcm::GcmTables kc;
-    __shared__ uint32_t te_rep[256 * 32];
     for (uint32_t i = threadIdx.x; i < sizeof(pkgcm::GcmTables) / 16; i += blockDim.x)
-        reinterpret_cast<uint4*>(&kc)[i] = __ldg(reinterpret_cast<const uint4*>(&kc_g->g) + i);
+        reinterpret_cast<uint4*>(kc)[i] = __ldg(reinterpret_cast<const uint4*>(&kc_g->g) + i);
+}
+
+__device__ __forceinline__ void stage_single(pkgcm::GcmTables& kc, uint32_t* te_rep, const KeyContext* __restrict__ kc_g)
+{
+    stage_key(&kc, kc_g);
     for (uint32_t x = threadIdx.x; x < 256; x += blockDim.x) {
         const uint32_t t = __ldg(&kc_g->te[0][x]);
         const uint4 t4 = make_uint4(t, t, t, t);
@@ -41,18 +50,58 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
         for (int q = 0; q < 8; ++q) reinterpret_cast<uint4*>(te_rep + x * 32)[q] = t4;
     }
     __syncthreads();
+}
+
+struct Staged {
+    const pkgcm::GcmTables* kc;
+    pkgcm::TeDual te;
+};
+
+__device__ __forceinline__ Staged stage_dual(uint8_t* smem, const KeyContext* __restrict__ kc_g)
+{
+    pkgcm::GcmTables* kc = reinterpret_cast<pkgcm::GcmTables*>(smem + kTabBytes);
+    uint32_t* rkr = reinterpret_cast<uint32_t*>(smem + kTabBytes + sizeof(pkgcm::GcmTables));
+    stage_key(kc, kc_g);
+    for (uint32_t i = threadIdx.x; i < 60; i += blockDim.x) {
+        const uint32_t k = __ldg(&kc_g->g.rk[i]);
+        rkr[i] = (k << 8) | (k >> 24);
+    }
+    for (uint32_t x = threadIdx.x; x < 512; x += blockDim.x) {       // x = 2·entry + table
+        const uint32_t t = __ldg(&kc_g->te[(x & 1u) * 2u][x >> 1]);
+        const uint4 t4 = make_uint4(t, t, t, t);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + x * 128u)[q] = t4;
+    }
+    __syncthreads();
+    return Staged{kc, pkgcm::TeDual{smem, rkr, (threadIdx.x & 31u) * 4u}};
+}
+
+// mode 0: seal   in = plaintext arena,  out = sealed arena (nonce || ct || tag per message)
+// mode 1: open   in = sealed arena,     out = plaintext arena; status[i] = 0 ok / 1 auth / 2 short
+__global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restrict__ kc_g,
+                                                       const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
+                                                       const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
+                                                       uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
+                                                       uint32_t* __restrict__ status, uint32_t n, int mode,
+                                                       uint32_t long_bytes)
+{
+    __shared__ pkgcm::GcmTables kc_s;
+    __shared__ uint32_t te_rep[256 * 32];
+    stage_single(kc_s, te_rep, kc_g);
+    const pkgcm::GcmTables* kc = &kc_s;
     const pkgcm::TeReplicated te{te_rep, threadIdx.x & 31u};
 
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const uint32_t len = in_len[i];
+    if (len >= long_bytes) return;                        // gcm_long_kernel's message
     const uint8_t* src = in + in_off[i];
     uint8_t* dst = out + out_off[i];
-    const uint32_t len = in_len[i];
     uint8_t tag[16];
     if (mode == 0) {
         const uint8_t* nonce = nonces + (size_t)i * pkgcm::kNonceBytes;
         for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];           // cipher.go:51-52
-        pkgcm::gcm_crypt_message(&kc, te, nonce, src, dst + pkgcm::kNonceBytes, len, false, tag);
+        pkgcm::gcm_crypt_message(kc, te, nonce, src, dst + pkgcm::kNonceBytes, len, false, tag);
         for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) dst[pkgcm::kNonceBytes + len + b] = tag[b];
     } else {
         if (len < pkgcm::kOverhead) {                     // shorter than nonce + tag: cipher.go:69-71 / Open fails
@@ -60,7 +109,7 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
             return;
         }
         const uint32_t clen = len - pkgcm::kOverhead;
-        pkgcm::gcm_crypt_message(&kc, te, src, src + pkgcm::kNonceBytes, dst, clen, true, tag);
+        pkgcm::gcm_crypt_message(kc, te, src, src + pkgcm::kNonceBytes, dst, clen, true, tag);
         uint32_t diff = 0;
         for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) diff |= (uint32_t)(tag[b] ^ src[pkgcm::kNonceBytes + clen + b]);
         if (diff != 0) {                                  // authentication failed: release no plaintext
@@ -68,6 +117,61 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
             status[i] = 1u;
         } else {
             status[i] = 0u;
+        }
+    }
+}
+
+// One WARP per long message (those gcm_kernel skipped; long_idx lists them).  Lane l takes the
+// 16-byte blocks l, l+32, ... — a warp reads and writes 512 consecutive bytes per step — and the
+// lanes' GHASH terms (pkgcm::gcm_lane_pass) XOR together through shuffles.
+__global__ void __launch_bounds__(kThreads) gcm_long_kernel(const KeyContext* __restrict__ kc_g,
+                                                            const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
+                                                            const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
+                                                            uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
+                                                            uint32_t* __restrict__ status, const uint32_t* __restrict__ long_idx,
+                                                            uint32_t n_long, int mode)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    const Staged st = stage_dual(smem, kc_g);
+    const pkgcm::GcmTables* kc = st.kc;
+    const pkgcm::TeDual& te = st.te;
+    const uint32_t lane = threadIdx.x & 31u;
+
+    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n_long) return;                              // whole warps leave together
+    const uint32_t i = long_idx[w];
+    const uint8_t* src = in + in_off[i];
+    uint8_t* dst = out + out_off[i];
+    const uint32_t len = in_len[i];                       // >= long_bytes > kOverhead
+    const uint8_t* nonce = mode == 0 ? nonces + (size_t)i * pkgcm::kNonceBytes : src;
+    const uint32_t clen = mode == 0 ? len : len - pkgcm::kOverhead;
+    uint64_t yh, yl;
+    pkgcm::gcm_lane_pass(kc, te, nonce, mode == 0 ? src : src + pkgcm::kNonceBytes,
+                         mode == 0 ? dst + pkgcm::kNonceBytes : dst, clen, mode != 0, lane, yh, yl);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        yh ^= __shfl_xor_sync(0xFFFFFFFFu, yh, d);
+        yl ^= __shfl_xor_sync(0xFFFFFFFFu, yl, d);
+    }
+    uint32_t ok = 1;
+    if (lane == 0) {
+        uint8_t tag[16];
+        pkgcm::gcm_tag(kc, te, nonce, yh, yl, tag);
+        if (mode == 0) {
+            for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];
+            for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) dst[pkgcm::kNonceBytes + len + b] = tag[b];
+        } else {
+            uint32_t diff = 0;
+            for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) diff |= (uint32_t)(tag[b] ^ src[pkgcm::kNonceBytes + clen + b]);
+            ok = diff == 0;
+            status[i] = ok ? 0u : 1u;
+        }
+    }
+    if (mode != 0) {
+        ok = __shfl_sync(0xFFFFFFFFu, ok, 0);
+        if (!ok) {                                        // authentication failed: release no plaintext
+            __syncwarp();
+            for (uint32_t b = lane; b < clen; b += 32u) dst[b] = 0;
         }
     }
 }
@@ -81,7 +185,8 @@ struct pk_gcm {
     KeyContext* d_kc = nullptr;
     uint8_t *d_in = nullptr, *d_out = nullptr, *d_nonce = nullptr;
     uint64_t *d_in_off = nullptr, *d_out_off = nullptr;
-    uint32_t *d_len = nullptr, *d_status = nullptr;
+    uint32_t *d_len = nullptr, *d_status = nullptr, *d_long = nullptr;
+    uint32_t* h_long = nullptr;                 // pinned: indices of the messages the warp kernel takes
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // bracket the kernel of the last call
     int last_cuda = 0;
@@ -100,6 +205,15 @@ namespace {
         }                                                   \
     } while (0)
 
+// Smallest message (bytes, as passed in) the warp-per-message kernel takes for a batch of n.
+// PK_GCM_LONG_BYTES overrides it (tools/bench_gcm.py sweeps it).
+uint32_t long_threshold(uint32_t n)
+{
+    const char* e = std::getenv("PK_GCM_LONG_BYTES");
+    if (e && *e) { const long forced = std::atol(e); return forced < 64 ? 64u : (uint32_t)forced; }
+    return n < 8192u ? 256u : n < 32768u ? 1024u : 2048u;
+}
+
 int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const uint32_t* in_len,
         const uint8_t* nonces, uint32_t n, uint8_t* out, const uint64_t* out_off, uint32_t* status)
 {
@@ -108,8 +222,15 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
     if (!in_off || !in_len || !out_off || !out || (mode == 0 && !nonces) || (mode == 1 && !status)) return PK_GCM_ERR_ARG;
     if (n > h->max_messages) return PK_GCM_ERR_CAPACITY;
     // validate layout: 16-byte aligned, non-overlapping slots in order; compute extents
+    // Messages of long_bytes or more go to the warp-per-message kernel.  It does one extra field
+    // multiplication per lane, so with enough messages to fill the machine one thread per message
+    // is the cheaper form until the message is a few KB; with few messages the warp form is what
+    // keeps the SMs busy.
+    const uint32_t long_bytes = long_threshold(n);
+    uint32_t n_long = 0;
     uint64_t in_end = 0, out_end = 0;
     for (uint32_t i = 0; i < n; ++i) {
+        if (in_len[i] >= long_bytes) h->h_long[n_long++] = i;
         const uint64_t need_out = mode == 0 ? (uint64_t)in_len[i] + pkgcm::kOverhead
                                             : (in_len[i] >= pkgcm::kOverhead ? in_len[i] - pkgcm::kOverhead : 0);
         if (in_off[i] % 16 || out_off[i] % 16) return PK_GCM_ERR_ALIGN;
@@ -127,14 +248,24 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
     PKG_CUDA(h, cudaMemcpyAsync(h->d_out_off, out_off, (size_t)n * 8, cudaMemcpyHostToDevice, st));
     PKG_CUDA(h, cudaMemcpyAsync(h->d_len, in_len, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     if (mode == 0) PKG_CUDA(h, cudaMemcpyAsync(h->d_nonce, nonces, (size_t)n * pkgcm::kNonceBytes, cudaMemcpyHostToDevice, st));
+    if (n_long) PKG_CUDA(h, cudaMemcpyAsync(h->d_long, h->h_long, (size_t)n_long * 4, cudaMemcpyHostToDevice, st));
     PKG_CUDA(h, cudaEventRecord(h->ev0, st));
-    // one thread per message: spread a small batch over more SMs with narrower blocks
-    const uint32_t threads = n >= 148u * 2u * kThreads ? kThreads : n >= 148u * 64u ? 64u : 32u;
-    gcm_kernel<<<(n + threads - 1) / threads, threads, 0, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
-                                                                   h->d_out, h->d_out_off, h->d_status, n, mode);
-    PKG_CUDA(h, cudaGetLastError());
+    if (n_long < n) {
+        // one thread per message: spread a small batch over more SMs with narrower blocks
+        const uint32_t threads = n >= 148u * 2u * kThreads ? kThreads : n >= 148u * 64u ? 64u : 32u;
+        gcm_kernel<<<(n + threads - 1) / threads, threads, 0, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
+                                                                       h->d_out, h->d_out_off, h->d_status, n, mode, long_bytes);
+        PKG_CUDA(h, cudaGetLastError());
+        ++h->launches;
+    }
+    if (n_long) {
+        const uint32_t warps = n_long >= 148u * 2u * 8u ? 8u : n_long >= 148u * 2u ? 2u : 1u;
+        gcm_long_kernel<<<(n_long + warps - 1) / warps, warps * 32u, kSmemBytes, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
+                                                                              h->d_out, h->d_out_off, h->d_status, h->d_long, n_long, mode);
+        PKG_CUDA(h, cudaGetLastError());
+        ++h->launches;
+    }
     PKG_CUDA(h, cudaEventRecord(h->ev1, st));
-    ++h->launches;
     if (out_end) PKG_CUDA(h, cudaMemcpyAsync(out, h->d_out, out_end, cudaMemcpyDeviceToHost, st));
     if (mode == 1) PKG_CUDA(h, cudaMemcpyAsync(status, h->d_status, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     PKG_CUDA(h, cudaStreamSynchronize(st));
@@ -183,6 +314,7 @@ int pk_gcm_init(int device, const uint8_t* key, uint32_t key_len, uint32_t max_m
     pkgcm::make_key_context(key, kc);
     const size_t n = max_messages;
     cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gcm_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
@@ -195,6 +327,8 @@ int pk_gcm_init(int device, const uint8_t* key, uint32_t key_len, uint32_t max_m
     if (e == cudaSuccess) e = cudaMalloc(&h->d_out_off, n * 8);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_len, n * 4);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_status, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_long, n * 4);
+    if (e == cudaSuccess) e = cudaMallocHost(&h->h_long, n * 4);
     std::memset(&kc, 0, sizeof kc);                       // do not leave key material on the stack
     if (e != cudaSuccess) {
         (void)cudaGetLastError();
@@ -213,6 +347,8 @@ void pk_gcm_destroy(pk_gcm* h)
     if (h->d_kc) { cudaMemset(h->d_kc, 0, sizeof(KeyContext)); cudaFree(h->d_kc); }
     void* bufs[] = {h->d_in, h->d_out, h->d_nonce, h->d_in_off, h->d_out_off, h->d_len, h->d_status};
     for (void* b : bufs) if (b) cudaFree(b);
+    if (h->d_long) cudaFree(h->d_long);
+    if (h->h_long) cudaFreeHost(h->h_long);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -230,6 +366,23 @@ int pk_gcm_open_batch(pk_gcm* h, const uint8_t* sealed, const uint64_t* sealed_o
                       uint32_t n, uint8_t* plain, const uint64_t* plain_off, uint32_t* status)
 {
     return run(h, 1, sealed, sealed_off, sealed_len, nullptr, n, plain, plain_off, status);
+}
+
+void* pk_gcm_host_alloc(pk_gcm* h, size_t bytes)
+{
+    if (!h || bytes == 0) return nullptr;
+    void* p = nullptr;
+    if (cudaSetDevice(h->device) != cudaSuccess || cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+        h->last_cuda = (int)cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+void pk_gcm_host_free(pk_gcm* h, void* p)
+{
+    if (!h || !p) return;
+    if (cudaFreeHost(p) != cudaSuccess) h->last_cuda = (int)cudaGetLastError();
 }
 
 uint64_t pk_gcm_launch_count(const pk_gcm* h) { return h ? h->launches : 0; }

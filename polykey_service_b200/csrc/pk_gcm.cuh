@@ -34,13 +34,17 @@ constexpr uint32_t kNonceBytes = 12;      // aesgcm.NonceSize(), cipher.go:45
 constexpr uint32_t kTagBytes   = 16;
 constexpr uint32_t kOverhead   = kNonceBytes + kTagBytes;
 
-// Per-key tables, built by make_key_context() on the host.  GcmTables (4.9 KB) is what a kernel
+// One field element, big-endian halves; 16 bytes so a table lookup is one 128-bit load.
+struct alignas(16) HEntry { uint64_t h, l; };
+
+// Per-key tables, built by make_key_context() on the host.  GcmTables (8.8 KB) is what a kernel
 // keeps in shared memory next to its bank-replicated copy of te[0].
 struct GcmTables {
     uint32_t rk[60];            // AES-256 round keys, big-endian words, 15 × 4
     uint32_t pad[4];
-    uint64_t hh[256], hl[256];  // Shoup table: (hh[b], hl[b]) = H · b(x), H = E_K(0^128); entry 0x80 is H
-    uint16_t r8[256];           // reduction of the byte shifted out at the low end (goes to bits 48..63)
+    HEntry ht[256];             // Shoup table: ht[b] = H · b(x), H = E_K(0^128); entry 0x80 is H
+    HEntry ht32[256];           // the same table for H^32 (the warp-per-message Horner step)
+    HEntry pw[32];              // pw[e-1] = H^e, e = 1..32
 };
 struct KeyContext {
     uint32_t te[4][256];        // T-tables: te[0][x] = (2·S[x], S[x], S[x], 3·S[x]) big-endian; te[k] = te[0] rotated right by 8k
@@ -123,25 +127,195 @@ PKG_HD void aes256_encrypt_block(const Te& te, const uint32_t* __restrict__ rk, 
 #undef PKG_SB
 }
 
+#if defined(__CUDACC__)
+// Device form used by the kernels: Te0 and Te2 (= Te0 rotated by 16) side by side, each replicated
+// per bank — entry x is 256 bytes: 32 lanes × Te0[x], then 32 lanes × Te2[x] (64 KB in all).
+//   * the address of a lookup is ONE byte-permute: (byte k of the state word) << 8 | lane·4,
+//     and Te2 is the same address + 128 (an immediate);
+//   * the two remaining rotations of a column are both by 8 and XOR is linear over rotations, so
+//     column = Te0[a] ^ Te2[c] ^ rotr8(Te0[b] ^ Te2[d] ^ rotl8(rk)) — one rotation, three 3-input
+//     logic ops.  `rkr` holds the round keys rotated left by 8.
+// That is 28 ALU-pipe instructions per round against 56 for the single replicated table
+// (shift + mask + lane-or per index, three rotations per column): the kernels are bound by that pipe.
+struct TeDual {
+    const uint8_t* tab;       // [256][2][32] words
+    const uint32_t* rkr;      // rotl8 of the 60 round-key words
+    uint32_t lane4;           // lane · 4
+    __device__ __forceinline__ uint32_t at(uint32_t word, uint32_t k, uint32_t second) const
+    {
+        const uint32_t off = __byte_perm(word, lane4, 0x5504u | (k << 4));
+        return *reinterpret_cast<const uint32_t*>(tab + off + second * 128u);
+    }
+    // TeTables-style access (last round helper, tag path): byte value -> rotated table word
+    __device__ __forceinline__ uint32_t operator()(int k, uint32_t x) const
+    {
+        const uint32_t t = *reinterpret_cast<const uint32_t*>(tab + (x << 8) + lane4 + ((k & 2) ? 128u : 0u));
+        return (k & 1) ? rotr32(t, 8u) : t;
+    }
+};
+
+__device__ __forceinline__ void aes256_encrypt_block(const TeDual& te, const uint32_t* __restrict__ rk, uint32_t s[4])
+{
+    uint32_t s0 = s[0] ^ rk[0], s1 = s[1] ^ rk[1], s2 = s[2] ^ rk[2], s3 = s[3] ^ rk[3];
+#pragma unroll 1
+    for (int r = 1; r < 14; ++r) {
+        const uint4 kr = *reinterpret_cast<const uint4*>(te.rkr + 4 * r);
+        const uint32_t u0 = te.at(s1, 2, 0) ^ te.at(s3, 0, 1) ^ kr.x;
+        const uint32_t u1 = te.at(s2, 2, 0) ^ te.at(s0, 0, 1) ^ kr.y;
+        const uint32_t u2 = te.at(s3, 2, 0) ^ te.at(s1, 0, 1) ^ kr.z;
+        const uint32_t u3 = te.at(s0, 2, 0) ^ te.at(s2, 0, 1) ^ kr.w;
+        const uint32_t t0 = te.at(s0, 3, 0) ^ te.at(s2, 1, 1) ^ __byte_perm(u0, 0, 0x0321);
+        const uint32_t t1 = te.at(s1, 3, 0) ^ te.at(s3, 1, 1) ^ __byte_perm(u1, 0, 0x0321);
+        const uint32_t t2 = te.at(s2, 3, 0) ^ te.at(s0, 1, 1) ^ __byte_perm(u2, 0, 0x0321);
+        const uint32_t t3 = te.at(s3, 3, 0) ^ te.at(s1, 1, 1) ^ __byte_perm(u3, 0, 0x0321);
+        s0 = t0; s1 = t1; s2 = t2; s3 = t3;
+    }
+    // last round: S[x] sits in bits 16..23 and 8..15 of Te0[x] and in bits 24..31 and 0..7 of Te2[x]
+    const uint4 k = *reinterpret_cast<const uint4*>(rk + 56);
+#define PKG_LAST(a, b, c, d)                                                                       \
+    ((te.at(a, 3, 1) & 0xFF000000u) | (te.at(b, 2, 0) & 0x00FF0000u) | (te.at(c, 1, 0) & 0x0000FF00u) | \
+     (te.at(d, 0, 1) & 0x000000FFu))
+    s[0] = PKG_LAST(s0, s1, s2, s3) ^ k.x;
+    s[1] = PKG_LAST(s1, s2, s3, s0) ^ k.y;
+    s[2] = PKG_LAST(s2, s3, s0, s1) ^ k.z;
+    s[3] = PKG_LAST(s3, s0, s1, s2) ^ k.w;
+#undef PKG_LAST
+}
+#endif  // __CUDACC__
+
 // (xh, xl) <- (xh, xl) · H in GF(2^128) (GCM bit order) with the key's 8-bit tables: walk the 16
 // bytes of X from the last to the first; each step shifts the accumulator right by one byte,
 // folds the byte that fell off back in at the top (r8), and adds H · (next byte of X).
-PKG_HD void ghash_mul(const GcmTables* __restrict__ kc, uint64_t& xh, uint64_t& xl)
+PKG_HD HEntry load_entry(const HEntry* __restrict__ t, uint32_t b)
 {
-    uint32_t b = (uint32_t)xl & 0xFFu;
-    uint64_t zh = kc->hh[b], zl = kc->hl[b];
+#if defined(__CUDA_ARCH__)
+    const uint4 v = *reinterpret_cast<const uint4*>(t + b);
+    HEntry e;
+    e.h = ((uint64_t)v.y << 32) | v.x;
+    e.l = ((uint64_t)v.w << 32) | v.z;
+    return e;
+#else
+    return t[b];
+#endif
+}
+
+// X <- X · V for the element V whose 8-bit Shoup table is `t`: Horner over the 16 bytes of X from
+// the last (highest powers of x) to the first.  Moving the accumulator right by 8 bits drops a
+// byte r off the low end: its bit j (0 = least significant) is the coefficient of x^(135-j) =
+// x^(7-j) · x^128, and x^128 = 1 + x + x^2 + x^7 — 0xE1 at the top — so the byte folds back as the
+// carry-less product r ⊗ 0x1C2 placed at bits 48..63: four shifts, no table.
+PKG_HD void ghash_mul_table(const HEntry* __restrict__ t, uint64_t& xh, uint64_t& xl)
+{
+    HEntry e = load_entry(t, (uint32_t)xl & 0xFFu);
+    uint64_t zh = e.h, zl = e.l;
 #pragma unroll 1
     for (int i = 1; i < 16; ++i) {
         const uint64_t word = i < 8 ? xl : xh;
-        b = (uint32_t)(word >> (8 * (i & 7))) & 0xFFu;
+        e = load_entry(t, (uint32_t)(word >> (8 * (i & 7))) & 0xFFu);
         const uint32_t rem = (uint32_t)zl & 0xFFu;
+        const uint32_t fold = (rem << 1) ^ (rem << 6) ^ (rem << 7) ^ (rem << 8);
         zl = (zh << 56) | (zl >> 8);
-        zh = (zh >> 8) ^ ((uint64_t)kc->r8[rem] << 48);
-        zh ^= kc->hh[b];
-        zl ^= kc->hl[b];
+        zh = (zh >> 8) ^ ((uint64_t)fold << 48) ^ e.h;
+        zl ^= e.l;
     }
     xh = zh;
     xl = zl;
+}
+PKG_HD void ghash_mul(const GcmTables* __restrict__ kc, uint64_t& xh, uint64_t& xl)
+{
+    ghash_mul_table(kc->ht, xh, xl);
+}
+
+// Textbook GF(2^128) multiplication (SP 800-38D Algorithm 1), bit by bit: X <- X · P for an
+// arbitrary P.  Slow (128 steps); used once per lane per long message, and by the unit test.
+PKG_HD void ghash_mul_bitwise(uint64_t ph, uint64_t pl, uint64_t& xh, uint64_t& xl)
+{
+    uint64_t zh = 0, zl = 0, vh = ph, vl = pl;
+#pragma unroll 1
+    for (int i = 0; i < 128; ++i) {
+        const uint64_t bit = i < 64 ? (xh >> (63 - i)) & 1u : (xl >> (127 - i)) & 1u;
+        if (bit) { zh ^= vh; zl ^= vl; }
+        const uint64_t carry = (vl & 1u) ? 0xE100000000000000ull : 0ull;
+        vl = (vh << 63) | (vl >> 1);
+        vh = (vh >> 1) ^ carry;
+    }
+    xh = zh; xl = zl;
+}
+
+// CTR-crypt one 16-byte (or final partial) block at offset `at` and return the CIPHERTEXT block
+// as big-endian words, zero padded.
+template <typename Te>
+PKG_HD void ctr_block(const GcmTables* __restrict__ kc, const Te& te, uint32_t n0, uint32_t n1, uint32_t n2,
+                      const uint8_t* __restrict__ in, uint8_t* __restrict__ out, uint32_t len, uint32_t at,
+                      bool decrypt, uint32_t c[4])
+{
+    uint32_t ks[4] = {n0, n1, n2, 2u + (at >> 4)};
+    aes256_encrypt_block(te, kc->rk, ks);
+    const uint32_t nb = len - at < 16 ? len - at : 16;
+    c[0] = c[1] = c[2] = c[3] = 0;
+    if (nb == 16) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t w = load32(in + at + 4 * j);
+            const uint32_t o = w ^ bswap32(ks[j]);
+            store32(out + at + 4 * j, o);
+            c[j] = bswap32(decrypt ? w : o);
+        }
+    } else {
+        for (uint32_t b = 0; b < nb; ++b) {
+            const uint8_t ib = in[at + b];
+            const uint8_t ob = (uint8_t)(ib ^ (uint8_t)(ks[b >> 2] >> (24 - 8 * (b & 3))));
+            out[at + b] = ob;
+            c[b >> 2] |= (uint32_t)(decrypt ? ib : ob) << (24 - 8 * (b & 3));
+        }
+    }
+}
+
+// Warp-per-message form, one lane's share.  GHASH is X = sum over blocks B_b · H^(m-b), b = 0..m-1,
+// where m = (ciphertext blocks) + 1 and the last block is the lengths block.  Lane l takes blocks
+// l, l+32, ...: Horner with H^32 over its own blocks, then one multiplication by H^(m - last block)
+// — the lanes' results XOR to X.  Returns this lane's term in (yh, yl); (0, 0) if it had no block.
+template <typename Te>
+PKG_HD void gcm_lane_pass(const GcmTables* __restrict__ kc, const Te& te, const uint8_t* __restrict__ nonce,
+                          const uint8_t* __restrict__ in, uint8_t* __restrict__ out, uint32_t len,
+                          bool decrypt, uint32_t lane, uint64_t& yh, uint64_t& yl)
+{
+    const uint32_t n0 = load_be32(nonce), n1 = load_be32(nonce + 4), n2 = load_be32(nonce + 8);
+    const uint32_t nblk = (len + 15u) >> 4;
+    const uint32_t m = nblk + 1u;
+    yh = 0; yl = 0;
+    uint32_t last = 0xFFFFFFFFu;
+    for (uint32_t b = lane; b < m; b += 32u) {
+        if (last != 0xFFFFFFFFu) ghash_mul_table(kc->ht32, yh, yl);
+        if (b < nblk) {
+            uint32_t c[4];
+            ctr_block(kc, te, n0, n1, n2, in, out, len, b << 4, decrypt, c);
+            yh ^= ((uint64_t)c[0] << 32) | c[1];
+            yl ^= ((uint64_t)c[2] << 32) | c[3];
+        } else {
+            yl ^= (uint64_t)len * 8u;              // the lengths block: len(A) = 0 || len(C) in bits
+        }
+        last = b;
+    }
+    if (last != 0xFFFFFFFFu) {
+        const uint32_t e = m - last;               // 1..32
+        ghash_mul_bitwise(kc->pw[e - 1].h, kc->pw[e - 1].l, yh, yl);
+    }
+}
+
+// tag = X ^ E_K(nonce || 1), as 16 bytes
+template <typename Te>
+PKG_HD void gcm_tag(const GcmTables* __restrict__ kc, const Te& te, const uint8_t* __restrict__ nonce,
+                    uint64_t xh, uint64_t xl, uint8_t tag[16])
+{
+    uint32_t j0[4] = {load_be32(nonce), load_be32(nonce + 4), load_be32(nonce + 8), 1u};
+    aes256_encrypt_block(te, kc->rk, j0);
+    const uint32_t t[4] = {(uint32_t)(xh >> 32) ^ j0[0], (uint32_t)xh ^ j0[1], (uint32_t)(xl >> 32) ^ j0[2], (uint32_t)xl ^ j0[3]};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        tag[4 * j] = (uint8_t)(t[j] >> 24); tag[4 * j + 1] = (uint8_t)(t[j] >> 16);
+        tag[4 * j + 2] = (uint8_t)(t[j] >> 8); tag[4 * j + 3] = (uint8_t)t[j];
+    }
 }
 
 // One message: CTR-mode encryption (or decryption) with counter blocks nonce || be32(2, 3, ...) and
@@ -221,6 +395,22 @@ static inline void make_sbox(uint8_t sbox[256])
     }
 }
 
+// 8-bit Shoup table of a field element V: entry b is V · b(x) where the byte's most significant
+// bit is x^0 (GCM's bit order): 0x80 -> V, 0x40 -> V·x, ... 0x01 -> V·x^7; the rest by linearity.
+static inline void make_shoup_table(uint64_t vh, uint64_t vl, HEntry t[256])
+{
+    for (int i = 0; i < 256; ++i) { t[i].h = 0; t[i].l = 0; }
+    t[0x80].h = vh; t[0x80].l = vl;
+    for (int i = 0x40; i > 0; i >>= 1) {
+        const uint64_t carry = (vl & 1u) ? 0xE100000000000000ull : 0ull;     // multiply by x
+        vl = (vh << 63) | (vl >> 1);
+        vh = (vh >> 1) ^ carry;
+        t[i].h = vh; t[i].l = vl;
+    }
+    for (int i = 2; i <= 0x80; i *= 2)
+        for (int j = 1; j < i; ++j) { t[i + j].h = t[i].h ^ t[j].h; t[i + j].l = t[i].l ^ t[j].l; }
+}
+
 // key: exactly 32 bytes (cipher.go:15-19 rejects anything else).
 static inline void make_key_context(const uint8_t key[32], KeyContext& kc)
 {
@@ -247,44 +437,18 @@ static inline void make_key_context(const uint8_t key[32], KeyContext& kc)
         }
         kc.g.rk[i] = kc.g.rk[i - 8] ^ t;
     }
-    // H = E_K(0^128).  Table entry b is H · b(x) where the byte's most significant bit is x^0
-    // (GCM's bit order): 0x80 -> H, 0x40 -> H·x, ... 0x01 -> H·x^7; the rest by linearity.
+    // H = E_K(0^128)
     uint32_t h[4] = {0, 0, 0, 0};
     aes256_encrypt_block(TeTables{kc.te}, kc.g.rk, h);
-    uint64_t vh = ((uint64_t)h[0] << 32) | h[1], vl = ((uint64_t)h[2] << 32) | h[3];
-    for (int i = 0; i < 256; ++i) { kc.g.hh[i] = 0; kc.g.hl[i] = 0; }
-    kc.g.hh[0x80] = vh; kc.g.hl[0x80] = vl;
-    for (int i = 0x40; i > 0; i >>= 1) {
-        const uint64_t carry = (vl & 1u) ? 0xE100000000000000ull : 0ull;     // multiply by x
-        vl = (vh << 63) | (vl >> 1);
-        vh = (vh >> 1) ^ carry;
-        kc.g.hh[i] = vh; kc.g.hl[i] = vl;
+    const uint64_t Hh = ((uint64_t)h[0] << 32) | h[1], Hl = ((uint64_t)h[2] << 32) | h[3];
+    make_shoup_table(Hh, Hl, kc.g.ht);
+    // H^1 .. H^32 (warp-per-message path: Horner step H^32, per-lane closing power H^e)
+    uint64_t ph = Hh, pl = Hl;
+    for (int e = 1; e <= 32; ++e) {
+        kc.g.pw[e - 1].h = ph; kc.g.pw[e - 1].l = pl;
+        ghash_mul_bitwise(Hh, Hl, ph, pl);
     }
-    for (int i = 2; i <= 0x80; i *= 2)
-        for (int j = 1; j < i; ++j) { kc.g.hh[i + j] = kc.g.hh[i] ^ kc.g.hh[j]; kc.g.hl[i + j] = kc.g.hl[i] ^ kc.g.hl[j]; }
-    // byte r falls off the low end when the accumulator moves right by 8 bits: its bit j (0 = least
-    // significant) is the coefficient of x^(135-j) = x^(7-j) · x^128, and x^128 = 1 + x + x^2 + x^7,
-    // i.e. 0xE1 at the top — so bit j contributes 0xE100 >> (7 - j) to the top 16 bits.
-    for (int r = 0; r < 256; ++r) {
-        uint16_t v = 0;
-        for (int j = 0; j < 8; ++j) if (r & (1 << j)) v ^= (uint16_t)(0xE100u >> (7 - j));
-        kc.g.r8[r] = v;
-    }
-}
-
-// Textbook GF(2^128) multiplication (SP 800-38D Algorithm 1), bit by bit — used only to check
-// the table-driven ghash_mul in the unit test.
-static inline void ghash_mul_bitwise(uint64_t hh, uint64_t hl, uint64_t& xh, uint64_t& xl)
-{
-    uint64_t zh = 0, zl = 0, vh = hh, vl = hl;
-    for (int i = 0; i < 128; ++i) {
-        const uint64_t bit = i < 64 ? (xh >> (63 - i)) & 1u : (xl >> (127 - i)) & 1u;
-        if (bit) { zh ^= vh; zl ^= vl; }
-        const uint64_t carry = (vl & 1u) ? 0xE100000000000000ull : 0ull;
-        vl = (vh << 63) | (vl >> 1);
-        vh = (vh >> 1) ^ carry;
-    }
-    xh = zh; xl = zl;
+    make_shoup_table(kc.g.pw[31].h, kc.g.pw[31].l, kc.g.ht32);
 }
 
 }  // namespace pkgcm

@@ -39,6 +39,8 @@ def lib() -> C.CDLL:
         L.pk_gcm_launch_count.argtypes, L.pk_gcm_launch_count.restype = [vp], C.c_uint64
         L.pk_gcm_last_cuda_error.argtypes = [vp]
         L.pk_gcm_last_kernel_ms.argtypes, L.pk_gcm_last_kernel_ms.restype = [vp], C.c_float
+        L.pk_gcm_host_alloc.argtypes, L.pk_gcm_host_alloc.restype = [vp, C.c_size_t], vp
+        L.pk_gcm_host_free.argtypes, L.pk_gcm_host_free.restype = [vp, vp], None
         _bound = True
     return L
 
@@ -62,9 +64,23 @@ class Gcm:
         rc = self._L.pk_gcm_init(device, bytes(key), len(key), max_messages, max_bytes, C.byref(self._h))
         if rc:
             raise GcmError(rc, "pk_gcm_init")
+        self._pinned = []
+
+    def pinned(self, nbytes: int, dtype=np.uint8) -> np.ndarray:
+        """A page-locked array (pk_gcm_host_alloc) of nbytes bytes viewed as dtype; freed by close()."""
+        nbytes = max(int(nbytes), 16)
+        p = self._L.pk_gcm_host_alloc(self._h, nbytes)
+        if not p:
+            raise GcmError(-5, "pk_gcm_host_alloc")
+        self._pinned.append(p)
+        buf = (C.c_uint8 * nbytes).from_address(p)
+        return np.frombuffer(buf, dtype=np.uint8).view(dtype)
 
     def close(self):
         if self._h:
+            for p in self._pinned:
+                self._L.pk_gcm_host_free(self._h, p)
+            self._pinned = []
             self._L.pk_gcm_destroy(self._h)
             self._h = C.c_void_p()
 

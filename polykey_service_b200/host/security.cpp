@@ -29,7 +29,23 @@ GpuCipher::GpuCipher(const Bytes& key, int device, uint32_t max_messages, uint64
     }
 }
 
-GpuCipher::~GpuCipher() { if (h_) pk_gcm_destroy(h_); }
+GpuCipher::~GpuCipher()
+{
+    if (!h_) return;
+    for (uint8_t* a : arena_) pk_gcm_host_free(h_, a);
+    pk_gcm_destroy(h_);
+}
+
+uint8_t* GpuCipher::arena(int which, size_t bytes)
+{
+    if (bytes > arena_bytes_[which]) {
+        pk_gcm_host_free(h_, arena_[which]);
+        const size_t want = bytes + bytes / 2;             // head-room so a slowly growing batch does not reallocate every call
+        arena_[which] = static_cast<uint8_t*>(pk_gcm_host_alloc(h_, want));
+        arena_bytes_[which] = arena_[which] ? want : 0;
+    }
+    return arena_[which];
+}
 
 BatchResult GpuCipher::BatchEncrypt(const std::vector<Bytes>& plaintexts, const std::vector<Bytes>* nonces)
 {
@@ -45,9 +61,12 @@ BatchResult GpuCipher::BatchEncrypt(const std::vector<Bytes>& plaintexts, const 
         pat += round16(plen[i]);
         sat += round16((uint64_t)plen[i] + PK_GCM_OVERHEAD);
     }
-    Bytes plain(pat + 16), sealed(sat + 16), nonce_arr((size_t)n * PK_GCM_NONCE_BYTES);
+    Bytes nonce_arr((size_t)n * PK_GCM_NONCE_BYTES);
+    uint8_t* plain = arena(0, pat + 16);
+    uint8_t* sealed = arena(1, sat + 16);
+    if (!plain || !sealed) return {{}, std::string("failed to encrypt plaintext: ") + pk_gcm_strerror(PK_GCM_ERR_CUDA)};
     for (uint32_t i = 0; i < n; ++i)
-        if (plen[i]) std::memcpy(plain.data() + poff[i], plaintexts[i].data(), plen[i]);
+        if (plen[i]) std::memcpy(plain + poff[i], plaintexts[i].data(), plen[i]);
     if (nonces) {
         for (uint32_t i = 0; i < n; ++i) {
             if ((*nonces)[i].size() != PK_GCM_NONCE_BYTES) return {{}, std::string("failed to encrypt plaintext: bad nonce length")};
@@ -61,12 +80,12 @@ BatchResult GpuCipher::BatchEncrypt(const std::vector<Bytes>& plaintexts, const 
             got += (size_t)r;
         }
     }
-    const int rc = pk_gcm_seal_batch(h_, plain.data(), poff.data(), plen.data(), nonce_arr.data(), n, sealed.data(), soff.data());
+    const int rc = pk_gcm_seal_batch(h_, plain, poff.data(), plen.data(), nonce_arr.data(), n, sealed, soff.data());
     if (rc != PK_GCM_OK) return {{}, std::string("failed to encrypt plaintext: ") + pk_gcm_strerror(rc)};   // cipher.go:119
     BatchResult out;
     out.values.reserve(n);
     for (uint32_t i = 0; i < n; ++i)
-        out.values.emplace_back(sealed.begin() + (ptrdiff_t)soff[i], sealed.begin() + (ptrdiff_t)(soff[i] + plen[i] + PK_GCM_OVERHEAD));
+        out.values.emplace_back(sealed + soff[i], sealed + soff[i] + plen[i] + PK_GCM_OVERHEAD);
     return out;
 }
 
@@ -84,10 +103,12 @@ BatchResult GpuCipher::BatchDecrypt(const std::vector<Bytes>& ciphertexts)
         sat += round16(slen[i]);
         pat += round16(slen[i] >= PK_GCM_OVERHEAD ? slen[i] - PK_GCM_OVERHEAD : 0);
     }
-    Bytes sealed(sat + 16), plain(pat + 16);
+    uint8_t* sealed = arena(0, sat + 16);
+    uint8_t* plain = arena(1, pat + 16);
+    if (!sealed || !plain) return {{}, std::string("failed to decrypt ciphertext: ") + pk_gcm_strerror(PK_GCM_ERR_CUDA)};
     for (uint32_t i = 0; i < n; ++i)
-        if (slen[i]) std::memcpy(sealed.data() + soff[i], ciphertexts[i].data(), slen[i]);
-    const int rc = pk_gcm_open_batch(h_, sealed.data(), soff.data(), slen.data(), n, plain.data(), poff.data(), status.data());
+        if (slen[i]) std::memcpy(sealed + soff[i], ciphertexts[i].data(), slen[i]);
+    const int rc = pk_gcm_open_batch(h_, sealed, soff.data(), slen.data(), n, plain, poff.data(), status.data());
     if (rc == PK_GCM_ERR_AUTH) {
         for (uint32_t i = 0; i < n; ++i) {               // the first failing item decides the message, cipher.go:133-137
             if (status[i] == 2)
@@ -101,7 +122,7 @@ BatchResult GpuCipher::BatchDecrypt(const std::vector<Bytes>& ciphertexts)
     BatchResult out;
     out.values.reserve(n);
     for (uint32_t i = 0; i < n; ++i)
-        out.values.emplace_back(plain.begin() + (ptrdiff_t)poff[i], plain.begin() + (ptrdiff_t)(poff[i] + slen[i] - PK_GCM_OVERHEAD));
+        out.values.emplace_back(plain + poff[i], plain + poff[i] + slen[i] - PK_GCM_OVERHEAD);
     return out;
 }
 

@@ -41,8 +41,12 @@ public:
     BatchResult BatchEncrypt(const std::vector<Bytes>& plaintexts, const std::vector<Bytes>* nonces = nullptr);
     BatchResult BatchDecrypt(const std::vector<Bytes>& ciphertexts);
 private:
+    // grow-only page-locked arenas (pk_gcm_host_alloc): 0 = input, 1 = output
+    uint8_t* arena(int which, size_t bytes);
     pk_gcm* h_ = nullptr;
     Error init_error_;
+    uint8_t* arena_[2] = {nullptr, nullptr};
+    size_t arena_bytes_[2] = {0, 0};
 };
 
 BytesResult Encrypt(const Bytes& key, const Bytes& plaintext);

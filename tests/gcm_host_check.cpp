@@ -50,8 +50,42 @@ extern "C" int gcmh_check_ghash(const uint8_t* key, uint64_t seed, int trials)
         seed = seed * 6364136223846793005ull + 1442695040888963407ull; uint64_t b = seed;
         uint64_t xh = a, xl = b, yh = a, yl = b;
         ghash_mul(&kc.g, xh, xl);
-        ghash_mul_bitwise(kc.g.hh[0x80], kc.g.hl[0x80], yh, yl);
+        ghash_mul_bitwise(kc.g.ht[0x80].h, kc.g.ht[0x80].l, yh, yl);
         if (xh != yh || xl != yl) ++bad;
     }
     return bad;
+}
+
+// The warp-per-message form run as a loop over 32 lanes on the host: must equal gcm_crypt_message.
+extern "C" void gcmh_seal_lanes(const uint8_t* key, const uint8_t* nonce, const uint8_t* pt, uint32_t len, uint8_t* out)
+{
+    KeyContext kc;
+    make_key_context(key, kc);
+    std::memcpy(out, nonce, 12);
+    uint64_t xh = 0, xl = 0;
+    for (uint32_t lane = 0; lane < 32; ++lane) {
+        uint64_t yh, yl;
+        gcm_lane_pass(&kc.g, TeTables{kc.te}, nonce, pt, out + 12, len, false, lane, yh, yl);
+        xh ^= yh; xl ^= yl;
+    }
+    uint8_t tag[16];
+    gcm_tag(&kc.g, TeTables{kc.te}, nonce, xh, xl, tag);
+    std::memcpy(out + 12 + len, tag, 16);
+}
+
+extern "C" int gcmh_open_lanes(const uint8_t* key, const uint8_t* sealed, uint32_t len, uint8_t* pt)
+{
+    if (len < 12) return 2;
+    if (len < 28) return 1;
+    KeyContext kc;
+    make_key_context(key, kc);
+    uint64_t xh = 0, xl = 0;
+    for (uint32_t lane = 0; lane < 32; ++lane) {
+        uint64_t yh, yl;
+        gcm_lane_pass(&kc.g, TeTables{kc.te}, sealed, sealed + 12, pt, len - 28, true, lane, yh, yl);
+        xh ^= yh; xl ^= yl;
+    }
+    uint8_t tag[16];
+    gcm_tag(&kc.g, TeTables{kc.te}, sealed, xh, xl, tag);
+    return std::memcmp(tag, sealed + len - 16, 16) == 0 ? 0 : 1;
 }

@@ -38,6 +38,8 @@ def gcmh(tmp_path_factory):
     L = C.CDLL(so)
     L.gcmh_seal.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint32, C.c_char_p]
     L.gcmh_open.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32, C.c_char_p]
+    L.gcmh_seal_lanes.argtypes = L.gcmh_seal.argtypes
+    L.gcmh_open_lanes.argtypes = L.gcmh_open.argtypes
     L.gcmh_encrypt_block.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
     L.gcmh_check_ghash.argtypes = [C.c_char_p, C.c_uint64, C.c_int]
     return L
@@ -95,3 +97,23 @@ def test_open_round_trip_and_tamper(gcmh):
         assert gcmh.gcmh_open(rng.bytes(32), sealed, len(sealed), out) == 1      # wrong key
     assert gcmh.gcmh_open(bytes(32), b"short", 5, C.create_string_buffer(1)) == 2  # cipher.go:69-71
     assert gcmh.gcmh_open(bytes(32), bytes(20), 20, C.create_string_buffer(1)) == 1
+
+
+def test_warp_per_message_form_matches_openssl(gcmh):
+    """The 32-lane split (blocks strided over lanes, Horner with H^32, closing power per lane) is
+    the same function as the serial GHASH: every length around the 32-block period, and the tag
+    check of the opening direction."""
+    rng = np.random.default_rng(5)
+    lengths = list(range(0, 40)) + [495, 496, 497, 511, 512, 513, 527, 528, 529, 1007, 1008, 1024,
+                                    1039, 1040, 1041, 2048, 4096, 4099, 16384 + 5]
+    for length in lengths:
+        key, nonce, pt = rng.bytes(32), rng.bytes(12), rng.bytes(length)
+        want = nonce + AESGCM(key).encrypt(nonce, pt, None)
+        out = C.create_string_buffer(length + 28)
+        gcmh.gcmh_seal_lanes(key, nonce, pt, length, out)
+        assert out.raw == want, length
+        back = C.create_string_buffer(max(1, length))
+        assert gcmh.gcmh_open_lanes(key, want, len(want), back) == 0 and back.raw[:length] == pt
+        bad = bytearray(want)
+        bad[len(bad) // 2] ^= 0x20
+        assert gcmh.gcmh_open_lanes(key, bytes(bad), len(bad), back) == 1

@@ -38,7 +38,7 @@ def test_batch_matches_openssl(G):
     with G.Gcm(key, max_messages=8192, max_bytes=8 << 20) as g:
         before = g.launch_count
         sealed = g.batch_encrypt(pts, nonces)
-        assert g.launch_count == before + 1                        # one launch for the whole batch
+        assert g.launch_count == before + 2                        # thread-per-message + warp-per-message kernels
         for s, p, nce in zip(sealed, pts, nonces):
             assert s == nce + ref.encrypt(nce, p, None)
         assert g.batch_decrypt(sealed) == pts                      # round trip on the GPU
@@ -108,5 +108,54 @@ def test_large_batch_of_secrets(G):
         sealed = g.batch_encrypt(pts, nonces)
         ref = AESGCM(key)
         for i in rng.integers(0, n, 2000).tolist() + [0, n - 1]:
+            assert sealed[i] == nonces[i] + ref.encrypt(nonces[i], pts[i], None)
+        assert g.batch_decrypt(sealed) == pts
+
+
+def test_long_messages_take_the_warp_kernel(G):
+    """Only long messages: one launch (the warp-per-message kernel), every length around the
+    32-block period, sealed bytes equal OpenSSL's, tampered long messages fail and release nothing."""
+    rng = np.random.default_rng(14)
+    key = rng.bytes(32)
+    lengths = [256, 257, 495, 496, 497, 511, 512, 513, 527, 528, 529, 1007, 1008, 1024, 1039, 1040,
+               1041, 2048, 4095, 4096, 4097, 16384 + 5, 65536, 100001] + rng.integers(256, 9000, 300).tolist()
+    pts = [rng.bytes(int(l)) for l in lengths]
+    nonces = [rng.bytes(12) for _ in lengths]
+    ref = AESGCM(key)
+    with G.Gcm(key, max_messages=512, max_bytes=8 << 20) as g:
+        before = g.launch_count
+        sealed = g.batch_encrypt(pts, nonces)
+        assert g.launch_count == before + 1
+        for s, p, nce in zip(sealed, pts, nonces):
+            assert s == nce + ref.encrypt(nce, p, None), len(p)
+        assert g.batch_decrypt(sealed) == pts
+        bad = list(sealed)
+        for k in (0, 5, 20, 23):
+            b = bytearray(bad[k])
+            b[len(b) // 2] ^= 0x04
+            bad[k] = bytes(b)
+        with pytest.raises(G.GcmError) as e:
+            g.batch_decrypt(bad)
+        assert e.value.code == -10
+        assert [int(i) for i in np.nonzero(e.value.status)[0]] == [0, 5, 20, 23]
+
+
+def test_large_batch_with_a_long_tail(G):
+    """A batch big enough for the higher thresholds (long_threshold in pk_gcm.cu): mostly short
+    secrets plus a tail of multi-KB ones, both kernels in one call."""
+    rng = np.random.default_rng(15)
+    key = rng.bytes(32)
+    n = 12000
+    lens = rng.integers(16, 200, n)
+    lens[rng.integers(0, n, 400)] = rng.integers(900, 6000, 400)
+    blob = rng.bytes(int(lens.sum()))
+    cuts = np.concatenate([[0], np.cumsum(lens)])
+    pts = [blob[int(cuts[i]):int(cuts[i + 1])] for i in range(n)]
+    nonce_blob = rng.bytes(12 * n)
+    nonces = [nonce_blob[12 * i:12 * i + 12] for i in range(n)]
+    ref = AESGCM(key)
+    with G.Gcm(key, max_messages=n, max_bytes=16 << 20) as g:
+        sealed = g.batch_encrypt(pts, nonces)
+        for i in np.nonzero(lens >= 900)[0].tolist() + rng.integers(0, n, 500).tolist():
             assert sealed[i] == nonces[i] + ref.encrypt(nonces[i], pts[i], None)
         assert g.batch_decrypt(sealed) == pts

@@ -3,7 +3,8 @@
 
 For each workload: seal a batch on the GPU through the C ABI (host buffers in and out), check it
 bit-exactly against OpenSSL, and time
-  gpu_e2e_ms     one pk_gcm_seal_batch call (copies + kernel + copies), median
+  gpu_e2e_ms     one pk_gcm_seal_batch call (copies + kernel + copies), median, pageable arenas
+  gpu_e2e_pinned_ms  the same with page-locked arenas (pk_gcm_host_alloc)
   gpu_kernel_ms  the kernel alone (CUDA events on its stream)
   cpu_ref_ms     OpenSSL with a fresh cipher per message — what BatchEncrypt does
                  (internal/adapters/security/cipher.go:116-122) — all cores / 1 core
@@ -23,7 +24,10 @@ sys.path.insert(0, ROOT)
 from polykey_service_b200 import gcm  # noqa: E402
 
 WORKLOADS = [("65536 x 64 B", 65536, 64), ("65536 x 256 B", 65536, 256), ("4096 x 4 KiB", 4096, 4096),
-             ("1024 x 64 B", 1024, 64)]
+             ("1024 x 64 B", 1024, 64), ("256 x 4 KiB", 256, 4096), ("32768 x 4 KiB", 32768, 4096)]
+# kernel-only sweep of the thread-per-message / warp-per-message split (PK_GCM_LONG_BYTES)
+SWEEP = [(65536, 512), (65536, 1024), (65536, 2048), (32768, 4096), (16384, 1024), (16384, 4096), (4096, 512),
+         (4096, 1024), (4096, 4096), (1024, 256), (1024, 1024), (256, 256), (256, 4096), (16, 16384)]
 
 
 def med(f, reps):
@@ -71,8 +75,18 @@ def main():
                 g.seal_arena(plain, poff, plen, nonces, sealed, soff)
                 ks.append(g.last_kernel_ms)
             kernel = sorted(ks)[len(ks) // 2]
+            # the same call with every arena page-locked (pk_gcm_host_alloc), as the host mirror packs them
+            pin = [g.pinned(a.nbytes, a.dtype) for a in (plain, poff, plen, nonces, sealed, soff)]
+            for dst, src in zip(pin, (plain, poff, plen, nonces, sealed, soff)):
+                dst[:src.size] = src
+            p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff = (d[:s_.size] for d, s_ in zip(pin, (plain, poff, plen, nonces, sealed, soff)))
+            p_sealed[:] = 0
+            g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff)
+            if not (np.asarray(p_sealed) == sealed).all():
+                raise SystemExit(f"pinned and pageable results differ for {name}")
+            e2e_pinned = med(lambda: g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff), 30)
         row = {"workload": name, "messages": n, "bytes": length, "payload_mb": n * length / 1e6,
-               "gpu_e2e_ms": e2e, "gpu_kernel_ms": kernel,
+               "gpu_e2e_ms": e2e, "gpu_e2e_pinned_ms": e2e_pinned, "gpu_kernel_ms": kernel,
                "cpu_ref_all_ms": med(lambda: cpu(cores, 1), 10), "cpu_ref_1core_ms": med(lambda: cpu(1, 1), 3),
                "cpu_reuse_all_ms": med(lambda: cpu(cores, 0), 10)}
         row["gpu_kernel_gbs"] = n * length / row["gpu_kernel_ms"] / 1e6
@@ -80,7 +94,27 @@ def main():
         row["cpu_ref_all_msgs_per_s"] = n / row["cpu_ref_all_ms"] * 1e3
         rows.append(row)
         print(row, file=sys.stderr, flush=True)
-    print(json.dumps({"cores": cores, "rows": rows}))
+    sweep = []
+    for n, length in SWEEP:
+        plen = np.full(n, length, dtype=np.uint32)
+        poff, ptotal = gcm.slots(plen)
+        soff, stotal = gcm.slots(plen.astype(np.uint64) + gcm.OVERHEAD)
+        plain = rng.integers(0, 256, ptotal, dtype=np.uint8)
+        nonces = rng.integers(0, 256, 12 * n, dtype=np.uint8)
+        sealed = np.zeros(stotal, dtype=np.uint8)
+        row = {"messages": n, "bytes": length}
+        with gcm.Gcm(key, max_messages=n, max_bytes=stotal + 64) as g:
+            for label, env in (("thread_ms", str(1 << 30)), ("warp_ms", "64"), ("default_ms", "")):
+                os.environ["PK_GCM_LONG_BYTES"] = env
+                ks = []
+                for _ in range(8):
+                    g.seal_arena(plain, poff, plen, nonces, sealed, soff)
+                    ks.append(g.last_kernel_ms)
+                row[label] = sorted(ks[2:])[len(ks[2:]) // 2]
+        os.environ["PK_GCM_LONG_BYTES"] = ""
+        sweep.append(row)
+        print(row, file=sys.stderr, flush=True)
+    print(json.dumps({"cores": cores, "rows": rows, "sweep": sweep}))
 
 
 if __name__ == "__main__":
