@@ -70,6 +70,12 @@ PK_GCM_API int  pk_gcm_open_batch(pk_gcm* h, const uint8_t* sealed, const uint64
                                   const uint32_t* sealed_len, uint32_t n, uint8_t* plain,
                                   const uint64_t* plain_off, uint32_t* status);
 
+/* How a batch is pipelined.  0 (default): batches of 4 MiB and more in page-locked arenas are cut
+ * into 2, 4 or 8 chunks of whole messages so that copy in, kernels and copy out overlap; 1: never
+ * (one copy in, the kernels, one copy out — what pk_gcm_last_kernel_ms needs to time the kernels
+ * alone); 2..8: that many.                                                                        */
+PK_GCM_API int   pk_gcm_set_chunks(pk_gcm* h, uint32_t chunks);
+
 /* Page-locked host memory for the arenas (plain, sealed, offsets, nonces): copies to and from
  * pinned memory run at PCIe rate; pageable memory is staged by the driver at about a third of it.
  * Any host pointer is accepted by the calls above; these are the fast ones.  NULL on failure.     */
@@ -78,7 +84,8 @@ PK_GCM_API void  pk_gcm_host_free(pk_gcm* h, void* p);
 
 PK_GCM_API const char* pk_gcm_strerror(int status);
 PK_GCM_API uint64_t    pk_gcm_launch_count(const pk_gcm* h);
-/* Device time of the kernel of the last seal/open call (CUDA events on its stream), ms; < 0 if none. */
+/* Device time from the first to the last kernel of the last seal/open call (CUDA events on their
+ * stream), ms; < 0 if none.  With a pipelined batch it includes waiting for the copies in.        */
 PK_GCM_API float       pk_gcm_last_kernel_ms(pk_gcm* h);
 PK_GCM_API int         pk_gcm_last_cuda_error(const pk_gcm* h);
 

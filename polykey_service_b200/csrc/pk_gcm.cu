@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
                                                        const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
                                                        const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
                                                        uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
-                                                       uint32_t* __restrict__ status, uint32_t n, int mode,
+                                                       uint32_t* __restrict__ status, uint32_t first, uint32_t n, int mode,
                                                        uint32_t long_bytes)
 {
     __shared__ pkgcm::GcmTables kc_s;
@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
     const pkgcm::GcmTables* kc = &kc_s;
     const pkgcm::TeReplicated te{te_rep, threadIdx.x & 31u};
 
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;      // messages [first, n)
     if (i >= n) return;
     const uint32_t len = in_len[i];
     if (len >= long_bytes) return;                        // gcm_long_kernel's message
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(kThreads) gcm_long_kernel(const KeyContext* __
                                                             const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
                                                             uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
                                                             uint32_t* __restrict__ status, const uint32_t* __restrict__ long_idx,
-                                                            uint32_t n_long, int mode)
+                                                            uint32_t first, uint32_t n_long, int mode)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     const Staged st = stage_dual(smem, kc_g);
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(kThreads) gcm_long_kernel(const KeyContext* __
     const pkgcm::TeDual& te = st.te;
     const uint32_t lane = threadIdx.x & 31u;
 
-    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t w = first + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);   // list entries [first, n_long)
     if (w >= n_long) return;                              // whole warps leave together
     const uint32_t i = long_idx[w];
     const uint8_t* src = in + in_off[i];
@@ -187,8 +187,11 @@ struct pk_gcm {
     uint64_t *d_in_off = nullptr, *d_out_off = nullptr;
     uint32_t *d_len = nullptr, *d_status = nullptr, *d_long = nullptr;
     uint32_t* h_long = nullptr;                 // pinned: indices of the messages the warp kernel takes
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // bracket the kernel of the last call
+    cudaStream_t stream = nullptr;              // copies in, and everything when a batch is not pipelined
+    cudaStream_t s_run = nullptr, s_out = nullptr;   // kernels / copies out of a pipelined batch
+    cudaEvent_t ev_in[8] = {}, ev_run[8] = {};  // chunk c: its input has landed / its kernels are done
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // bracket the kernels of the last call
+    uint32_t chunks = 0;                        // 0 = choose per batch, 1 = never pipeline, 2..8 = this many
     int last_cuda = 0;
     uint64_t launches = 0;
 };
@@ -204,6 +207,13 @@ namespace {
             return PK_GCM_ERR_CUDA;                         \
         }                                                   \
     } while (0)
+
+bool is_pinned(const void* p)
+{
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
 
 // Smallest message (bytes, as passed in) the warp-per-message kernel takes for a batch of n.
 // PK_GCM_LONG_BYTES overrides it (tools/bench_gcm.py sweeps it).
@@ -242,33 +252,78 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
     if (in_end && !in) return PK_GCM_ERR_ARG;
 
     PKG_CUDA(h, cudaSetDevice(h->device));
-    cudaStream_t st = h->stream;
-    if (in_end) PKG_CUDA(h, cudaMemcpyAsync(h->d_in, in, in_end, cudaMemcpyHostToDevice, st));
-    PKG_CUDA(h, cudaMemcpyAsync(h->d_in_off, in_off, (size_t)n * 8, cudaMemcpyHostToDevice, st));
-    PKG_CUDA(h, cudaMemcpyAsync(h->d_out_off, out_off, (size_t)n * 8, cudaMemcpyHostToDevice, st));
-    PKG_CUDA(h, cudaMemcpyAsync(h->d_len, in_len, (size_t)n * 4, cudaMemcpyHostToDevice, st));
-    if (mode == 0) PKG_CUDA(h, cudaMemcpyAsync(h->d_nonce, nonces, (size_t)n * pkgcm::kNonceBytes, cudaMemcpyHostToDevice, st));
-    if (n_long) PKG_CUDA(h, cudaMemcpyAsync(h->d_long, h->h_long, (size_t)n_long * 4, cudaMemcpyHostToDevice, st));
-    PKG_CUDA(h, cudaEventRecord(h->ev0, st));
-    if (n_long < n) {
-        // one thread per message: spread a small batch over more SMs with narrower blocks
-        const uint32_t threads = n >= 148u * 2u * kThreads ? kThreads : n >= 148u * 64u ? 64u : 32u;
-        gcm_kernel<<<(n + threads - 1) / threads, threads, 0, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
-                                                                       h->d_out, h->d_out_off, h->d_status, n, mode, long_bytes);
-        PKG_CUDA(h, cudaGetLastError());
-        ++h->launches;
+    // A large batch is cut into chunks of whole messages: the copy in of chunk c+1, the kernels of
+    // chunk c and the copy out of chunk c-1 run at the same time (PCIe is full duplex), on three
+    // streams chained by events.  Slots are in increasing order, so a chunk is one byte range of
+    // each arena and one range of the long-message list.
+    // Measured (profiles/README.md §6): pays from about 4 MiB of traffic, and only with page-locked
+    // arenas — a pageable copy is staged synchronously by the driver and chunking only adds calls.
+    uint32_t chunks = h->chunks;
+    if (chunks == 0) {
+        const uint64_t traffic = in_end + out_end;
+        chunks = traffic >= (64u << 20) ? 8u : traffic >= (8u << 20) ? 4u : traffic >= (4u << 20) ? 2u : 1u;
+        if (chunks > 1 && !(is_pinned(in) && is_pinned(out))) chunks = 1;
     }
-    if (n_long) {
-        const uint32_t warps = n_long >= 148u * 2u * 8u ? 8u : n_long >= 148u * 2u ? 2u : 1u;
-        gcm_long_kernel<<<(n_long + warps - 1) / warps, warps * 32u, kSmemBytes, st>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
-                                                                              h->d_out, h->d_out_off, h->d_status, h->d_long, n_long, mode);
-        PKG_CUDA(h, cudaGetLastError());
-        ++h->launches;
+    if (chunks > 8u) chunks = 8u;
+    if (chunks > n) chunks = n;
+    const bool piped = chunks > 1;
+    cudaStream_t s_in = h->stream, s_run = piped ? h->s_run : h->stream, s_out = piped ? h->s_out : h->stream;
+    PKG_CUDA(h, cudaMemcpyAsync(h->d_in_off, in_off, (size_t)n * 8, cudaMemcpyHostToDevice, s_in));
+    PKG_CUDA(h, cudaMemcpyAsync(h->d_out_off, out_off, (size_t)n * 8, cudaMemcpyHostToDevice, s_in));
+    PKG_CUDA(h, cudaMemcpyAsync(h->d_len, in_len, (size_t)n * 4, cudaMemcpyHostToDevice, s_in));
+    if (mode == 0) PKG_CUDA(h, cudaMemcpyAsync(h->d_nonce, nonces, (size_t)n * pkgcm::kNonceBytes, cudaMemcpyHostToDevice, s_in));
+    if (n_long) PKG_CUDA(h, cudaMemcpyAsync(h->d_long, h->h_long, (size_t)n_long * 4, cudaMemcpyHostToDevice, s_in));
+    uint32_t lo = 0, l_lo = 0;
+    for (uint32_t c = 0; c < chunks; ++c) {
+        // chunk c = messages [lo, hi): cut by bytes, so chunks carry equal copy time
+        uint32_t hi = n;
+        if (c + 1 < chunks) {
+            const uint64_t cut = in_end / chunks * (c + 1);
+            hi = lo;
+            while (hi < n && in_off[hi] < cut) ++hi;
+        }
+        if (hi == lo) continue;
+        const uint64_t in_lo = in_off[lo], in_hi = hi < n ? in_off[hi] : in_end;
+        const uint64_t out_lo = out_off[lo], out_hi = hi < n ? out_off[hi] : out_end;
+        uint32_t l_hi = l_lo;
+        while (l_hi < n_long && h->h_long[l_hi] < hi) ++l_hi;
+        if (in_hi > in_lo) PKG_CUDA(h, cudaMemcpyAsync(h->d_in + in_lo, in + in_lo, in_hi - in_lo, cudaMemcpyHostToDevice, s_in));
+        if (piped) {
+            PKG_CUDA(h, cudaEventRecord(h->ev_in[c], s_in));
+            PKG_CUDA(h, cudaStreamWaitEvent(s_run, h->ev_in[c], 0));
+        }
+        if (lo == 0) PKG_CUDA(h, cudaEventRecord(h->ev0, s_run));
+        const uint32_t cnt = hi - lo, cnt_long = l_hi - l_lo;
+        if (cnt_long < cnt) {
+            // one thread per message: spread a small batch over more SMs with narrower blocks
+            const uint32_t threads = cnt >= 148u * 2u * kThreads ? kThreads : cnt >= 148u * 64u ? 64u : 32u;
+            gcm_kernel<<<(cnt + threads - 1) / threads, threads, 0, s_run>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
+                                                                             h->d_out, h->d_out_off, h->d_status, lo, hi, mode, long_bytes);
+            PKG_CUDA(h, cudaGetLastError());
+            ++h->launches;
+        }
+        if (cnt_long) {
+            const uint32_t warps = cnt_long >= 148u * 2u * 8u ? 8u : cnt_long >= 148u * 2u ? 2u : 1u;   // 16-warp CTAs measured slower
+            gcm_long_kernel<<<(cnt_long + warps - 1) / warps, warps * 32u, kSmemBytes, s_run>>>(
+                h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce, h->d_out, h->d_out_off, h->d_status, h->d_long, l_lo, l_hi, mode);
+            PKG_CUDA(h, cudaGetLastError());
+            ++h->launches;
+        }
+        if (hi == n) PKG_CUDA(h, cudaEventRecord(h->ev1, s_run));
+        if (piped) {
+            PKG_CUDA(h, cudaEventRecord(h->ev_run[c], s_run));
+            PKG_CUDA(h, cudaStreamWaitEvent(s_out, h->ev_run[c], 0));
+        }
+        if (out_hi > out_lo) PKG_CUDA(h, cudaMemcpyAsync(out + out_lo, h->d_out + out_lo, out_hi - out_lo, cudaMemcpyDeviceToHost, s_out));
+        if (mode == 1) PKG_CUDA(h, cudaMemcpyAsync(status + lo, h->d_status + lo, (size_t)cnt * 4, cudaMemcpyDeviceToHost, s_out));
+        lo = hi;
+        l_lo = l_hi;
     }
-    PKG_CUDA(h, cudaEventRecord(h->ev1, st));
-    if (out_end) PKG_CUDA(h, cudaMemcpyAsync(out, h->d_out, out_end, cudaMemcpyDeviceToHost, st));
-    if (mode == 1) PKG_CUDA(h, cudaMemcpyAsync(status, h->d_status, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
-    PKG_CUDA(h, cudaStreamSynchronize(st));
+    PKG_CUDA(h, cudaStreamSynchronize(s_out));
+    if (piped) {                                           // all three idle before the handle is reused
+        PKG_CUDA(h, cudaStreamSynchronize(s_run));
+        PKG_CUDA(h, cudaStreamSynchronize(s_in));
+    }
     if (mode == 1)
         for (uint32_t i = 0; i < n; ++i)
             if (status[i] != 0) return PK_GCM_ERR_AUTH;       // BatchDecrypt fails as a whole, cipher.go:135-137
@@ -316,6 +371,12 @@ int pk_gcm_init(int device, const uint8_t* key, uint32_t key_len, uint32_t max_m
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gcm_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->s_run, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking);
+    for (int c = 0; c < 8 && e == cudaSuccess; ++c) {
+        e = cudaEventCreateWithFlags(&h->ev_in[c], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_run[c], cudaEventDisableTiming);
+    }
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_kc, sizeof kc);
@@ -344,11 +405,19 @@ void pk_gcm_destroy(pk_gcm* h)
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->s_run) cudaStreamSynchronize(h->s_run);
+    if (h->s_out) cudaStreamSynchronize(h->s_out);
     if (h->d_kc) { cudaMemset(h->d_kc, 0, sizeof(KeyContext)); cudaFree(h->d_kc); }
     void* bufs[] = {h->d_in, h->d_out, h->d_nonce, h->d_in_off, h->d_out_off, h->d_len, h->d_status};
     for (void* b : bufs) if (b) cudaFree(b);
     if (h->d_long) cudaFree(h->d_long);
     if (h->h_long) cudaFreeHost(h->h_long);
+    for (int c = 0; c < 8; ++c) {
+        if (h->ev_in[c]) cudaEventDestroy(h->ev_in[c]);
+        if (h->ev_run[c]) cudaEventDestroy(h->ev_run[c]);
+    }
+    if (h->s_run) cudaStreamDestroy(h->s_run);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -383,6 +452,13 @@ void pk_gcm_host_free(pk_gcm* h, void* p)
 {
     if (!h || !p) return;
     if (cudaFreeHost(p) != cudaSuccess) h->last_cuda = (int)cudaGetLastError();
+}
+
+int pk_gcm_set_chunks(pk_gcm* h, uint32_t chunks)
+{
+    if (!h || chunks > 8u) return PK_GCM_ERR_ARG;
+    h->chunks = chunks;
+    return PK_GCM_OK;
 }
 
 uint64_t pk_gcm_launch_count(const pk_gcm* h) { return h ? h->launches : 0; }

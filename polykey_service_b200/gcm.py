@@ -39,6 +39,7 @@ def lib() -> C.CDLL:
         L.pk_gcm_launch_count.argtypes, L.pk_gcm_launch_count.restype = [vp], C.c_uint64
         L.pk_gcm_last_cuda_error.argtypes = [vp]
         L.pk_gcm_last_kernel_ms.argtypes, L.pk_gcm_last_kernel_ms.restype = [vp], C.c_float
+        L.pk_gcm_set_chunks.argtypes = [vp, u32]
         L.pk_gcm_host_alloc.argtypes, L.pk_gcm_host_alloc.restype = [vp, C.c_size_t], vp
         L.pk_gcm_host_free.argtypes, L.pk_gcm_host_free.restype = [vp, vp], None
         _bound = True
@@ -75,6 +76,12 @@ class Gcm:
         self._pinned.append(p)
         buf = (C.c_uint8 * nbytes).from_address(p)
         return np.frombuffer(buf, dtype=np.uint8).view(dtype)
+
+    def set_chunks(self, chunks: int):
+        """0 = pipeline large batches (default), 1 = never, 2..8 = that many chunks."""
+        rc = self._L.pk_gcm_set_chunks(self._h, chunks)
+        if rc:
+            raise GcmError(rc, "pk_gcm_set_chunks")
 
     def close(self):
         if self._h:

@@ -36,6 +36,7 @@ def test_batch_matches_openssl(G):
     nonces = [rng.bytes(12) for _ in lengths]
     ref = AESGCM(key)
     with G.Gcm(key, max_messages=8192, max_bytes=8 << 20) as g:
+        g.set_chunks(1)
         before = g.launch_count
         sealed = g.batch_encrypt(pts, nonces)
         assert g.launch_count == before + 2                        # thread-per-message + warp-per-message kernels
@@ -123,6 +124,7 @@ def test_long_messages_take_the_warp_kernel(G):
     nonces = [rng.bytes(12) for _ in lengths]
     ref = AESGCM(key)
     with G.Gcm(key, max_messages=512, max_bytes=8 << 20) as g:
+        g.set_chunks(1)
         before = g.launch_count
         sealed = g.batch_encrypt(pts, nonces)
         assert g.launch_count == before + 1
@@ -159,3 +161,36 @@ def test_large_batch_with_a_long_tail(G):
         for i in np.nonzero(lens >= 900)[0].tolist() + rng.integers(0, n, 500).tolist():
             assert sealed[i] == nonces[i] + ref.encrypt(nonces[i], pts[i], None)
         assert g.batch_decrypt(sealed) == pts
+
+
+def test_pipelined_chunks_give_the_same_bytes(G):
+    """A batch cut into 2..8 chunks (copy in / kernels / copy out overlapped) equals the unchunked
+    call, in both directions, with long messages straddling the cuts and a failing message whose
+    status lands in the right place."""
+    rng = np.random.default_rng(16)
+    key = rng.bytes(32)
+    n = 3000
+    lens = rng.integers(0, 700, n)
+    lens[rng.integers(0, n, 60)] = rng.integers(2000, 60000, 60)
+    pts = [rng.bytes(int(l)) for l in lens]
+    nonces = [rng.bytes(12) for _ in range(n)]
+    with G.Gcm(key, max_messages=n, max_bytes=16 << 20) as g:
+        g.set_chunks(1)
+        want = g.batch_encrypt(pts, nonces)
+        ref = AESGCM(key)
+        for i in rng.integers(0, n, 300).tolist():
+            assert want[i] == nonces[i] + ref.encrypt(nonces[i], pts[i], None)
+        for chunks in (0, 2, 3, 8):
+            g.set_chunks(chunks)
+            assert g.batch_encrypt(pts, nonces) == want, chunks
+            assert g.batch_decrypt(want) == pts, chunks
+            bad = list(want)
+            for k in (1, n // 2, n - 1):
+                b = bytearray(bad[k])
+                b[-1] ^= 1
+                bad[k] = bytes(b)
+            with pytest.raises(G.GcmError) as e:
+                g.batch_decrypt(bad)
+            assert [int(i) for i in np.nonzero(e.value.status)[0]] == [1, n // 2, n - 1], chunks
+        with pytest.raises(G.GcmError):
+            g.set_chunks(9)

@@ -4,7 +4,7 @@
 For each workload: seal a batch on the GPU through the C ABI (host buffers in and out), check it
 bit-exactly against OpenSSL, and time
   gpu_e2e_ms     one pk_gcm_seal_batch call (copies + kernel + copies), median, pageable arenas
-  gpu_e2e_pinned_ms  the same with page-locked arenas (pk_gcm_host_alloc)
+  gpu_e2e_pinned_ms  the same with page-locked arenas (pk_gcm_host_alloc);  _serial: chunking off
   gpu_kernel_ms  the kernel alone (CUDA events on its stream)
   cpu_ref_ms     OpenSSL with a fresh cipher per message — what BatchEncrypt does
                  (internal/adapters/security/cipher.go:116-122) — all cores / 1 core
@@ -70,6 +70,7 @@ def main():
             while time.perf_counter() < t_end:
                 g.seal_arena(plain, poff, plen, nonces, sealed, soff)
             e2e = med(lambda: g.seal_arena(plain, poff, plen, nonces, sealed, soff), 30)
+            g.set_chunks(1)                                      # kernels alone: no copy overlapping them
             ks = []
             for _ in range(10):
                 g.seal_arena(plain, poff, plen, nonces, sealed, soff)
@@ -84,9 +85,15 @@ def main():
             g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff)
             if not (np.asarray(p_sealed) == sealed).all():
                 raise SystemExit(f"pinned and pageable results differ for {name}")
+            e2e_pinned_serial = med(lambda: g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff), 30)
+            g.set_chunks(0)                                      # default: large batches pipelined in chunks
+            p_sealed[:] = 0
+            g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff)
+            if not (np.asarray(p_sealed) == sealed).all():
+                raise SystemExit(f"pipelined result differs for {name}")
             e2e_pinned = med(lambda: g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff), 30)
         row = {"workload": name, "messages": n, "bytes": length, "payload_mb": n * length / 1e6,
-               "gpu_e2e_ms": e2e, "gpu_e2e_pinned_ms": e2e_pinned, "gpu_kernel_ms": kernel,
+               "gpu_e2e_ms": e2e, "gpu_e2e_pinned_ms": e2e_pinned, "gpu_e2e_pinned_serial_ms": e2e_pinned_serial, "gpu_kernel_ms": kernel,
                "cpu_ref_all_ms": med(lambda: cpu(cores, 1), 10), "cpu_ref_1core_ms": med(lambda: cpu(1, 1), 3),
                "cpu_reuse_all_ms": med(lambda: cpu(cores, 0), 10)}
         row["gpu_kernel_gbs"] = n * length / row["gpu_kernel_ms"] / 1e6
@@ -104,6 +111,7 @@ def main():
         sealed = np.zeros(stotal, dtype=np.uint8)
         row = {"messages": n, "bytes": length}
         with gcm.Gcm(key, max_messages=n, max_bytes=stotal + 64) as g:
+            g.set_chunks(1)
             for label, env in (("thread_ms", str(1 << 30)), ("warp_ms", "64"), ("default_ms", "")):
                 os.environ["PK_GCM_LONG_BYTES"] = env
                 ks = []

@@ -8,7 +8,7 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:gcm_
 python -c "
 import json
 d=json.load(open('gpurun_out/bench_gcm.json'))
-for r in d['rows']: print('%-16s e2e=%.3f ms (pinned %.3f) kernel=%.3f ms (%.1f GB/s) | cpu ref all=%.3f 1core=%.3f reuse all=%.3f'%(r['workload'],r['gpu_e2e_ms'],r['gpu_e2e_pinned_ms'],r['gpu_kernel_ms'],r['gpu_kernel_gbs'],r['cpu_ref_all_ms'],r['cpu_ref_1core_ms'],r['cpu_reuse_all_ms']))
+for r in d['rows']: print('%-16s e2e=%.3f ms (pinned %.3f, unchunked %.3f) kernel=%.3f ms (%.1f GB/s) | cpu ref all=%.3f 1core=%.3f reuse all=%.3f'%(r['workload'],r['gpu_e2e_ms'],r['gpu_e2e_pinned_ms'],r['gpu_e2e_pinned_serial_ms'],r['gpu_kernel_ms'],r['gpu_kernel_gbs'],r['cpu_ref_all_ms'],r['cpu_ref_1core_ms'],r['cpu_reuse_all_ms']))
 "
 python -c "
 import json

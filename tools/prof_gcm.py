@@ -19,6 +19,7 @@ plain = rng.integers(0, 256, ptotal, dtype=np.uint8)
 nonces = rng.integers(0, 256, 12 * n, dtype=np.uint8)
 sealed = np.zeros(stotal, dtype=np.uint8)
 with gcm.Gcm(rng.bytes(32), max_messages=n, max_bytes=stotal + 64) as g:
+    g.set_chunks(1)
     for _ in range(reps):
         g.seal_arena(plain, poff, plen, nonces, sealed, soff)
         print("kernel_ms", g.last_kernel_ms)
