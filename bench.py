@@ -139,6 +139,16 @@ def dist_setup(n_gpus: int):
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
+        # keep this rank's threads and (first-touch) its page-locked arenas on the GPU's NUMA node
+        try:
+            from polykey_service_b200 import shard
+            pr = torch.cuda.get_device_properties(local)
+            bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+            cpus = shard.bind_to_gpu_numa(bdf)
+            print(f"[rank {rank}] gpu {bdf}: bound to {len(cpus)} local cpus" if cpus else
+                  f"[rank {rank}] gpu {bdf}: affinity unchanged", file=sys.stderr)
+        except (AttributeError, OSError) as e:
+            print(f"[rank {rank}] NUMA binding skipped: {e}", file=sys.stderr)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         return world, rank, local, dist
     return 1, 0, 0, None

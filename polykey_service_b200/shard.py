@@ -44,3 +44,42 @@ def merge_shards(total: int, world: int, shard_records):
     for rank, rec in enumerate(shard_records):
         out[shard_ids(total, world, rank)] = rec
     return out
+
+
+def parse_cpulist(text: str) -> list[int]:
+    """'0-15,32-47' -> [0..15, 32..47] (the kernel's cpulist format)."""
+    cpus: list[int] = []
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.extend(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def gpu_local_cpus(pci_bus_id: str, sysfs: str = "/sys/bus/pci/devices") -> list[int]:
+    """CPUs on the NUMA node a GPU hangs off, from sysfs (<bdf>/local_cpulist); [] if unknown.
+    pci_bus_id as CUDA/NVML print it: '00000000:1B:00.0' or '0000:1b:00.0'."""
+    dom, _, rest = pci_bus_id.strip().lower().partition(":")
+    bdf = f"{dom[-4:]:0>4}:{rest}"
+    try:
+        with open(f"{sysfs}/{bdf}/local_cpulist") as f:
+            return parse_cpulist(f.read())
+    except (OSError, ValueError):
+        return []
+
+
+def bind_to_gpu_numa(pci_bus_id: str, sysfs: str = "/sys/bus/pci/devices") -> list[int]:
+    """Pin this process to the CPUs local to its GPU BEFORE it allocates page-locked arenas, so
+    that first-touch places them on the GPU's NUMA node and every rank's copies stay off the
+    inter-socket link (the multi-GPU limiter is host-side).  Returns the CPU set now
+    in force; leaves the affinity alone (and returns []) when sysfs has no answer or the local
+    set does not intersect what the process may use (containers with a cpuset)."""
+    import os
+    local = set(gpu_local_cpus(pci_bus_id, sysfs))
+    allowed = os.sched_getaffinity(0)
+    chosen = sorted(local & allowed)
+    if not chosen or len(chosen) == len(allowed):
+        return []
+    os.sched_setaffinity(0, chosen)
+    return chosen

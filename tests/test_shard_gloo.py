@@ -69,3 +69,29 @@ def test_shard_helpers_roundtrip(oracle):
         whole = oracle.route_batch(t, b)[1]
         recs = [oracle.route_batch(t, select_requests(b, i))[1] for i in ids]
         assert (merge_shards(257, world, recs) == whole).all()
+
+
+def test_numa_binding_helpers(tmp_path):
+    """sysfs parsing and the affinity choice of shard.bind_to_gpu_numa (fake sysfs tree; the
+    process's real affinity is restored)."""
+    import os
+    from polykey_service_b200 import shard
+    assert shard.parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    assert shard.parse_cpulist("") == []
+    dev = tmp_path / "0000:1b:00.0"
+    dev.mkdir()
+    allowed = sorted(os.sched_getaffinity(0))
+    (dev / "local_cpulist").write_text(f"{allowed[0]}\n")
+    assert shard.gpu_local_cpus("00000000:1B:00.0", str(tmp_path)) == [allowed[0]]
+    assert shard.gpu_local_cpus("0000:ff:00.0", str(tmp_path)) == []
+    try:
+        if len(allowed) > 1:
+            assert shard.bind_to_gpu_numa("0000:1b:00.0", str(tmp_path)) == [allowed[0]]
+            assert os.sched_getaffinity(0) == {allowed[0]}
+        os.sched_setaffinity(0, allowed)
+        assert shard.bind_to_gpu_numa("0000:ff:00.0", str(tmp_path)) == []          # unknown device
+        (dev / "local_cpulist").write_text("100000-100001\n")                        # outside the cpuset
+        assert shard.bind_to_gpu_numa("0000:1b:00.0", str(tmp_path)) == []
+        assert os.sched_getaffinity(0) == set(allowed)
+    finally:
+        os.sched_setaffinity(0, allowed)
