@@ -132,9 +132,40 @@ Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, c
     return r;
 }
 
+// {"level":"INFO","msg":"routed batch","gpu":0,"requests":4096,"payload_bytes":8388608,
+//  "trigger":"full","duration":"212.4µs","classes":[1024,1023,1025,1024],"no_provider":0}
+// classes = decisions per tool class 0..3 (mock.go:32-64's four arms); on a failed batch the level
+// is ERROR and "error" carries the text every request of the batch is answered with.
+void BatchingService::log_batch(const Shard* s, const Arena& a, int rc)
+{
+    if (!cfg_.batch_log) return;
+    const int64_t now = std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now().time_since_epoch()).count();
+    size_t gpu = 0;
+    while (gpu < shards_.size() && shards_[gpu].get() != s) ++gpu;
+    std::string line = std::string("{\"level\":\"") + (rc ? "ERROR" : "INFO") + "\",\"msg\":\"routed batch\",\"gpu\":" +
+                       std::to_string(gpu) + ",\"requests\":" + std::to_string(a.reqs.size()) + ",\"payload_bytes\":" +
+                       std::to_string(a.bytes) + ",\"trigger\":\"" + a.trigger + "\",\"duration\":\"" +
+                       LoggingInterceptor::format_duration(now - a.t_submit_ns) + "\"";
+    if (rc) {
+        line += ",\"error\":\"routing failed: " + s->be->error_string(rc) + "\"";
+    } else {
+        uint64_t cls[4] = {0, 0, 0, 0}, none = 0;
+        for (size_t i = 0; i < a.reqs.size(); ++i) {
+            ++cls[a.out[i].tool_class & 3u];
+            if (a.out[i].flags & PK_FLAG_NO_PROVIDER) ++none;
+        }
+        line += ",\"classes\":[" + std::to_string(cls[0]) + "," + std::to_string(cls[1]) + "," + std::to_string(cls[2]) + "," +
+                std::to_string(cls[3]) + "],\"no_provider\":" + std::to_string(none);
+    }
+    line += "}";
+    std::lock_guard<std::mutex> g(log_mu_);
+    cfg_.batch_log->push_back(std::move(line));
+}
+
 void BatchingService::complete(Shard* s, Arena& a, int rc)
 {
     if (rc == 0) rc = s->be->wait((uint32_t)(&a - s->arenas.data()));
+    log_batch(s, a, rc);
     if (rc != 0) {
         healthy_.store(false);
         std::lock_guard<std::mutex> g(s->mu);
@@ -218,6 +249,10 @@ void BatchingService::flusher(Shard* s)
         ++s->st.batches;
         s->st.requests += n;
         if (full) ++s->st.flush_full; else if (went_idle) ++s->st.flush_idle; else ++s->st.flush_deadline;
+        a.trigger = full ? "full" : went_idle ? "idle" : "deadline";
+        a.bytes = 0;
+        for (const Pending* p : a.reqs) a.bytes += p->payload.size();
+        a.t_submit_ns = std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now().time_since_epoch()).count();
         if (n > s->st.max_batch_seen) s->st.max_batch_seen = n;
         lk.unlock();
 

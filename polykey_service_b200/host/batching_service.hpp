@@ -74,6 +74,11 @@ struct BatchingConfig {
                                            // (a closed population of callers is all queued by then)
     uint64_t max_payload_bytes = 32u << 20;
     uint32_t max_name_bytes_per_request = 64;
+    // One summary record per routed batch: the reference writes three
+    // synchronous log lines per REQUEST (main.go:33, 44-48; server.go:28-33), which dominate its
+    // CPU path; a batching front-end can say the same once per flush.  JSON lines in the style of
+    // the reference's slog handler minus the timestamp; nullptr = no batch log.
+    std::vector<std::string>* batch_log = nullptr;
 };
 
 struct BatchingStats {
@@ -110,6 +115,9 @@ private:
         std::vector<uint8_t> names;
         std::vector<Pending*> reqs;
         bool inflight = false;
+        uint64_t bytes = 0;                 // payload bytes of the batch in flight
+        const char* trigger = "";           // "full" | "idle" | "deadline"
+        int64_t t_submit_ns = 0;
     };
     struct Shard {
         RouteBackend* be = nullptr;
@@ -128,12 +136,14 @@ private:
     };
     void flusher(Shard* s);
     void complete(Shard* s, Arena& a, int rc);
+    void log_batch(const Shard* s, const Arena& a, int rc);
 
     Service* inner_;
     BatchingConfig cfg_;
     std::vector<std::unique_ptr<Shard>> shards_;
     std::atomic<uint64_t> next_id_{0};
     std::atomic<bool> stopping_{false}, healthy_{true};
+    std::mutex log_mu_;                     // flushers of different GPUs share the sink
 };
 
 }  // namespace polykey

@@ -146,6 +146,8 @@ static void test_batching(uint32_t n_gpus, uint32_t threads, uint32_t per_thread
     }
     BatchingConfig cfg;
     cfg.max_batch = max_batch; cfg.max_wait_us = 300; cfg.max_payload_bytes = 1 << 20;
+    std::vector<std::string> batch_log;
+    cfg.batch_log = &batch_log;
     BatchingService svc(inner.get(), bes, cfg);
     CHECK(svc.healthy());
     static const char* names[] = {"example_tool", "struct_tool", "file_tool", "nope", "", "example_tool "};
@@ -179,6 +181,20 @@ static void test_batching(uint32_t n_gpus, uint32_t threads, uint32_t per_thread
         CHECK(seen == st.requests);
     }
     svc.Shutdown();
+    // batch log: ONE record per flush (not three per request), and the records add up to the stream
+    CHECK(batch_log.size() == st.batches);
+    uint64_t logged = 0, cls_sum = 0;
+    for (const std::string& line : batch_log) {
+        CHECK(line.rfind("{\"level\":\"INFO\",\"msg\":\"routed batch\",\"gpu\":", 0) == 0 && line.back() == '}');
+        const size_t r = line.find("\"requests\":"), c = line.find("\"classes\":[");
+        CHECK(r != std::string::npos && c != std::string::npos && line.find("\"trigger\":\"") != std::string::npos &&
+              line.find("\"duration\":\"") != std::string::npos && line.find("\"no_provider\":") != std::string::npos);
+        if (r == std::string::npos || c == std::string::npos) continue;
+        logged += std::strtoull(line.c_str() + r + 11, nullptr, 10);
+        const char* q = line.c_str() + c + 11;
+        for (int k = 0; k < 4; ++k) { char* end; cls_sum += std::strtoull(q, &end, 10); q = end + 1; }
+    }
+    CHECK(logged == st.requests && cls_sum == st.requests);
     Context ctx;
     Result r = svc.ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr);
     CHECK(r.error && !r.resp);                                                       // after Shutdown: error, not a hang
@@ -194,10 +210,14 @@ static void test_device_error_path()
     OracleBackend be(2);
     be.fail_after = 0;                                                               // every submit fails
     BatchingConfig cfg; cfg.max_batch = 4; cfg.max_wait_us = 100;
+    std::vector<std::string> batch_log;
+    cfg.batch_log = &batch_log;
     BatchingService svc(inner.get(), {&be}, cfg);
     Context ctx;
     Result r = svc.ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr);
     CHECK(r.error && r.error->rfind("routing failed: ", 0) == 0 && !r.resp);          // plain error -> gRPC Unknown
+    CHECK(batch_log.size() == 1 && batch_log[0].rfind("{\"level\":\"ERROR\",\"msg\":\"routed batch\"", 0) == 0 &&
+          batch_log[0].find("\"error\":\"routing failed: ") != std::string::npos);
     CHECK(!svc.healthy());                                                           // -> health NOT_SERVING
     r = svc.ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr);
     CHECK(r.error.has_value());
