@@ -285,7 +285,13 @@ def run_gpu(args):
     sampler = ClockSampler(local)
     sampler.start()
     slots = list(range(ring))
-    use_graph = not args.no_graph
+    PDL = 0x100                                                   # PK_LAUNCH_PDL, include/pk_route.h
+    issue = "plain" if args.no_graph else args.issue
+    ISSUE = {"pdl": (1 | PDL, "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch "
+                              "(a kernel may start while its predecessor drains; batches are independent)"),
+             "serial": (1, "one CUDA graph of K kernel nodes in a chain, each starting after its predecessor completed"),
+             "plain": (0, "K plain launches")}
+    use_graph, issue_desc = ISSUE[issue]
 
     # bring clocks up, then the W warm-up steps
     t_end = time.perf_counter() + (0.0 if args.no_prewarm else 0.4)
@@ -305,10 +311,12 @@ def run_gpu(args):
     ms = reduce_max(dist, local, ms)
     value = world * args.steps * n / (ms / 1e3)
     per_launch_s = ms / 1e3 / args.steps
-    # the other issue mode, for the record
-    ms_alt = router.launch_many(slots, args.steps, use_graph=not use_graph)
-    # independent batches may overlap on the GPU: the same K launches as one graph of 4 parallel chains
-    ms_ovl = router.launch_many(slots, args.steps, use_graph=4)
+    # the other issue modes, for the record (same K launches, same stream)
+    other = {}
+    for name, mode in (("pdl", 1 | PDL), ("serial", 1), ("plain", 0), ("plain_pdl", PDL), ("four_chains", 4)):
+        if mode != use_graph:
+            other[name] = reduce_max(dist, local, router.launch_many(slots, args.steps, use_graph=mode)) / args.steps
+    ms_serial = other.get("serial", ms / args.steps)
 
     # ---- e2e: host buffers through pk_submit / pk_wait, copies inside the timed region ----
     e2e_batches, host_bufs = [], []
@@ -399,8 +407,7 @@ def run_gpu(args):
                    "parallelism": f"dp{world}: requests sharded by id, no collective",
                    "l2": f"ring of {ring} resident batches = {ring * batch_bytes / 2**20:.0f} MiB > 126 MiB L2, "
                          "launch k reads batch k mod ring",
-                   "issue": ("one CUDA graph of K kernel nodes" if use_graph else "K plain launches") +
-                            " on one stream, CUDA events on that stream"},
+                   "issue": issue_desc + "; one stream, CUDA events on that stream"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "kernel": "route_kernel (fused scan+hash+select)",
@@ -413,10 +420,11 @@ def run_gpu(args):
                                          "api": "pk_route_batch, one batch per call"}},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "alt_issue_ms_per_step": ms_alt / args.steps,
-        "overlapped": {"value": world * args.steps * n / (ms_ovl / 1e3), "unit": UNIT, "ms_per_step": ms_ovl / args.steps,
-                       "note": "same K launches as a graph of 4 parallel chains (independent batches overlap); "
-                               "not used for value/roofline, which time one launch after another"},
+        "issue_modes_ms_per_step": dict(other, **{issue: ms / args.steps}),
+        "serial": {"ms_per_step": ms_serial, "value": world * n / (ms_serial / 1e3), "unit": UNIT,
+                   "frac": alg_bytes / (ms_serial / 1e3) / 1e9 / peak,
+                   "note": "the same K launches with every kernel waiting for its predecessor to complete: what ONE "
+                           "batch costs on an idle GPU (launch + two dependent HBM round trips + drain)"},
     }
     line.update(extra_cpu)
     emit(line)
@@ -435,7 +443,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS))
-    ap.add_argument("--no-graph", action="store_true", help="issue K plain launches instead of one graph")
+    ap.add_argument("--issue", default="pdl", choices=["pdl", "serial", "plain"],
+                    help="how the K timed launches are issued on their one stream (default: graph chain + programmatic dependent launch)")
+    ap.add_argument("--no-graph", action="store_true", help="same as --issue plain")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-prewarm", action="store_true",
                     help="skip the 0.4 s clock ramp-up before the W warm-up steps (for ncu launch lists)")

@@ -179,7 +179,13 @@ PK_API int  pk_wait(pk_handle* h, uint32_t slot);
  * nodes in a chain, or (use_graph = k >= 2) as a graph of k parallel chains, launch j in
  * chain j % k, so that independent batches may overlap on the GPU; it brackets them with
  * CUDA events on that stream, waits, and reports the device time in *elapsed_ms;
+ * use_graph | PK_LAUNCH_PDL issues the same launches with programmatic stream serialization
+ * (programmatic dependent launch): still one stream / one chain, but a kernel may start while
+ * its predecessor drains — batches are independent; a batch with long requests, which owns
+ * per-request scratch in its slot, waits for its predecessor first.  Stream order for what
+ * follows is kept.
  * pk_fetch copies the slot's records out (synchronous).                               */
+#define PK_LAUNCH_PDL 0x100
 PK_API int  pk_stage(pk_handle* h, uint32_t slot,
               const uint8_t* payload, const uint64_t* pay_off, const uint32_t* pay_len,
               const uint8_t* names, const uint32_t* name_off, uint32_t n);

@@ -164,10 +164,10 @@ int enqueue_uploads(pk_handle* h, Slot& s, const uint8_t* payload, size_t meta_b
     return PK_OK;
 }
 
-int launch_slot(pk_handle* h, const Slot& s, cudaStream_t stream)
+int launch_slot(pk_handle* h, const Slot& s, cudaStream_t stream, bool pdl = false)
 {
     if (s.params.n == 0) return PK_OK;
-    PK_CUDA(h, pk::launch_route(s.params, s.max_len, h->num_sms, stream));
+    PK_CUDA(h, pk::launch_route(s.params, s.max_len, h->num_sms, stream, pdl));
     ++h->launches;
     return PK_OK;
 }
@@ -420,10 +420,12 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
     // every listed slot's earlier work must be visible to this stream
     for (uint32_t k = 1; k < n_list; ++k) PK_CUDA(h, cudaStreamSynchronize(h->slots[slots[k]].stream));
 
+    const bool pdl = (use_graph & PK_LAUNCH_PDL) != 0;
+    use_graph &= ~PK_LAUNCH_PDL;
     if (!use_graph) {
         PK_CUDA(h, cudaEventRecord(h->ev0, st));
         for (uint32_t k = 0; k < count; ++k) {
-            int rc = launch_slot(h, h->slots[slots[k % n_list]], st);
+            int rc = launch_slot(h, h->slots[slots[k % n_list]], st, pdl);
             if (rc) return rc;
         }
         PK_CUDA(h, cudaEventRecord(h->ev1, st));
@@ -435,7 +437,7 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
         const uint32_t width = use_graph >= 2 ? (uint32_t)use_graph : 1u;
         if (width == 1 || n_list < width) {
             for (uint32_t k = 0; k < count && rc == PK_OK; ++k)
-                rc = launch_slot(h, h->slots[slots[k % n_list]], st);
+                rc = launch_slot(h, h->slots[slots[k % n_list]], st, pdl);
         } else {
             // fork: chain b runs on the stream of listed slot b (b >= 1) or on st (b == 0)
             cudaError_t fe = cudaEventRecord(h->ev0, st);
@@ -444,7 +446,7 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
             if (fe != cudaSuccess) rc = PK_ERR_CUDA;
             for (uint32_t k = 0; k < count && rc == PK_OK; ++k) {
                 const uint32_t b = k % width;
-                rc = launch_slot(h, h->slots[slots[k % n_list]], b == 0 ? st : h->slots[slots[b]].stream);
+                rc = launch_slot(h, h->slots[slots[k % n_list]], b == 0 ? st : h->slots[slots[b]].stream, pdl);
             }
             // join
             for (uint32_t b = 1; b < width && rc == PK_OK; ++b) {

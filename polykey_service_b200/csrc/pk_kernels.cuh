@@ -33,10 +33,13 @@ struct RouteParams {
     uint32_t        n_extra;
     uint32_t        reqs_per_cta;   // R: set by launch_route
     uint32_t        one;            // the integer 1 (see pk_spec.cuh: keeps adds on the FMA pipe)
+    uint32_t        pdl;            // launched with programmatic stream serialization: set by launch_route
 };
 
 // Chooses the lane-group width, requests per CTA and grid, and launches the fused
 // scan+hash+select kernel on `stream`.  max_len: the longest payload of the batch.
-cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStream_t stream);
+// pdl: launch with programmatic stream serialization (programmatic dependent launch) — the grid
+// may start while the previous kernel of the stream is still running; see route_kernel.
+cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl = false);
 
 }  // namespace pk

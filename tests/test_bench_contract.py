@@ -56,4 +56,7 @@ def test_product_arm_line(oracle, pk):
     assert cb["kind"] == "port" and cb["value"] > 0 and cb["cores"] >= 1
     c = d["clocks"]
     assert c["sm_max_mhz"] and c["sm_mhz"] and isinstance(c["reasons"], list)
-    assert "l2" in d["config"] and "workload" in d["config"]
+    assert "l2" in d["config"] and "workload" in d["config"] and "programmatic dependent launch" in d["config"]["issue"]
+    modes = d["issue_modes_ms_per_step"]
+    assert {"pdl", "serial", "plain", "plain_pdl", "four_chains"} <= set(modes) and modes["pdl"] == d["ms_per_step"]
+    assert d["serial"]["ms_per_step"] == modes["serial"] and 0 < d["serial"]["frac"] <= r["frac"] * 1.25

@@ -212,6 +212,32 @@ def test_async_slots_and_resident_form(pk, router, oracle):
                              oracle.route_batch(t, batches[(s + 1) % 3], threads=8)[1], f"resident {s}")
 
 
+def test_programmatic_dependent_launch(pk, oracle):
+    """PK_LAUNCH_PDL: consecutive launches of one stream may overlap.  Same records as the oracle
+    for plain launches and for a graph chain; a slot with long requests (which owns per-request
+    scratch) launched back to back with itself stays correct; a copy out that follows sees the
+    last launch complete."""
+    t = oracle.default_table()
+    PDL = 0x100
+    batches = [oracle.gen_batch(900, 3000, 0, 4000, mode=0), oracle.gen_batch(901, 2500, 0, 200, mode=2),
+               oracle.gen_batch(902, 48, 10000, 200000, mode=0), oracle.gen_batch(903, 4096, 2048, mode=0)]
+    want = [oracle.route_batch(t, b, threads=8)[1] for b in batches]
+    router = pk.Router(device=0, max_requests=4096, max_payload_bytes=16 << 20, n_slots=4)
+    try:
+        for s, b in enumerate(batches):
+            router.stage(s, b)
+        before = router.launch_count
+        for mode in (PDL, 1 | PDL, 2 | PDL):
+            for slots in ([0, 1, 2, 3], [2], [3, 2], [1]):
+                assert router.launch_many(slots, 12, use_graph=mode) > 0
+                for s in slots:
+                    assert_records_equal(router.fetch(s, int(batches[s]["pay_len"].size)), want[s],
+                                         f"pdl mode {mode:#x} slot {s}")
+        assert router.launch_count == before + 3 * 4 * 12
+    finally:
+        router.close()
+
+
 def test_long_requests_twice_scratch_is_clean(router, oracle):
     """Multi-segment requests use the per-request scratch accumulators; a second pass over the
     same slot must see them zeroed by the first."""

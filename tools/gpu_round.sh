@@ -25,6 +25,6 @@ import json,glob
 for f in sorted(glob.glob('gpurun_out/bench_c?.json')+glob.glob('gpurun_out/bench_ref*.json')):
     try:
         d=json.load(open(f)); r=d.get('roofline') or {}
-        print('%-28s value=%.4g ms/step=%.5f frac=%s e2e=%.4g cpu=%s ovl=%s clocks=%s'%(f.split('/')[-1], d['value'], d['ms_per_step'], r.get('frac'), d['e2e']['value'], (d.get('cpu_baseline') or {}).get('value'), (d.get('overlapped') or {}).get('value'), d.get('clocks')))
+        print('%-28s value=%.4g ms/step=%.5f frac=%s e2e=%.4g cpu=%s serial=%s clocks=%s'%(f.split('/')[-1], d['value'], d['ms_per_step'], r.get('frac'), d['e2e']['value'], (d.get('cpu_baseline') or {}).get('value'), (d.get('serial') or {}).get('ms_per_step'), d.get('clocks')))
     except Exception as e: print(f, 'ERR', e)
 PY
