@@ -348,14 +348,26 @@ def run_gpu(args):
 
     e2e_pipelined(max(3, min(10, k_e2e)))                          # warm
     barrier_sync(dist, local)
+    direct_before = router.direct_count
     e0 = time.perf_counter()
     e2e_s = e2e_pipelined(k_e2e)
     e1 = time.perf_counter()
     barrier_sync(dist, local)
+    used_direct = router.direct_count - direct_before == k_e2e       # the library's own choice for this batch size
     e2e_s = reduce_max(dist, local, e2e_s)
     e2e_value = world * k_e2e * n / e2e_s
     rc, want = O.route_batch(table, e2e_batches[(k_e2e - 1) % len(e2e_batches)], threads=cores)
     assert (outs[(k_e2e - 1) % depth] == want).all(), "e2e records differ from the oracle"
+    # the other transfer path, for the record (same call, same buffers)
+    router.set_direct_bytes(0 if used_direct else 1 << 40)
+    k_alt = max(10, k_e2e // 4)
+    e2e_pipelined(3)
+    barrier_sync(dist, local)
+    e2e_alt_s = reduce_max(dist, local, e2e_pipelined(k_alt)) / k_alt
+    router.set_direct_bytes(16 << 20)
+    transfer = {True: "none issued: the kernel reads the page-locked arenas over PCIe and writes the records into the "
+                      "caller's page-locked buffer (pk_set_direct_bytes, default for batches up to 16 MiB)",
+                False: "cudaMemcpyAsync H2D (payload, metadata) and D2H (records) around the kernel"}
 
     # synchronous single-call latency (what one flush costs a waiting request)
     lat = []
@@ -415,7 +427,9 @@ def run_gpu(args):
         "cpu_baseline": cpu_baseline,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": k_e2e, "pipeline_depth": depth, "ms_per_step": e2e_s / k_e2e * 1e3,
-                "api": "pk_submit/pk_wait, pinned host arenas",
+                "api": "pk_submit/pk_wait, pinned host arenas", "copies": transfer[used_direct],
+                "other_path": {"copies": transfer[not used_direct], "ms_per_step": e2e_alt_s * 1e3,
+                               "value": world * n / e2e_alt_s, "unit": UNIT},
                 "sync_call_latency_us": {"p50": lat[len(lat) // 2], "p99": lat[min(len(lat) - 1, int(len(lat) * 0.99))],
                                          "api": "pk_route_batch, one batch per call"}},
         "gpu_launches": int(launches),

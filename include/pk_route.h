@@ -160,6 +160,16 @@ PK_API int  pk_route_batch(pk_handle* h,
                     const uint8_t* names, const uint32_t* name_off /* n+1 */,
                     uint32_t n, pk_decision* out /* n */);
 
+/* Batches up to a size skip the copies.  When a batch's payload + metadata come to at most
+ * `bytes` (default 16 MiB; 0 turns the path off), it has no request longer than 16 KiB, and
+ * `payload` and `out` are page-locked host memory the GPU can address (pk_host_alloc, or any
+ * cudaHostAlloc / cudaHostRegister'ed block), pk_submit / pk_route_batch launch the kernel
+ * directly on the caller's buffers: it reads the bytes over PCIe and writes the records into
+ * `out` — one launch instead of copy, copy, launch, copy.  Same records; the buffers must stay
+ * untouched until pk_wait returns, as in the copying path.  pk_direct_count: batches so routed. */
+PK_API int      pk_set_direct_bytes(pk_handle* h, uint64_t bytes);
+PK_API uint64_t pk_direct_count(const pk_handle* h);
+
 /* Asynchronous form of the same call for a pipelined flusher: pk_submit enqueues
  * H2D → kernel → D2H on slot `slot`'s stream and returns; pk_wait blocks until
  * that slot's records are in `out`.  Use pinned buffers (pk_host_alloc) or the

@@ -92,6 +92,8 @@ def lib() -> C.CDLL:
         L.pk_wait.argtypes = [vp, u32]
         L.pk_stage.argtypes = [vp, u32] + batch
         L.pk_launch.argtypes = [vp, u32]
+        L.pk_set_direct_bytes.argtypes = [vp, C.c_uint64]
+        L.pk_direct_count.argtypes, L.pk_direct_count.restype = [vp], C.c_uint64
         L.pk_launch_many.argtypes = [vp, vp, u32, u32, C.c_int, C.POINTER(C.c_float)]
         L.pk_fetch.argtypes = [vp, u32, vp]
         L.pk_sync.argtypes = [vp]
@@ -252,6 +254,15 @@ class Router:
     @property
     def launch_count(self) -> int:
         return int(self._L.pk_launch_count(self._h))
+
+    @property
+    def direct_count(self) -> int:
+        """Batches routed straight out of page-locked host memory (no copies)."""
+        return int(self._L.pk_direct_count(self._h))
+
+    def set_direct_bytes(self, nbytes: int):
+        """Largest batch (payload + metadata bytes) that takes the no-copy path; 0 = never."""
+        self._check(self._L.pk_set_direct_bytes(self._h, int(nbytes)), "pk_set_direct_bytes")
 
     def host_alloc(self, nbytes: int, dtype=np.uint8) -> np.ndarray:
         """Pinned host array owned by the C side (freed on close)."""

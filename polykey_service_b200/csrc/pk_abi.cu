@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <utility>
 #include <vector>
 
 #include "../../include/pk_route.h"
@@ -28,6 +29,7 @@ struct Slot {
     pk_decision* d_out = nullptr;
     pk::SegScratch* d_scratch = nullptr;
     uint8_t*     h_meta = nullptr;      // pinned staging for the metadata blob
+    uint8_t*     h_meta_dev = nullptr;  // the same block as the GPU addresses it
     uint32_t     n = 0;
     uint32_t     max_len = 0;           // longest payload of the prepared batch
     bool         staged = false;        // params describe a resident batch
@@ -47,6 +49,9 @@ struct pk_handle {
     std::vector<Slot> slots;
     int        last_cuda = 0;
     uint64_t   launches = 0;
+    uint64_t   direct_batches = 0;      // batches routed straight out of host memory (no copies)
+    uint64_t   direct_bytes = 0;        // largest batch (payload + metadata bytes) that takes that path
+    std::vector<std::pair<const uint8_t*, size_t>> pinned;   // pk_host_alloc's blocks: known device-readable
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 
@@ -150,6 +155,19 @@ int prepare(pk_handle* h, Slot& s, const uint64_t* pay_off, const uint32_t* pay_
     s.n = n;
     s.max_len = max_len;
     return PK_OK;
+}
+
+// Is [p, p + bytes) page-locked host memory the GPU can address?  Blocks from pk_host_alloc are
+// known; anything else is asked of the driver.  Returns the device-side address or nullptr.
+const uint8_t* device_view(pk_handle* h, const void* p, size_t bytes)
+{
+    const uint8_t* b = static_cast<const uint8_t*>(p);
+    for (const auto& blk : h->pinned)
+        if (b >= blk.first && b + bytes <= blk.first + blk.second) return b;   // unified addressing: same address
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+    if (a.type != cudaMemoryTypeHost || !a.devicePointer) return nullptr;
+    return static_cast<const uint8_t*>(a.devicePointer);
 }
 
 int enqueue_uploads(pk_handle* h, Slot& s, const uint8_t* payload, size_t meta_bytes,
@@ -288,6 +306,11 @@ int pk_init(int device, const pk_table* tbl, const pk_config* cfg, pk_handle** o
         PK_INIT_CUDA(cudaMalloc(&s.d_scratch, n * sizeof(pk::SegScratch)));
         PK_INIT_CUDA(cudaMemset(s.d_scratch, 0, n * sizeof(pk::SegScratch)));
         PK_INIT_CUDA(cudaHostAlloc(&s.h_meta, h->meta_cap, cudaHostAllocDefault));
+        PK_INIT_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&s.h_meta_dev), s.h_meta, 0));
+    }
+    {
+        const char* e = std::getenv("PK_DIRECT_BYTES");          // tuning aid; pk_set_direct_bytes at run time
+        h->direct_bytes = e && *e ? (uint64_t)std::atoll(e) : (16u << 20);
     }
     PK_INIT_CUDA(cudaDeviceSynchronize());
 #undef PK_INIT_CUDA
@@ -344,6 +367,33 @@ int pk_submit(pk_handle* h, uint32_t slot, const uint8_t* payload, const uint64_
     s.staged = false;
     int rc = prepare(h, s, pay_off, pay_len, names, name_off, n, &meta_bytes, &pb, &pbytes);
     if (rc) return rc;
+    // Small batch in page-locked memory: no copies at all.  The kernel reads the payload and the
+    // metadata blob straight out of host memory and writes its records straight into `out`, so the
+    // call is ONE launch instead of copy, copy, launch, copy — each of which costs a few µs of
+    // submission and completion latency that a small batch cannot amortise.
+    if (pbytes + meta_bytes <= h->direct_bytes && s.params.n_extra == 0) {
+        const uint8_t* d_pay = pbytes ? device_view(h, payload + pb, pbytes) : s.d_payload;
+        const uint8_t* d_out = device_view(h, out, (size_t)n * sizeof(pk_decision));
+        if (d_pay && d_out) {
+            pk::RouteParams P = s.params;
+            // the metadata sections: same offsets, in the host copy of the blob
+            auto in_host_blob = [&](const void* q) {
+                return s.h_meta_dev + (static_cast<const uint8_t*>(q) - s.d_meta);
+            };
+            P.payload  = d_pay;
+            P.pay_off  = reinterpret_cast<const uint64_t*>(in_host_blob(P.pay_off));
+            P.pay_len  = reinterpret_cast<const uint32_t*>(in_host_blob(P.pay_len));
+            P.name_off = reinterpret_cast<const uint32_t*>(in_host_blob(P.name_off));
+            P.names    = in_host_blob(P.names);
+            P.out      = reinterpret_cast<pk_decision*>(const_cast<uint8_t*>(d_out));
+            PK_CUDA(h, pk::launch_route(P, s.max_len, h->num_sms, s.stream));
+            ++h->launches;
+            ++h->direct_batches;
+            PK_CUDA(h, cudaEventRecord(s.done, s.stream));
+            s.inflight = true;                                             // nothing resident: staged stays false
+            return PK_OK;
+        }
+    }
     rc = enqueue_uploads(h, s, payload, meta_bytes, pb, pbytes);
     if (rc) return rc;
     rc = launch_slot(h, s, s.stream);
@@ -501,14 +551,28 @@ void* pk_host_alloc(pk_handle* h, size_t bytes)
     void* p = nullptr;
     cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocPortable);
     if (e != cudaSuccess) { h->last_cuda = (int)e; (void)cudaGetLastError(); return nullptr; }
+    h->pinned.emplace_back(static_cast<const uint8_t*>(p), bytes);
     return p;
 }
 
 void pk_host_free(pk_handle* h, void* p)
 {
     if (!p) return;
-    if (h) cudaSetDevice(h->device);
+    if (h) {
+        cudaSetDevice(h->device);
+        for (size_t k = 0; k < h->pinned.size(); ++k)
+            if (h->pinned[k].first == p) { h->pinned.erase(h->pinned.begin() + (ptrdiff_t)k); break; }
+    }
     cudaFreeHost(p);
 }
+
+int pk_set_direct_bytes(pk_handle* h, uint64_t bytes)
+{
+    if (!h) return PK_ERR_ARG;
+    h->direct_bytes = bytes;
+    return PK_OK;
+}
+
+uint64_t pk_direct_count(const pk_handle* h) { return h ? h->direct_batches : 0; }
 
 }  // extern "C"

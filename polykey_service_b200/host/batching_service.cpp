@@ -10,6 +10,14 @@ namespace polykey {
 namespace {
 inline uint64_t round16(uint64_t x) { return (x + 15u) & ~uint64_t(15); }
 using Clock = std::chrono::steady_clock;
+inline void cpu_relax()
+{
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#else
+    std::this_thread::yield();
+#endif
+}
 }  // namespace
 
 // ---------------------------------------------------------------- CudaBackend ------------
@@ -116,12 +124,21 @@ Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, c
         std::lock_guard<std::mutex> g(s->mu);
         if (stopping_.load()) return Result{nullptr, std::string("routing stage is shut down")};
         s->q.push_back(&p);
+        s->queued.store((uint32_t)s->q.size(), std::memory_order_release);
     }
     s->cv.notify_one();
-    {
-        std::unique_lock<std::mutex> w(s->done_mu);         // block this RPC's thread only
-        s->done_cv.wait(w, [&] { return p.done; });
+    // Wait for the decision: poll first while few callers are waiting (the batch comes back in
+    // tens of µs), then sleep.  `done` is the flusher's last access to p, so returning on it is safe.
+    const uint32_t ahead = s->waiting.fetch_add(1, std::memory_order_relaxed);
+    if (ahead < cfg_.caller_spin_max_waiters && cfg_.caller_spin_us) {
+        const auto until = Clock::now() + std::chrono::microseconds(cfg_.caller_spin_us);
+        while (!p.done.load(std::memory_order_acquire) && Clock::now() < until) cpu_relax();
     }
+    if (!p.done.load(std::memory_order_acquire)) {
+        std::unique_lock<std::mutex> w(s->done_mu);         // block this RPC's thread only
+        s->done_cv.wait(w, [&] { return p.done.load(std::memory_order_acquire); });
+    }
+    s->waiting.fetch_sub(1, std::memory_order_relaxed);
 
     if (p.rc != 0) {
         // plain error: server.go:37-40 returns it verbatim (gRPC Unknown)
@@ -177,7 +194,7 @@ void BatchingService::complete(Shard* s, Arena& a, int rc)
             Pending* p = a.reqs[i];
             p->rc = rc;
             if (rc == 0) p->decision = a.out[i];
-            p->done = true;
+            p->done.store(true, std::memory_order_release);  // p may be gone from here on
         }
     }
     s->done_cv.notify_all();
@@ -208,8 +225,18 @@ void BatchingService::flusher(Shard* s)
                 continue;
             }
             if (stopping_.load()) return;
-            s->cv.wait(lk, [&] { return !s->q.empty() || stopping_.load(); });
-            if (s->q.empty()) return;
+            // closed-loop callers come back within microseconds of their last answer: poll for
+            // them before paying for a futex sleep and its wake-up
+            lk.unlock();
+            const auto spin_until = Clock::now() + std::chrono::microseconds(cfg_.flusher_spin_us);
+            while (s->queued.load(std::memory_order_acquire) == 0 && !stopping_.load() && Clock::now() < spin_until)
+                cpu_relax();
+            lk.lock();
+            if (s->q.empty()) {
+                if (stopping_.load()) return;
+                s->cv.wait(lk, [&] { return !s->q.empty() || stopping_.load(); });
+                if (s->q.empty()) return;
+            }
         }
         // a batch is open: wait for it to fill or for the deadline of its first request
         const auto deadline = Clock::now() + std::chrono::microseconds(cfg_.max_wait_us);
@@ -218,7 +245,14 @@ void BatchingService::flusher(Shard* s)
         while (!full && !stopping_.load()) {
             const size_t before = s->q.size();
             const auto until = std::min(deadline, Clock::now() + idle);
-            s->cv.wait_until(lk, until);
+            if (idle <= std::chrono::microseconds(100)) {
+                // a short window is polled: a timed futex wait of 20 µs returns after 70 (timer slack)
+                lk.unlock();
+                while (s->queued.load(std::memory_order_acquire) == before && Clock::now() < until) cpu_relax();
+                lk.lock();
+            } else {
+                s->cv.wait_until(lk, until);
+            }
             full = s->q.size() >= cfg_.max_batch;
             if (full) break;
             const auto now = Clock::now();
@@ -246,6 +280,7 @@ void BatchingService::flusher(Shard* s)
             at += sz;
             ++n;
         }
+        s->queued.store((uint32_t)s->q.size(), std::memory_order_release);
         ++s->st.batches;
         s->st.requests += n;
         if (full) ++s->st.flush_full; else if (went_idle) ++s->st.flush_idle; else ++s->st.flush_deadline;

@@ -72,6 +72,12 @@ struct BatchingConfig {
     uint32_t max_wait_us = 200;            // deadline from the first queued request
     uint32_t idle_flush_us = 20;           // flush earlier once no request has arrived for this long
                                            // (a closed population of callers is all queued by then)
+    // Waiting without the kernel's help.  A futex sleep costs 10-70 µs to get out of (wake-up
+    // latency, timer slack) — more than the GPU takes to route a small batch — so short waits poll:
+    uint32_t flusher_spin_us = 100;        // an idle flusher polls its queue this long before it sleeps
+    uint32_t caller_spin_us = 150;         // a caller polls for its decision this long before it sleeps ...
+    uint32_t caller_spin_max_waiters = 8;  // ... unless more callers than this are already waiting (they would
+                                           // only steal cores from each other and from the flusher)
     uint64_t max_payload_bytes = 32u << 20;
     uint32_t max_name_bytes_per_request = 64;
     // One summary record per routed batch: the reference writes three
@@ -105,7 +111,7 @@ private:
         std::string payload;
         pk_decision decision{};
         int rc = 0;
-        bool done = false;                  // guarded by Shard::done_mu
+        std::atomic<bool> done{false};      // set (release) under Shard::done_mu as the flusher's LAST access
     };
     struct Arena {                          // one per backend slot
         uint8_t* payload = nullptr;
@@ -124,6 +130,8 @@ private:
         std::mutex mu;
         std::condition_variable cv;
         std::deque<Pending*> q;
+        std::atomic<uint32_t> queued{0};    // q.size(), readable without the lock (polling flusher)
+        std::atomic<uint32_t> waiting{0};   // callers blocked in ExecuteTool on this shard
         std::vector<Arena> arenas;
         std::thread th;
         BatchingStats st;

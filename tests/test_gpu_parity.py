@@ -212,6 +212,54 @@ def test_async_slots_and_resident_form(pk, router, oracle):
                              oracle.route_batch(t, batches[(s + 1) % 3], threads=8)[1], f"resident {s}")
 
 
+def test_small_batches_skip_the_copies(pk, oracle):
+    """A small batch in page-locked buffers is routed by ONE launch on the caller's memory (no
+    H2D / D2H copies): same records; pageable buffers, long requests, big batches and a zero
+    threshold all take the copying path."""
+    t = oracle.default_table()
+    r = pk.Router(device=0, max_requests=4096, max_payload_bytes=16 << 20, n_slots=2)
+    try:
+        r.set_direct_bytes(256 << 10)                 # the default is 16 MiB; a small one keeps the cases small
+        buf = r.host_alloc(4 << 20)
+        out = np.frombuffer(r.host_alloc(24 * 4096), dtype=pk.DECISION_DTYPE)
+        seen = r.direct_count
+        for k, (n, lo, hi, mode) in enumerate([(1, 0, 0, 0), (1, 16, 16, 0), (3, 0, 100, 2), (64, 0, 3000, 0),
+                                                (100, 2048, 2048, 1), (257, 0, 700, 3), (17, 0, 16384, 4)]):
+            b = oracle.gen_batch(7000 + k, n, lo, hi, mode=mode, payload_out=buf)
+            want = oracle.route_batch(t, b, threads=4)[1]
+            out[:] = 0
+            got = r.route_batch(b, out=out[:n])
+            assert_records_equal(got, want, f"direct case {k}")
+            seen += 1
+            assert r.direct_count == seen, k
+            # submit / wait on the other slot, twice in a row
+            for _ in range(2):
+                out[:n] = 0
+                r.submit(1, b, out[:n])
+                r.wait(1)
+                assert_records_equal(out[:n], want, f"direct submit case {k}")
+            seen += 2
+            assert r.direct_count == seen
+            with pytest.raises(pk.PkError):
+                r.launch(1)                                   # nothing was staged on the device
+        b = oracle.gen_batch(7100, 64, 0, 3000, mode=0)                                  # pageable payload
+        assert_records_equal(r.route_batch(b), oracle.route_batch(t, b, threads=4)[1], "pageable")
+        b = oracle.gen_batch(7101, 8, 16385, 30000, mode=0, payload_out=buf)             # long requests
+        assert_records_equal(r.route_batch(b, out=out[:8]), oracle.route_batch(t, b, threads=4)[1], "long")
+        b = oracle.gen_batch(7102, 1024, 2048, 2048, mode=0, payload_out=buf)            # 2 MiB > threshold
+        assert_records_equal(r.route_batch(b, out=out[:1024]), oracle.route_batch(t, b, threads=4)[1], "big")
+        assert r.direct_count == seen
+        r.set_direct_bytes(1 << 40)                                                      # ... unless asked to
+        assert_records_equal(r.route_batch(b, out=out[:1024]), oracle.route_batch(t, b, threads=4)[1], "big direct")
+        assert r.direct_count == seen + 1
+        r.set_direct_bytes(0)
+        b = oracle.gen_batch(7103, 4, 100, 100, mode=0, payload_out=buf)
+        assert_records_equal(r.route_batch(b, out=out[:4]), oracle.route_batch(t, b, threads=4)[1], "off")
+        assert r.direct_count == seen + 1
+    finally:
+        r.close()
+
+
 def test_programmatic_dependent_launch(pk, oracle):
     """PK_LAUNCH_PDL: consecutive launches of one stream may overlap.  Same records as the oracle
     for plain launches and for a graph chain; a slot with long requests (which owns per-request

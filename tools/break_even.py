@@ -31,9 +31,12 @@ def med(f, reps):
     return ts[len(ts) // 2] * 1e6
 
 
+DEFAULT_DIRECT = 16 << 20      # pk_abi.cu's default for pk_set_direct_bytes
+
+
 def main():
     plen = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
-    sizes = [1, 4, 16, 64, 256, 1024, 4096, 16384, 65536]
+    sizes = [1, 4, 8, 16, 32, 64, 256, 1024, 4096, 16384, 65536]
     cores = os.cpu_count() or 1
     table = O.default_table()
     rows = []
@@ -54,6 +57,16 @@ def main():
         while time.perf_counter() < t_end:
             r.route_batch(batches[0], out=outs[0][:n])
         gpu_sync = med(lambda: r.route_batch(batches[0], out=outs[0][:n]), reps)
+        # the two paths forced: copies (H2D, H2D, launch, D2H) and no copies (the kernel works on the
+        # caller's page-locked buffers); the default above picks by batch bytes (pk_set_direct_bytes)
+        r.set_direct_bytes(0)
+        gpu_sync_copy = med(lambda: r.route_batch(batches[0], out=outs[0][:n]), reps)
+        r.set_direct_bytes(1 << 40)
+        before = r.direct_count
+        got = r.route_batch(batches[0], out=outs[0][:n])
+        assert (got == want).all() and r.direct_count == before + 1
+        gpu_sync_direct = med(lambda: r.route_batch(batches[0], out=outs[0][:n]), reps)
+        r.set_direct_bytes(DEFAULT_DIRECT)
 
         def pipe(k=reps):
             infl = [False] * 3
@@ -70,10 +83,20 @@ def main():
         t0 = time.perf_counter()
         pipe(reps)
         gpu_pipe = (time.perf_counter() - t0) / reps * 1e6
+        pipe_forced = {}
+        for label, thr in (("copy", 0), ("direct", 1 << 40)):
+            r.set_direct_bytes(thr)
+            pipe(6)
+            t0 = time.perf_counter()
+            pipe(reps)
+            pipe_forced[label] = (time.perf_counter() - t0) / reps * 1e6
+        r.set_direct_bytes(DEFAULT_DIRECT)
         cpu_b_all = med(lambda: O.route_batch(table, batches[0], threads=cores, fast=True), max(5, reps // 4))
         cpu_b_1 = med(lambda: O.route_batch(table, batches[0], threads=1, fast=True), max(5, reps // 8))
         cpu_a_1 = med(lambda: O.route_batch(table, batches[0], threads=1, switch_only=True), max(5, reps // 4))
-        rows.append({"n": n, "gpu_sync_us": gpu_sync, "gpu_pipe_us": gpu_pipe, "cpu_b_all_us": cpu_b_all,
+        rows.append({"n": n, "gpu_sync_us": gpu_sync, "gpu_sync_copy_us": gpu_sync_copy,
+                     "gpu_sync_direct_us": gpu_sync_direct, "gpu_pipe_us": gpu_pipe,
+                     "gpu_pipe_copy_us": pipe_forced["copy"], "gpu_pipe_direct_us": pipe_forced["direct"], "cpu_b_all_us": cpu_b_all,
                      "cpu_b_1core_us": cpu_b_1, "cpu_b_best_us": min(cpu_b_all, cpu_b_1), "cpu_a_1core_us": cpu_a_1})
         print(rows[-1], file=sys.stderr, flush=True)
         r.close()

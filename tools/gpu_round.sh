@@ -10,7 +10,8 @@ timeout 900 python bench.py > gpurun_out/bench_c1.json 2> gpurun_out/bench_c1.er
 timeout 900 python bench.py --impl reference --steps 400 --warmup 10 > gpurun_out/bench_ref_c1.json 2> gpurun_out/bench_ref_c1.err; echo "bench ref rc=$?"
 timeout 900 python bench.py --workload c2 --steps 2000 --warmup 10 > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "bench c2 rc=$?"
 timeout 900 python bench.py --workload c3 --steps 60 --warmup 5 > gpurun_out/bench_c3.json 2> gpurun_out/bench_c3.err; echo "bench c3 rc=$?"
-timeout 900 python tools/break_even.py 2048 > gpurun_out/break_even_2k.json 2> gpurun_out/break_even_2k.err; echo "break-even rc=$?"
+timeout 900 python tools/break_even.py 2048 > gpurun_out/break_even_2k.json 2> gpurun_out/break_even_2k.err; echo "break-even 2k rc=$?"
+timeout 900 python tools/break_even.py 256 > gpurun_out/break_even_256.json 2> gpurun_out/break_even_256.err; echo "break-even 256 rc=$?"
 # ncu: launch list of the bench command, then full captures (each after its plain run exited 0)
 timeout 600 python bench.py --steps 20 --warmup 3 --no-cpu --no-prewarm > gpurun_out/plain_c1.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_c1.csv \
