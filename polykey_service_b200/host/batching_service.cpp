@@ -98,10 +98,59 @@ BatchingStats BatchingService::stats() const
     for (const auto& s : shards_) {
         std::lock_guard<std::mutex> g(s->mu);
         t.requests += s->st.requests; t.batches += s->st.batches; t.flush_full += s->st.flush_full;
-        t.flush_deadline += s->st.flush_deadline; t.flush_idle += s->st.flush_idle; t.errors += s->st.errors;
+        t.flush_deadline += s->st.flush_deadline; t.flush_idle += s->st.flush_idle; t.flush_eager += s->st.flush_eager;
+        t.errors += s->st.errors;
         if (s->st.max_batch_seen > t.max_batch_seen) t.max_batch_seen = s->st.max_batch_seen;
     }
     return t;
+}
+
+bool BatchingService::push(Shard* s, Pending* p)
+{
+    static std::atomic<unsigned> next_stripe{0};
+    static thread_local const unsigned stripe = next_stripe.fetch_add(1) % kInboxes;
+    Inbox& in = s->inbox[stripe];
+    {
+        std::lock_guard<std::mutex> g(in.mu);
+        if (in.closed) return false;
+        in.v.push_back(p);
+    }
+    s->queued.fetch_add(1);                                  // seq_cst: pairs with the flusher's sleeping / queued check
+    if (s->sleeping.load()) {                                // a polling flusher needs no wake-up call
+        { std::lock_guard<std::mutex> g(s->mu); }            // it is either before its predicate check or already waiting
+        s->cv.notify_one();
+    }
+    return true;
+}
+
+// Flusher only: move everything the inboxes hold into the backlog.  O(1) per inbox under its lock.
+size_t BatchingService::drain(Shard* s)
+{
+    static thread_local std::vector<Pending*> tmp;
+    size_t got = 0;
+    for (Inbox& in : s->inbox) {
+        {
+            std::lock_guard<std::mutex> g(in.mu);
+            if (in.v.empty()) continue;
+            tmp.swap(in.v);
+        }
+        s->backlog.insert(s->backlog.end(), tmp.begin(), tmp.end());
+        got += tmp.size();
+        tmp.clear();
+    }
+    return got;
+}
+
+// Flusher only, when stopping with nothing left: refuse further pushes.  false = something
+// slipped in meanwhile; drain it and try again.
+bool BatchingService::close_inboxes(Shard* s)
+{
+    for (Inbox& in : s->inbox) {
+        std::lock_guard<std::mutex> g(in.mu);
+        if (!in.v.empty()) return false;
+        in.closed = true;
+    }
+    return true;
 }
 
 Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, const Struct* parameters,
@@ -120,13 +169,7 @@ Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, c
 
     const uint64_t id = next_id_.fetch_add(1);
     Shard* s = shards_[id % shards_.size()].get();          // shard by request id, no exchange
-    {
-        std::lock_guard<std::mutex> g(s->mu);
-        if (stopping_.load()) return Result{nullptr, std::string("routing stage is shut down")};
-        s->q.push_back(&p);
-        s->queued.store((uint32_t)s->q.size(), std::memory_order_release);
-    }
-    s->cv.notify_one();
+    if (!push(s, &p)) return Result{nullptr, std::string("routing stage is shut down")};
     // Wait for the decision: poll first while few callers are waiting (the batch comes back in
     // tens of µs), then sleep.  `done` is the flusher's last access to p, so returning on it is safe.
     const uint32_t ahead = s->waiting.fetch_add(1, std::memory_order_relaxed);
@@ -179,6 +222,24 @@ void BatchingService::log_batch(const Shard* s, const Arena& a, int rc)
     cfg_.batch_log->push_back(std::move(line));
 }
 
+bool BatchingService::EnqueueAsync(AsyncRequest& r, std::string toolName, std::string payload)
+{
+    if (stopping_.load() || shards_.empty() || !healthy_.load()) return false;
+    if (round16(payload.size()) > cfg_.max_payload_bytes) return false;
+    r.name_ = std::move(toolName);
+    r.payload_ = std::move(payload);
+    r.rc_ = 0;
+    r.done_.store(false, std::memory_order_relaxed);
+    Pending* p = new Pending;
+    p->name = &r.name_;
+    p->payload.swap(r.payload_);
+    p->async = &r;
+    const uint64_t id = next_id_.fetch_add(1);
+    Shard* s = shards_[id % shards_.size()].get();
+    if (!push(s, p)) { r.payload_.swap(p->payload); delete p; r.done_.store(true); return false; }
+    return true;
+}
+
 void BatchingService::complete(Shard* s, Arena& a, int rc)
 {
     if (rc == 0) rc = s->be->wait((uint32_t)(&a - s->arenas.data()));
@@ -192,6 +253,14 @@ void BatchingService::complete(Shard* s, Arena& a, int rc)
         std::lock_guard<std::mutex> w(s->done_mu);
         for (size_t i = 0; i < a.reqs.size(); ++i) {
             Pending* p = a.reqs[i];
+            if (AsyncRequest* r = p->async) {
+                r->rc_ = rc;
+                if (rc == 0) r->decision_ = a.out[i];
+                r->payload_.swap(p->payload);                // hand the buffer back for reuse
+                delete p;
+                r->done_.store(true, std::memory_order_release);   // r may be reused from here on
+                continue;
+            }
             p->rc = rc;
             if (rc == 0) p->decision = a.out[i];
             p->done.store(true, std::memory_order_release);  // p may be gone from here on
@@ -217,79 +286,85 @@ void BatchingService::flusher(Shard* s)
     };
 
     for (;;) {
-        std::unique_lock<std::mutex> lk(s->mu);
-        if (s->q.empty()) {
-            if (!inflight.empty()) {                        // nothing new: finish the oldest batch now
-                lk.unlock();
-                finish_oldest();
-                continue;
-            }
-            if (stopping_.load()) return;
+        drain(s);
+        if (s->backlog.empty()) {
+            if (!inflight.empty()) { finish_oldest(); continue; }   // nothing new: finish the oldest batch now
             // closed-loop callers come back within microseconds of their last answer: poll for
             // them before paying for a futex sleep and its wake-up
-            lk.unlock();
             const auto spin_until = Clock::now() + std::chrono::microseconds(cfg_.flusher_spin_us);
             while (s->queued.load(std::memory_order_acquire) == 0 && !stopping_.load() && Clock::now() < spin_until)
                 cpu_relax();
-            lk.lock();
-            if (s->q.empty()) {
-                if (stopping_.load()) return;
-                s->cv.wait(lk, [&] { return !s->q.empty() || stopping_.load(); });
-                if (s->q.empty()) return;
+            if (s->queued.load() == 0) {
+                if (stopping_.load()) {
+                    if (close_inboxes(s)) return;
+                    continue;
+                }
+                std::unique_lock<std::mutex> lk(s->mu);
+                s->sleeping.store(true);                     // seq_cst, then the predicate: see push()
+                s->cv.wait(lk, [&] { return s->queued.load() != 0 || stopping_.load(); });
+                s->sleeping.store(false);
             }
+            continue;
         }
-        // a batch is open: wait for it to fill or for the deadline of its first request
+        // a batch is open: take it now (work-conserving), or hold it for more / the deadline of its first request
         const auto deadline = Clock::now() + std::chrono::microseconds(cfg_.max_wait_us);
         const auto idle = std::chrono::microseconds(cfg_.idle_flush_us ? cfg_.idle_flush_us : cfg_.max_wait_us);
-        bool full = s->q.size() >= cfg_.max_batch, went_idle = false;
-        while (!full && !stopping_.load()) {
-            const size_t before = s->q.size();
+        bool full = s->backlog.size() >= cfg_.max_batch, went_idle = false;
+        const bool eager = cfg_.eager_flush && !full;       // a busy GPU makes the next batch bigger by itself
+        while (!eager && !full && !stopping_.load()) {
+            const size_t before = s->backlog.size();
+            const uint32_t seen = s->queued.load(std::memory_order_acquire);
             const auto until = std::min(deadline, Clock::now() + idle);
             if (idle <= std::chrono::microseconds(100)) {
                 // a short window is polled: a timed futex wait of 20 µs returns after 70 (timer slack)
-                lk.unlock();
-                while (s->queued.load(std::memory_order_acquire) == before && Clock::now() < until) cpu_relax();
-                lk.lock();
+                while (s->queued.load(std::memory_order_acquire) == seen && Clock::now() < until) cpu_relax();
             } else {
-                s->cv.wait_until(lk, until);
+                std::unique_lock<std::mutex> lk(s->mu);
+                s->sleeping.store(true);
+                s->cv.wait_until(lk, until, [&] { return s->queued.load() != seen || stopping_.load(); });
+                s->sleeping.store(false);
             }
-            full = s->q.size() >= cfg_.max_batch;
+            drain(s);
+            full = s->backlog.size() >= cfg_.max_batch;
             if (full) break;
             const auto now = Clock::now();
             if (now >= deadline) break;
-            if (s->q.size() == before && now >= until) { went_idle = true; break; }   // nothing new arrived
+            if (s->backlog.size() == before && now >= until) { went_idle = true; break; }   // nothing new arrived
         }
         if (free_slots.empty()) {                           // free the slot we are about to reuse
-            lk.unlock();
             finish_oldest();
-            lk.lock();
+            drain(s);                                       // and take along what arrived meanwhile
         }
         const size_t slot = free_slots.back();
         free_slots.pop_back();
         Arena& a = s->arenas[slot];
         uint64_t at = 0;
         uint32_t n = 0;
-        while (!s->q.empty() && n < cfg_.max_batch) {
-            Pending* p = s->q.front();
+        a.bytes = 0;
+        while (!s->backlog.empty() && n < cfg_.max_batch) {
+            Pending* p = s->backlog.front();
             const uint64_t sz = round16(p->payload.size());
             if (at + sz > cfg_.max_payload_bytes) break;    // arena full: the rest goes to the next batch
-            s->q.pop_front();
+            s->backlog.pop_front();
             a.pay_off[n] = at;
             a.pay_len[n] = (uint32_t)p->payload.size();
+            a.bytes += p->payload.size();
             a.reqs.push_back(p);
             at += sz;
             ++n;
         }
-        s->queued.store((uint32_t)s->q.size(), std::memory_order_release);
-        ++s->st.batches;
-        s->st.requests += n;
-        if (full) ++s->st.flush_full; else if (went_idle) ++s->st.flush_idle; else ++s->st.flush_deadline;
-        a.trigger = full ? "full" : went_idle ? "idle" : "deadline";
-        a.bytes = 0;
-        for (const Pending* p : a.reqs) a.bytes += p->payload.size();
+        s->queued.fetch_sub(n);
+        const bool was_full = n >= cfg_.max_batch;          // (an eager batch may have filled while a slot was awaited)
+        a.trigger = (full || was_full) ? "full" : eager ? "eager" : went_idle ? "idle" : "deadline";
         a.t_submit_ns = std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now().time_since_epoch()).count();
-        if (n > s->st.max_batch_seen) s->st.max_batch_seen = n;
-        lk.unlock();
+        {
+            std::lock_guard<std::mutex> g(s->mu);
+            ++s->st.batches;
+            s->st.requests += n;
+            if (full || was_full) ++s->st.flush_full; else if (eager) ++s->st.flush_eager;
+            else if (went_idle) ++s->st.flush_idle; else ++s->st.flush_deadline;
+            if (n > s->st.max_batch_seen) s->st.max_batch_seen = n;
+        }
 
         // pack outside the lock: one memcpy per request into the (pinned) arena — gRPC buffers
         // live on the caller's heap and cannot be DMA sources

@@ -204,6 +204,40 @@ static void test_batching(uint32_t n_gpus, uint32_t threads, uint32_t per_thread
                 (unsigned long long)st.flush_idle, (unsigned long long)st.max_batch_seen);
 }
 
+// EnqueueAsync: the non-blocking half an event-loop server (or an open-loop load generator) uses.
+static void test_async()
+{
+    auto inner = NewMockService();
+    OracleBackend be0(2), be1(2);
+    BatchingConfig cfg; cfg.max_batch = 64; cfg.max_wait_us = 200; cfg.max_payload_bytes = 1 << 20;
+    BatchingService svc(inner.get(), {&be0, &be1}, cfg);
+    static const char* names[] = {"example_tool", "struct_tool", "file_tool", "nope"};
+    std::vector<AsyncRequest> ring(512);
+    std::vector<std::string> payloads(ring.size());
+    uint32_t bad = 0;
+    for (int round = 0; round < 3; ++round) {                                        // requests are reusable
+        for (size_t i = 0; i < ring.size(); ++i) {
+            payloads[i] = "{\"prompt\":\"";
+            for (size_t k = 0; k < (i * 7 + round) % 90; ++k) payloads[i] += "tok" + std::to_string(k) + " ";
+            payloads[i] += "\"}";
+            CHECK(ring[i].done());
+            CHECK(svc.EnqueueAsync(ring[i], names[i & 3], payloads[i]));
+        }
+        for (size_t i = 0; i < ring.size(); ++i) {
+            while (!ring[i].done()) std::this_thread::yield();
+            const pk_decision want = oracle_one(be0.table_, names[i & 3], payloads[i]);
+            if (ring[i].rc() != 0 || std::memcmp(&want, &ring[i].decision(), sizeof want) != 0) ++bad;
+        }
+    }
+    CHECK(bad == 0);
+    CHECK(be0.requests > 0 && be1.requests > 0 && be0.requests + be1.requests == 3 * ring.size());
+    AsyncRequest big;
+    CHECK(!svc.EnqueueAsync(big, "example_tool", std::string((2 << 20), 'x')) && big.done());   // over the arena: refused
+    svc.Shutdown();
+    AsyncRequest late;
+    CHECK(!svc.EnqueueAsync(late, "example_tool", "{}") && late.done());                       // after Shutdown: refused
+}
+
 static void test_device_error_path()
 {
     auto inner = NewMockService();
@@ -250,6 +284,7 @@ int main(int argc, char** argv)
     test_batching(1, 16, 120, 32);
     test_batching(2, 16, 120, 64);
     test_batching(4, 32, 60, 4096);
+    test_async();
     test_device_error_path();
     test_cuda_backend_fails_loudly();
     std::printf(g_fail ? "HOST TESTS FAILED (%d)\n" : "HOST TESTS OK\n", g_fail);
