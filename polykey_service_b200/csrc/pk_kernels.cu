@@ -49,6 +49,10 @@ namespace {
 
 constexpr int      kWarpsPerCta = 8;
 constexpr int      kThreads     = kWarpsPerCta * 32;
+#ifndef PK_TINY_PRE
+#define PK_TINY_PRE 1      // tiny-payload path: requests whose loads are in flight per lane group (at 32
+                           // registers a deeper prefetch spills: measured C2 8.43 / 8.56 / 8.96 µs for 1 / 2 / 4)
+#endif
 constexpr int      kUnroll      = PK_UNROLL;  // 128-bit loads in flight per lane
 constexpr unsigned kFull        = 0xFFFFFFFFu;
 constexpr int      kPartialSlots = 32 * 65;   // >= G * (R + 1) for every (G, R) launch_route picks
@@ -336,7 +340,7 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
 {
     static_assert(!kWarpFinal || G == 32, "latency mode finalises with the full warp");
     __shared__ uint64_t psum[kPartialSlots];     // [k][R+1]: lane-in-group k's digest for request i
-    __shared__ uint32_t ptok[kPartialSlots];
+    __shared__ uint16_t ptok[kPartialSlots];      // a lane sees at most 512 bytes of a segment: its count fits 16 bits
     __shared__ DevTable s_tbl;                   // the routing table, staged once per CTA
     __shared__ __align__(16) uint8_t s_names[kNameStage];   // this CTA's tool names, when they fit
 
@@ -406,10 +410,10 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
             if (lane < 16u && lane * 128u < len0)
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(pay0 + lane * 128u));
         }
-        names_staged = names_sz <= kNameStage;
-        if (names_staged)
-            for (uint32_t j = threadIdx.x; j < names_sz; j += kThreads) s_names[j] = __ldg(P.names + names_lo + j);
     }
+    names_staged = names_sz <= kNameStage;
+    if (names_staged)
+        for (uint32_t j = threadIdx.x; j < names_sz; j += kThreads) s_names[j] = __ldg(P.names + names_lo + j);
     if (threadIdx.x < sizeof(DevTable) / 16) reinterpret_cast<uint4*>(&s_tbl)[threadIdx.x] = tbl_part;
 
     // ---- phase 1: scan (first segment of) each request ----
@@ -425,11 +429,11 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
                 continue;
             }
             psum[lane * ld + i] = digest;
-            ptok[lane * ld + i] = tok;
+            ptok[lane * ld + i] = (uint16_t)tok;
         }
     } else {
         // tiny payloads: one block per lane, kPre requests' loads in flight per lane group
-        constexpr uint32_t kPre = 4;
+        constexpr uint32_t kPre = PK_TINY_PRE;
         constexpr uint32_t kStride = kWarpsPerCta * kGroups;
         for (uint32_t i0 = wid * kGroups + grp; i0 < r_here; i0 += kPre * kStride) {
             uint32_t len[kPre];
@@ -454,7 +458,7 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
                     uint32_t tok;
                     scan_tiny(x[u], len[u], lig, P.one, digest, tok);
                     psum[lig * ld + i] = digest;
-                    ptok[lig * ld + i] = tok;
+                    ptok[lig * ld + i] = (uint16_t)tok;
                 }
             }
         }
@@ -475,8 +479,10 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
         }
         const uint32_t noff = __ldg(P.name_off + req);
         const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
-        const uint8_t* name = names_staged ? s_names + (noff - names_lo) : P.names + noff;
-        decide_call(&s_tbl, name, nlen, len, sum, tok, P.out + req);
+        // table and names both in shared memory (the usual case): decide() inlined on shared-memory
+        // operands — LDS instead of generic loads through uniform-register descriptors
+        if (names_staged) decide(&s_tbl, s_names + (noff - names_lo), nlen, len, sum, tok, P.out + req);
+        else              decide_call(&s_tbl, P.names + noff, nlen, len, sum, tok, P.out + req);
     }
 }
 
