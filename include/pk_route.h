@@ -192,8 +192,8 @@ PK_API int  pk_wait(pk_handle* h, uint32_t slot);
  * use_graph | PK_LAUNCH_PDL issues the same launches with programmatic stream serialization
  * (programmatic dependent launch): still one stream / one chain, but a kernel may start while
  * its predecessor drains — batches are independent; a batch with long requests, which owns
- * per-request scratch in its slot, waits for its predecessor first.  Stream order for what
- * follows is kept.
+ * per-request scratch in its slot, is launched without the attribute (it starts after its
+ * predecessor completed).  Stream order for what follows is kept.
  * pk_fetch copies the slot's records out (synchronous).                               */
 #define PK_LAUNCH_PDL 0x100
 PK_API int  pk_stage(pk_handle* h, uint32_t slot,

@@ -490,19 +490,17 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
 // arenas and the table and writes its own records — so the next kernel of the stream may start
 // while this one is still running: every CTA releases its dependents at once, and the launch
 // latency, the two dependent HBM round trips (offsets, then bytes) and the tail of one batch
-// overlap the body of its neighbours.  What two launches of the SAME slot share is that slot's
-// long-request scratch, so a batch with long requests waits for its predecessor before it starts;
-// every other batch waits at its END, which keeps stream order for whatever follows (a copy out
-// after kernel k sees kernels <= k complete) without holding anything back.
+// overlap the body of its neighbours.  The wait for the predecessor is the LAST instruction,
+// which keeps stream order for whatever follows (a copy out after kernel k sees kernels <= k
+// complete) without holding anything back.  What two launches of the SAME slot share is that
+// slot's long-request scratch, so launch_route never sets pdl for a batch with long requests —
+// those are bandwidth-bound launches of hundreds of µs that have nothing to gain from overlap.
 template <int G, bool kWarpFinal>
 __global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : PK_MIN_CTAS_TINY) route_kernel(const RouteParams P)
 {
-    if (P.pdl) {
-        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-        if (P.n_extra != 0u) asm volatile("griddepcontrol.wait;" ::: "memory");
-    }
+    if (P.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     route_body<G, kWarpFinal>(P);
-    if (P.pdl && P.n_extra == 0u) asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (P.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 #if PK_TMA
@@ -565,6 +563,7 @@ cudaError_t launch_one(const RouteParams& p, uint32_t ctas, cudaStream_t stream)
 cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl)
 {
     if (p.n == 0) return cudaSuccess;
+    pdl = pdl && p.n_extra == 0u;       // long requests share their slot's scratch between launches: no overlap
     // lanes per request: a full warp, or a half / quarter warp when every payload fits one step
     const int G = max_len <= 8u * kBlockBytes ? 8 : max_len <= 16u * kBlockBytes ? 16 : 32;
     const uint32_t r_min = kWarpsPerCta * (32u / G);          // one request per lane group per pass

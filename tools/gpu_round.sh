@@ -9,7 +9,7 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smok
 timeout 900 python bench.py > gpurun_out/bench_c1.json 2> gpurun_out/bench_c1.err; echo "bench c1 (defaults) rc=$?"
 timeout 900 python bench.py --impl reference --steps 400 --warmup 10 > gpurun_out/bench_ref_c1.json 2> gpurun_out/bench_ref_c1.err; echo "bench ref rc=$?"
 timeout 900 python bench.py --workload c2 --steps 2000 --warmup 10 > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "bench c2 rc=$?"
-timeout 900 python bench.py --workload c3 --steps 60 --warmup 5 > gpurun_out/bench_c3.json 2> gpurun_out/bench_c3.err; echo "bench c3 rc=$?"
+timeout 900 python bench.py --workload c3 --steps 300 --warmup 60 > gpurun_out/bench_c3.json 2> gpurun_out/bench_c3.err; echo "bench c3 rc=$?"
 timeout 900 python tools/break_even.py 2048 > gpurun_out/break_even_2k.json 2> gpurun_out/break_even_2k.err; echo "break-even 2k rc=$?"
 timeout 900 python tools/break_even.py 256 > gpurun_out/break_even_256.json 2> gpurun_out/break_even_256.err; echo "break-even 256 rc=$?"
 # ncu: launch list of the bench command, then full captures (each after its plain run exited 0)
