@@ -164,17 +164,23 @@ static int main_open(int argc, char** argv)
     cfg.max_payload_bytes = (uint64_t)cfg.max_batch * ((payload_bytes + 64 + 15) & ~size_t(15));
     pk_table table;
     pk_default_table(&table);
-    std::unique_ptr<RouteBackend> dev;
-    if (const char* e = std::getenv("PK_NULL_BACKEND_US")) {
-        dev.reset(new NullBackend(std::atof(e)));
-        std::fprintf(stderr, "NULL backend: front-end measurement only, nothing is routed\n");
-    } else {
-        auto* cb = new CudaBackend(0, table, cfg.max_batch, cfg.max_payload_bytes, 3);
-        dev.reset(cb);
-        if (!cb->ok()) { std::fprintf(stderr, "no CUDA backend (status %d): there is no CPU fallback\n", cb->status()); return 1; }
+    // PK_BACKENDS=N: one backend (flusher, table replica) per GPU 0..N-1; requests shard by id
+    const unsigned nb = std::getenv("PK_BACKENDS") ? (unsigned)std::max(1, std::atoi(std::getenv("PK_BACKENDS"))) : 1u;
+    std::vector<std::unique_ptr<RouteBackend>> devs;
+    std::vector<RouteBackend*> bes;
+    for (unsigned g = 0; g < nb; ++g) {
+        if (const char* e = std::getenv("PK_NULL_BACKEND_US")) {
+            devs.emplace_back(new NullBackend(std::atof(e)));
+            if (g == 0) std::fprintf(stderr, "NULL backend: front-end measurement only, nothing is routed\n");
+        } else {
+            auto* cb = new CudaBackend((int)g, table, cfg.max_batch, cfg.max_payload_bytes, 3);
+            devs.emplace_back(cb);
+            if (!cb->ok()) { std::fprintf(stderr, "no CUDA backend on device %u (status %d): there is no CPU fallback\n", g, cb->status()); return 1; }
+        }
+        bes.push_back(devs.back().get());
     }
     auto inner = NewMockService();
-    BatchingService svc(inner.get(), {dev.get()}, cfg);
+    BatchingService svc(inner.get(), bes, cfg);
     run_open(svc, std::min(rate, 2e5), 0.3, payload_bytes, gens);     // warm
     const BatchingStats before = svc.stats();
     OpenResult r = run_open(svc, rate, seconds, payload_bytes, gens);
@@ -182,10 +188,10 @@ static int main_open(int argc, char** argv)
     svc.Shutdown();
     const double n = (double)r.lat_us.size();
     const uint64_t batches = st.batches - before.batches, reqs = st.requests - before.requests;
-    std::printf("{\"mode\": \"open-loop\", \"offered_per_s\": %.0f, \"generators\": %u, \"max_batch\": %u, \"max_wait_us\": %u, \"idle_flush_us\": %u, \"eager\": %d, "
+    std::printf("{\"mode\": \"open-loop\", \"backends\": %u, \"offered_per_s\": %.0f, \"generators\": %u, \"max_batch\": %u, \"max_wait_us\": %u, \"idle_flush_us\": %u, \"eager\": %d, "
                 "\"payload_bytes\": %zu, \"completed_per_s\": %.1f, \"dropped\": %llu, \"errors\": %llu, "
                 "\"latency_us\": {\"p50\": %.1f, \"p90\": %.1f, \"p99\": %.1f, \"p999\": %.1f, \"max\": %.1f}, \"batches\": %llu, \"mean_batch\": %.1f}\n",
-                rate, gens, cfg.max_batch, cfg.max_wait_us, cfg.idle_flush_us, (int)cfg.eager_flush, payload_bytes, n / r.seconds,
+                nb, rate, gens, cfg.max_batch, cfg.max_wait_us, cfg.idle_flush_us, (int)cfg.eager_flush, payload_bytes, n / r.seconds,
                 (unsigned long long)r.dropped, (unsigned long long)r.errors,
                 pct(r.lat_us, 0.50), pct(r.lat_us, 0.90), pct(r.lat_us, 0.99), pct(r.lat_us, 0.999),
                 r.lat_us.empty() ? 0.0 : *std::max_element(r.lat_us.begin(), r.lat_us.end()),
