@@ -3,7 +3,10 @@
 
 #include <sys/random.h>
 
+#include <algorithm>
 #include <cstring>
+#include <memory>
+#include <mutex>
 
 namespace polykey::security {
 
@@ -127,13 +130,67 @@ BatchResult GpuCipher::BatchDecrypt(const std::vector<Bytes>& ciphertexts)
 }
 
 // ---- the reference's four exported functions (cipher.go:92-141) ----
+// They take the key on every call.  Building a GPU context (device buffers, pinned arenas, the
+// key's tables) costs a millisecond or two — more than sealing 65,536 secrets — so the last few
+// contexts are kept, keyed by the key bytes, and rebuilt only when a call needs more room.
+namespace {
+struct Cached {
+    Bytes key;
+    uint32_t max_messages = 0;
+    uint64_t max_bytes = 0;
+    std::unique_ptr<GpuCipher> cipher;
+    uint64_t last_use = 0;
+};
+std::mutex g_cache_mu;                                    // also serialises calls: a context is one-caller-at-a-time
+std::vector<Cached> g_cache;
+uint64_t g_cache_clock = 0;
+constexpr size_t kCachedContexts = 4;
+
+// Caller holds g_cache_mu.
+GpuCipher& context_for(const Bytes& key, uint32_t messages, uint64_t bytes)
+{
+    Cached* slot = nullptr;
+    for (Cached& c : g_cache)
+        if (c.key.size() == key.size() && std::memcmp(c.key.data(), key.data(), key.size()) == 0) slot = &c;
+    if (!slot) {
+        if (g_cache.size() < kCachedContexts) {
+            g_cache.emplace_back();
+            slot = &g_cache.back();
+        } else {
+            slot = &g_cache[0];
+            for (Cached& c : g_cache) if (c.last_use < slot->last_use) slot = &c;
+            std::fill(slot->key.begin(), slot->key.end(), (uint8_t)0);
+            slot->cipher.reset();
+            slot->max_messages = 0;
+            slot->max_bytes = 0;
+        }
+        slot->key = key;
+    }
+    if (!slot->cipher || slot->cipher->init_error() || messages > slot->max_messages || bytes > slot->max_bytes) {
+        slot->cipher.reset();                             // free the old buffers before allocating larger ones
+        slot->max_messages = std::max<uint32_t>(messages + messages / 2, 1024u);
+        slot->max_bytes = std::max<uint64_t>(bytes + bytes / 2, 1u << 20);
+        slot->cipher.reset(new GpuCipher(key, 0, slot->max_messages, slot->max_bytes));
+    }
+    slot->last_use = ++g_cache_clock;
+    return *slot->cipher;
+}
+}  // namespace
+
+void DropCachedContexts()
+{
+    std::lock_guard<std::mutex> g(g_cache_mu);
+    for (Cached& c : g_cache) std::fill(c.key.begin(), c.key.end(), (uint8_t)0);
+    g_cache.clear();
+}
+
 BatchResult BatchEncrypt(const Bytes& key, const std::vector<Bytes>& plaintexts)
 {
     if (Error e = validateKey(key)) return {{}, e};       // cipher.go:111-113
     uint64_t bytes = 64;
     for (const Bytes& p : plaintexts) bytes += round16(p.size() + PK_GCM_OVERHEAD);
-    GpuCipher c(key, 0, (uint32_t)plaintexts.size() + 1, bytes);
-    return c.BatchEncrypt(plaintexts);
+    std::lock_guard<std::mutex> g(g_cache_mu);
+    return context_for(key, (uint32_t)plaintexts.size() + 1, bytes).BatchEncrypt(plaintexts);
 }
 
 BatchResult BatchDecrypt(const Bytes& key, const std::vector<Bytes>& ciphertexts)
@@ -141,8 +198,8 @@ BatchResult BatchDecrypt(const Bytes& key, const std::vector<Bytes>& ciphertexts
     if (Error e = validateKey(key)) return {{}, e};       // cipher.go:127-129
     uint64_t bytes = 64;
     for (const Bytes& c : ciphertexts) bytes += round16(c.size());
-    GpuCipher c(key, 0, (uint32_t)ciphertexts.size() + 1, bytes);
-    return c.BatchDecrypt(ciphertexts);
+    std::lock_guard<std::mutex> g(g_cache_mu);
+    return context_for(key, (uint32_t)ciphertexts.size() + 1, bytes).BatchDecrypt(ciphertexts);
 }
 
 namespace {

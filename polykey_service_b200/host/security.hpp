@@ -10,8 +10,9 @@
 //   generateNonce (crypto/rand)    cipher.go:25-31    getrandom(2)
 //
 // Same results and error behaviour: output nonce || ciphertext || tag; a batch fails as a whole
-// on the first bad item, with the reference's wrapped messages.  The free functions build a GPU
-// context per call (as the reference rebuilds its cipher per call); hold a GpuCipher to amortise it.
+// on the first bad item, with the reference's wrapped messages.  The free functions take the
+// key on every call like the reference's; the last few GPU contexts are cached by key (a context
+// costs more to build than a batch of 65,536 secrets to seal), DropCachedContexts() releases them.
 #pragma once
 #include <cstdint>
 #include <optional>
@@ -53,5 +54,6 @@ BytesResult Encrypt(const Bytes& key, const Bytes& plaintext);
 BytesResult Decrypt(const Bytes& key, const Bytes& ciphertext);
 BatchResult BatchEncrypt(const Bytes& key, const std::vector<Bytes>& plaintexts);
 BatchResult BatchDecrypt(const Bytes& key, const std::vector<Bytes>& ciphertexts);
+void DropCachedContexts();                              // zeroes and frees the cached per-key GPU contexts
 
 }  // namespace polykey::security

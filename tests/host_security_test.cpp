@@ -55,6 +55,26 @@ static void test_round_trip()
     std::vector<Bytes> nonces(pts.size(), Bytes(12, 9));
     BatchResult d1 = c.BatchEncrypt(pts, &nonces), d2 = c.BatchEncrypt(pts, &nonces);
     CHECK(!d1.error && d1.values == d2.values);
+    // the free functions cache contexts by key: more keys than cache slots, growing batches, and
+    // every result still opens under its own key only
+    std::vector<Bytes> keys;
+    std::vector<BatchResult> sealed;
+    for (int k = 0; k < 7; ++k) {
+        keys.emplace_back(32, (uint8_t)(0x50 + k));
+        std::vector<Bytes> batch((size_t)(3 + 700 * k), Bytes((size_t)(10 + 37 * k), (uint8_t)k));
+        sealed.push_back(BatchEncrypt(keys.back(), batch));
+        CHECK(!sealed.back().error && sealed.back().values.size() == batch.size());
+    }
+    for (int k = 6; k >= 0; --k) {
+        BatchResult d = BatchDecrypt(keys[(size_t)k], sealed[(size_t)k].values);
+        CHECK(!d.error && d.values.size() == (size_t)(3 + 700 * k) && d.values[0] == Bytes((size_t)(10 + 37 * k), (uint8_t)k));
+        BatchResult wrong = BatchDecrypt(keys[(size_t)((k + 1) % 7)], sealed[(size_t)k].values);
+        CHECK(wrong.error.has_value());
+    }
+    DropCachedContexts();
+    BatchResult again = BatchDecrypt(keys[2], sealed[2].values);                     // rebuilt on demand
+    CHECK(!again.error && again.values.size() == sealed[2].values.size());
+    DropCachedContexts();
 }
 
 int main(int argc, char** argv)
