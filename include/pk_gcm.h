@@ -76,6 +76,15 @@ PK_GCM_API int  pk_gcm_open_batch(pk_gcm* h, const uint8_t* sealed, const uint64
  * alone); 2..8: that many.                                                                        */
 PK_GCM_API int   pk_gcm_set_chunks(pk_gcm* h, uint32_t chunks);
 
+/* Small batches of long messages are sealed / opened in place.  When the arena bytes in + out come
+ * to at most `bytes` (default 4 MiB; 0 turns it off), every message is one the warp-per-message
+ * kernel takes (256 bytes or more for batches under 8,192 messages), and EVERY array of the call —
+ * arenas, offsets, lengths, nonces, status — is page-locked host memory the GPU can address
+ * (pk_gcm_host_alloc), no copy is issued: the kernel works on the caller's buffers over PCIe.
+ * pk_gcm_direct_count: batches so done.                                                          */
+PK_GCM_API int      pk_gcm_set_direct_bytes(pk_gcm* h, uint64_t bytes);
+PK_GCM_API uint64_t pk_gcm_direct_count(const pk_gcm* h);
+
 /* Page-locked host memory for the arenas (plain, sealed, offsets, nonces): copies to and from
  * pinned memory run at PCIe rate; pageable memory is staged by the driver at about a third of it.
  * Any host pointer is accepted by the calls above; these are the fast ones.  NULL on failure.     */

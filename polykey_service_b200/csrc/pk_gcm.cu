@@ -187,6 +187,9 @@ struct pk_gcm {
     uint64_t *d_in_off = nullptr, *d_out_off = nullptr;
     uint32_t *d_len = nullptr, *d_status = nullptr, *d_long = nullptr;
     uint32_t* h_long = nullptr;                 // pinned: indices of the messages the warp kernel takes
+    uint32_t* h_long_dev = nullptr;             // the same block as the GPU addresses it
+    uint64_t direct_bytes = 0;                  // largest batch (arena bytes in + out) sealed / opened in place
+    uint64_t direct_batches = 0;
     cudaStream_t stream = nullptr;              // copies in, and everything when a batch is not pipelined
     cudaStream_t s_run = nullptr, s_out = nullptr;   // kernels / copies out of a pipelined batch
     cudaEvent_t ev_in[8] = {}, ev_run[8] = {};  // chunk c: its input has landed / its kernels are done
@@ -213,6 +216,17 @@ bool is_pinned(const void* p)
     cudaPointerAttributes a{};
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
     return a.type == cudaMemoryTypeHost;
+}
+
+// The device-side address of page-locked host memory the GPU can read and write, else nullptr.
+template <typename T>
+T* device_view(T* p)
+{
+    if (!p) return nullptr;
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+    if (a.type != cudaMemoryTypeHost || !a.devicePointer) return nullptr;
+    return static_cast<T*>(a.devicePointer);
 }
 
 // Smallest message (bytes, as passed in) the warp-per-message kernel takes for a batch of n.
@@ -252,6 +266,46 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
     if (in_end && !in) return PK_GCM_ERR_ARG;
 
     PKG_CUDA(h, cudaSetDevice(h->device));
+    // A small batch of long messages whose every array is page-locked is sealed / opened IN PLACE:
+    // the warp-per-message kernel reads the caller's arena over PCIe, 512 contiguous bytes per
+    // warp-step, and writes the result straight back — one launch and a synchronisation instead of
+    // up to six stream operations around it (256 x 4 KiB: 0.071 ms against 0.135).  Not for the
+    // thread-per-message kernel: its 4-byte accesses, a message apart, are hopeless over PCIe
+    // (65,536 x 64 B: 3.2 ms against 0.33).
+    if (n_long == n && in_end + out_end <= h->direct_bytes) {
+        const uint8_t* v_in = in_end ? device_view(in) : h->d_in;
+        uint8_t* v_out = out_end ? device_view(out) : h->d_out;
+        const uint64_t* v_in_off = device_view(in_off);
+        const uint64_t* v_out_off = device_view(out_off);
+        const uint32_t* v_len = device_view(in_len);
+        const uint8_t* v_nonce = mode == 0 ? device_view(nonces) : h->d_nonce;
+        uint32_t* v_status = mode == 1 ? device_view(status) : h->d_status;
+        if (v_in && v_out && v_in_off && v_out_off && v_len && v_nonce && v_status) {
+            cudaStream_t st = h->stream;
+            PKG_CUDA(h, cudaEventRecord(h->ev0, st));
+            if (n_long < n) {
+                const uint32_t threads = n >= 148u * 64u ? 64u : 32u;
+                gcm_kernel<<<(n + threads - 1) / threads, threads, 0, st>>>(h->d_kc, v_in, v_in_off, v_len, v_nonce, v_out, v_out_off,
+                                                                               v_status, 0u, n, mode, long_bytes);
+                PKG_CUDA(h, cudaGetLastError());
+                ++h->launches;
+            }
+            if (n_long) {
+                const uint32_t warps = n_long >= 148u * 2u ? 2u : 1u;
+                gcm_long_kernel<<<(n_long + warps - 1) / warps, warps * 32u, kSmemBytes, st>>>(
+                    h->d_kc, v_in, v_in_off, v_len, v_nonce, v_out, v_out_off, v_status, h->h_long_dev, 0u, n_long, mode);
+                PKG_CUDA(h, cudaGetLastError());
+                ++h->launches;
+            }
+            PKG_CUDA(h, cudaEventRecord(h->ev1, st));
+            PKG_CUDA(h, cudaStreamSynchronize(st));
+            ++h->direct_batches;
+            if (mode == 1)
+                for (uint32_t i = 0; i < n; ++i)
+                    if (status[i] != 0) return PK_GCM_ERR_AUTH;
+            return PK_GCM_OK;
+        }
+    }
     // A large batch is cut into chunks of whole messages: the copy in of chunk c+1, the kernels of
     // chunk c and the copy out of chunk c-1 run at the same time (PCIe is full duplex), on three
     // streams chained by events.  Slots are in increasing order, so a chunk is one byte range of
@@ -390,6 +444,11 @@ int pk_gcm_init(int device, const uint8_t* key, uint32_t key_len, uint32_t max_m
     if (e == cudaSuccess) e = cudaMalloc(&h->d_status, n * 4);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_long, n * 4);
     if (e == cudaSuccess) e = cudaMallocHost(&h->h_long, n * 4);
+    if (e == cudaSuccess) e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->h_long_dev), h->h_long, 0);
+    {
+        const char* env = std::getenv("PK_GCM_DIRECT_BYTES");     // tuning aid; pk_gcm_set_direct_bytes at run time
+        h->direct_bytes = env && *env ? (uint64_t)std::atoll(env) : (4u << 20);
+    }
     std::memset(&kc, 0, sizeof kc);                       // do not leave key material on the stack
     if (e != cudaSuccess) {
         (void)cudaGetLastError();
@@ -453,6 +512,15 @@ void pk_gcm_host_free(pk_gcm* h, void* p)
     if (!h || !p) return;
     if (cudaFreeHost(p) != cudaSuccess) h->last_cuda = (int)cudaGetLastError();
 }
+
+int pk_gcm_set_direct_bytes(pk_gcm* h, uint64_t bytes)
+{
+    if (!h) return PK_GCM_ERR_ARG;
+    h->direct_bytes = bytes;
+    return PK_GCM_OK;
+}
+
+uint64_t pk_gcm_direct_count(const pk_gcm* h) { return h ? h->direct_batches : 0; }
 
 int pk_gcm_set_chunks(pk_gcm* h, uint32_t chunks)
 {

@@ -40,6 +40,8 @@ def lib() -> C.CDLL:
         L.pk_gcm_last_cuda_error.argtypes = [vp]
         L.pk_gcm_last_kernel_ms.argtypes, L.pk_gcm_last_kernel_ms.restype = [vp], C.c_float
         L.pk_gcm_set_chunks.argtypes = [vp, u32]
+        L.pk_gcm_set_direct_bytes.argtypes = [vp, C.c_uint64]
+        L.pk_gcm_direct_count.argtypes, L.pk_gcm_direct_count.restype = [vp], C.c_uint64
         L.pk_gcm_host_alloc.argtypes, L.pk_gcm_host_alloc.restype = [vp, C.c_size_t], vp
         L.pk_gcm_host_free.argtypes, L.pk_gcm_host_free.restype = [vp, vp], None
         _bound = True
@@ -82,6 +84,16 @@ class Gcm:
         rc = self._L.pk_gcm_set_chunks(self._h, chunks)
         if rc:
             raise GcmError(rc, "pk_gcm_set_chunks")
+
+    def set_direct_bytes(self, nbytes: int):
+        """Largest batch (arena bytes in + out) worked on in place, no copies; 0 = never."""
+        rc = self._L.pk_gcm_set_direct_bytes(self._h, int(nbytes))
+        if rc:
+            raise GcmError(rc, "pk_gcm_set_direct_bytes")
+
+    @property
+    def direct_count(self) -> int:
+        return int(self._L.pk_gcm_direct_count(self._h))
 
     def close(self):
         if self._h:

@@ -55,8 +55,12 @@ BatchResult GpuCipher::BatchEncrypt(const std::vector<Bytes>& plaintexts, const 
     if (init_error_) return {{}, init_error_};
     const uint32_t n = (uint32_t)plaintexts.size();
     if (n == 0) return {{}, std::nullopt};
-    std::vector<uint64_t> poff(n), soff(n);
-    std::vector<uint32_t> plen(n);
+    uint64_t* poff = reinterpret_cast<uint64_t*>(arena(2, (size_t)n * 8));
+    uint64_t* soff = reinterpret_cast<uint64_t*>(arena(3, (size_t)n * 8));
+    uint32_t* plen = reinterpret_cast<uint32_t*>(arena(4, (size_t)n * 4));
+    uint8_t* nonce_arr = arena(5, (size_t)n * PK_GCM_NONCE_BYTES);
+    if (!poff || !soff || !plen || !nonce_arr) return {{}, std::string("failed to encrypt plaintext: ") + pk_gcm_strerror(PK_GCM_ERR_CUDA)};
+    const size_t nonce_bytes = (size_t)n * PK_GCM_NONCE_BYTES;
     uint64_t pat = 0, sat = 0;
     for (uint32_t i = 0; i < n; ++i) {
         plen[i] = (uint32_t)plaintexts[i].size();
@@ -64,7 +68,6 @@ BatchResult GpuCipher::BatchEncrypt(const std::vector<Bytes>& plaintexts, const 
         pat += round16(plen[i]);
         sat += round16((uint64_t)plen[i] + PK_GCM_OVERHEAD);
     }
-    Bytes nonce_arr((size_t)n * PK_GCM_NONCE_BYTES);
     uint8_t* plain = arena(0, pat + 16);
     uint8_t* sealed = arena(1, sat + 16);
     if (!plain || !sealed) return {{}, std::string("failed to encrypt plaintext: ") + pk_gcm_strerror(PK_GCM_ERR_CUDA)};
@@ -73,17 +76,17 @@ BatchResult GpuCipher::BatchEncrypt(const std::vector<Bytes>& plaintexts, const 
     if (nonces) {
         for (uint32_t i = 0; i < n; ++i) {
             if ((*nonces)[i].size() != PK_GCM_NONCE_BYTES) return {{}, std::string("failed to encrypt plaintext: bad nonce length")};
-            std::memcpy(nonce_arr.data() + (size_t)i * PK_GCM_NONCE_BYTES, (*nonces)[i].data(), PK_GCM_NONCE_BYTES);
+            std::memcpy(nonce_arr + (size_t)i * PK_GCM_NONCE_BYTES, (*nonces)[i].data(), PK_GCM_NONCE_BYTES);
         }
     } else {
         size_t got = 0;                                  // generateNonce, cipher.go:25-31
-        while (got < nonce_arr.size()) {
-            const ssize_t r = getrandom(nonce_arr.data() + got, nonce_arr.size() - got, 0);
+        while (got < nonce_bytes) {
+            const ssize_t r = getrandom(nonce_arr + got, nonce_bytes - got, 0);
             if (r <= 0) return {{}, std::string("failed to encrypt plaintext: failed to generate nonce")};
             got += (size_t)r;
         }
     }
-    const int rc = pk_gcm_seal_batch(h_, plain, poff.data(), plen.data(), nonce_arr.data(), n, sealed, soff.data());
+    const int rc = pk_gcm_seal_batch(h_, plain, poff, plen, nonce_arr, n, sealed, soff);
     if (rc != PK_GCM_OK) return {{}, std::string("failed to encrypt plaintext: ") + pk_gcm_strerror(rc)};   // cipher.go:119
     BatchResult out;
     out.values.reserve(n);
@@ -97,8 +100,12 @@ BatchResult GpuCipher::BatchDecrypt(const std::vector<Bytes>& ciphertexts)
     if (init_error_) return {{}, init_error_};
     const uint32_t n = (uint32_t)ciphertexts.size();
     if (n == 0) return {{}, std::nullopt};
-    std::vector<uint64_t> soff(n), poff(n);
-    std::vector<uint32_t> slen(n), status(n, 0);
+    uint64_t* soff = reinterpret_cast<uint64_t*>(arena(2, (size_t)n * 8));
+    uint64_t* poff = reinterpret_cast<uint64_t*>(arena(3, (size_t)n * 8));
+    uint32_t* slen = reinterpret_cast<uint32_t*>(arena(4, (size_t)n * 4));
+    uint32_t* status = reinterpret_cast<uint32_t*>(arena(6, (size_t)n * 4));
+    if (!soff || !poff || !slen || !status) return {{}, std::string("failed to decrypt ciphertext: ") + pk_gcm_strerror(PK_GCM_ERR_CUDA)};
+    std::memset(status, 0, (size_t)n * 4);
     uint64_t sat = 0, pat = 0;
     for (uint32_t i = 0; i < n; ++i) {
         slen[i] = (uint32_t)ciphertexts[i].size();
@@ -111,7 +118,7 @@ BatchResult GpuCipher::BatchDecrypt(const std::vector<Bytes>& ciphertexts)
     if (!sealed || !plain) return {{}, std::string("failed to decrypt ciphertext: ") + pk_gcm_strerror(PK_GCM_ERR_CUDA)};
     for (uint32_t i = 0; i < n; ++i)
         if (slen[i]) std::memcpy(sealed + soff[i], ciphertexts[i].data(), slen[i]);
-    const int rc = pk_gcm_open_batch(h_, sealed, soff.data(), slen.data(), n, plain, poff.data(), status.data());
+    const int rc = pk_gcm_open_batch(h_, sealed, soff, slen, n, plain, poff, status);
     if (rc == PK_GCM_ERR_AUTH) {
         for (uint32_t i = 0; i < n; ++i) {               // the first failing item decides the message, cipher.go:133-137
             if (status[i] == 2)

@@ -42,12 +42,14 @@ public:
     BatchResult BatchEncrypt(const std::vector<Bytes>& plaintexts, const std::vector<Bytes>* nonces = nullptr);
     BatchResult BatchDecrypt(const std::vector<Bytes>& ciphertexts);
 private:
-    // grow-only page-locked arenas (pk_gcm_host_alloc): 0 = input, 1 = output
+    // grow-only page-locked arenas (pk_gcm_host_alloc): 0 = input, 1 = output, 2 / 3 = their slot
+    // offsets, 4 = lengths, 5 = nonces, 6 = status — every array of a call page-locked, so that
+    // small batches of long messages are worked on in place (pk_gcm_set_direct_bytes)
     uint8_t* arena(int which, size_t bytes);
     pk_gcm* h_ = nullptr;
     Error init_error_;
-    uint8_t* arena_[2] = {nullptr, nullptr};
-    size_t arena_bytes_[2] = {0, 0};
+    uint8_t* arena_[7] = {};
+    size_t arena_bytes_[7] = {};
 };
 
 BytesResult Encrypt(const Bytes& key, const Bytes& plaintext);

@@ -194,3 +194,56 @@ def test_pipelined_chunks_give_the_same_bytes(G):
             assert [int(i) for i in np.nonzero(e.value.status)[0]] == [1, n // 2, n - 1], chunks
         with pytest.raises(G.GcmError):
             g.set_chunks(9)
+
+
+def test_small_batches_in_place(G):
+    """Every array of the call page-locked and the batch small: sealed and opened in place (no
+    copies issued) — same bytes as OpenSSL, tampering still detected, pageable arrays or a zero
+    threshold take the copying path."""
+    rng = np.random.default_rng(17)
+    key = rng.bytes(32)
+    ref = AESGCM(key)
+    lens = np.array([256, 257, 271, 272, 273, 495, 496, 511, 512, 513, 1000, 4096, 5000] + rng.integers(256, 3000, 200).tolist(),
+                    dtype=np.uint32)                                              # all long: the warp-per-message kernel's
+    n = lens.size
+    with G.Gcm(key, max_messages=512, max_bytes=4 << 20) as g:
+        poff, ptotal = G.slots(lens)
+        soff, stotal = G.slots(lens.astype(np.uint64) + G.OVERHEAD)
+        pin = lambda a: (lambda d: (d.__setitem__(slice(0, a.size), a), d[:a.size])[1])(g.pinned(max(a.nbytes, 16), a.dtype))
+        plain = pin(rng.integers(0, 256, max(ptotal, 16), dtype=np.uint8))
+        nonces = pin(rng.integers(0, 256, 12 * n, dtype=np.uint8))
+        p_lens, p_poff, p_soff = pin(lens), pin(poff), pin(soff)
+        sealed = pin(np.zeros(max(stotal, 16), dtype=np.uint8))
+        before = g.direct_count
+        g.seal_arena(plain, p_poff, p_lens, nonces, sealed, p_soff)
+        assert g.direct_count == before + 1
+        for i in range(n):
+            nce = bytes(nonces[12 * i:12 * i + 12])
+            pt = bytes(plain[int(poff[i]):int(poff[i]) + int(lens[i])])
+            got = bytes(sealed[int(soff[i]):int(soff[i]) + int(lens[i]) + G.OVERHEAD])
+            assert got == nce + ref.encrypt(nce, pt, None), int(lens[i])
+        # open in place, then with one ciphertext bit flipped
+        slens = pin((lens + G.OVERHEAD).astype(np.uint32))
+        back = pin(np.zeros(max(ptotal, 16), dtype=np.uint8))
+        rc = g._L.pk_gcm_open_batch(g._h, sealed.ctypes.data, p_soff.ctypes.data, slens.ctypes.data, n, back.ctypes.data,
+                                    p_poff.ctypes.data, pin(np.zeros(n, dtype=np.uint32)).ctypes.data)
+        assert rc == 0 and g.direct_count == before + 2
+        for i in range(n):
+            assert bytes(back[int(poff[i]):int(poff[i]) + int(lens[i])]) == bytes(plain[int(poff[i]):int(poff[i]) + int(lens[i])])
+        sealed[int(soff[10]) + 20] ^= 1
+        status = pin(np.zeros(n, dtype=np.uint32))
+        rc = g._L.pk_gcm_open_batch(g._h, sealed.ctypes.data, p_soff.ctypes.data, slens.ctypes.data, n, back.ctypes.data,
+                                    p_poff.ctypes.data, status.ctypes.data)
+        assert rc == -10 and [int(i) for i in np.nonzero(status)[0]] == [10] and g.direct_count == before + 3
+        assert not back[int(poff[10]):int(poff[10]) + int(lens[10])].any()        # nothing released for the failed one
+        sealed[int(soff[10]) + 20] ^= 1
+        # pageable lengths array -> copies; one short message in the batch -> copies; threshold 0 -> copies
+        g.seal_arena(plain, p_poff, lens, nonces, sealed, p_soff)
+        p_lens[3] = 40
+        g.seal_arena(plain, p_poff, p_lens, nonces, sealed, p_soff)
+        nce, pt = bytes(nonces[36:48]), bytes(plain[int(poff[3]):int(poff[3]) + 40])
+        assert bytes(sealed[int(soff[3]):int(soff[3]) + 68]) == nce + ref.encrypt(nce, pt, None)
+        p_lens[3] = lens[3]
+        g.set_direct_bytes(0)
+        g.seal_arena(plain, p_poff, p_lens, nonces, sealed, p_soff)
+        assert g.direct_count == before + 3

@@ -4,7 +4,8 @@
 For each workload: seal a batch on the GPU through the C ABI (host buffers in and out), check it
 bit-exactly against OpenSSL, and time
   gpu_e2e_ms     one pk_gcm_seal_batch call (copies + kernel + copies), median, pageable arenas
-  gpu_e2e_pinned_ms  the same with page-locked arenas (pk_gcm_host_alloc);  _serial: chunking off
+  gpu_e2e_pinned_ms  the same with page-locked arenas (pk_gcm_host_alloc), library defaults;
+                     _serial: copies, chunking off;  _copies: copies, chunked;  gpu_e2e_inplace_ms: no copies
   gpu_kernel_ms  the kernel alone (CUDA events on its stream)
   cpu_ref_ms     OpenSSL with a fresh cipher per message — what BatchEncrypt does
                  (internal/adapters/security/cipher.go:116-122) — all cores / 1 core
@@ -81,6 +82,7 @@ def main():
             for dst, src in zip(pin, (plain, poff, plen, nonces, sealed, soff)):
                 dst[:src.size] = src
             p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff = (d[:s_.size] for d, s_ in zip(pin, (plain, poff, plen, nonces, sealed, soff)))
+            g.set_direct_bytes(0)                                # copies, one chunk
             p_sealed[:] = 0
             g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff)
             if not (np.asarray(p_sealed) == sealed).all():
@@ -91,9 +93,20 @@ def main():
             g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff)
             if not (np.asarray(p_sealed) == sealed).all():
                 raise SystemExit(f"pipelined result differs for {name}")
+            e2e_pinned_copies = med(lambda: g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff), 30)
+            g.set_direct_bytes(1 << 40)                          # in place whatever the size
+            p_sealed[:] = 0
+            g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff)
+            if not (np.asarray(p_sealed) == sealed).all():
+                raise SystemExit(f"in-place result differs for {name}")
+            e2e_inplace = med(lambda: g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff), 30)
+            g.set_direct_bytes(4 << 20)                          # the library's default
+            direct_before = g.direct_count
             e2e_pinned = med(lambda: g.seal_arena(p_plain, p_poff, p_plen, p_nonces, p_sealed, p_soff), 30)
+            in_place = g.direct_count > direct_before
         row = {"workload": name, "messages": n, "bytes": length, "payload_mb": n * length / 1e6,
-               "gpu_e2e_ms": e2e, "gpu_e2e_pinned_ms": e2e_pinned, "gpu_e2e_pinned_serial_ms": e2e_pinned_serial, "gpu_kernel_ms": kernel,
+               "gpu_e2e_ms": e2e, "gpu_e2e_pinned_ms": e2e_pinned, "gpu_e2e_pinned_serial_ms": e2e_pinned_serial, "gpu_e2e_pinned_copies_ms": e2e_pinned_copies,
+               "gpu_e2e_inplace_ms": e2e_inplace, "default_is_in_place": in_place, "gpu_kernel_ms": kernel,
                "cpu_ref_all_ms": med(lambda: cpu(cores, 1), 10), "cpu_ref_1core_ms": med(lambda: cpu(1, 1), 3),
                "cpu_reuse_all_ms": med(lambda: cpu(cores, 0), 10)}
         row["gpu_kernel_gbs"] = n * length / row["gpu_kernel_ms"] / 1e6
