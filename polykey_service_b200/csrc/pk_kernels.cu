@@ -56,6 +56,9 @@ constexpr int      kThreads     = kWarpsPerCta * 32;
 constexpr int      kUnroll      = PK_UNROLL;  // 128-bit loads in flight per lane
 constexpr unsigned kFull        = 0xFFFFFFFFu;
 constexpr int      kPartialSlots = 32 * 65;   // >= G * (R + 1) for every (G, R) launch_route picks
+constexpr uint32_t kTinyWarpMax = 8192;       // launch_route: batches of tiny payloads up to this size take a warp per request
+                                              // (serial µs, packed vs warp each: 1 request 4.3 / 2.2, 1,024: 6.1 / 2.9,
+                                              // 4,096: 6.3 / 3.8, 8,192: 6.5 / 5.6, 16,384: 7.7 / 13.2)
 constexpr uint32_t kNameStage   = 4096;       // bytes of tool names a CTA stages in shared memory
 
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p)
@@ -565,7 +568,12 @@ cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStrea
     if (p.n == 0) return cudaSuccess;
     pdl = pdl && p.n_extra == 0u;       // long requests share their slot's scratch between launches: no overlap
     // lanes per request: a full warp, or a half / quarter warp when every payload fits one step
-    const int G = max_len <= 8u * kBlockBytes ? 8 : max_len <= 16u * kBlockBytes ? 16 : 32;
+    int G = max_len <= 8u * kBlockBytes ? 8 : max_len <= 16u * kBlockBytes ? 16 : 32;
+    // Few tiny requests: a warp each (latency mode below) beats packing them 2 or 4 to a warp —
+    // the packed path pays a CTA barrier and a second phase that only pay off when warps are scarce.
+    static const char* const g_env = std::getenv("PK_TINY_WARP_MAX");      // tuning aid: largest such batch
+    const uint32_t tiny_warp_max = g_env ? (uint32_t)std::atoi(g_env) : kTinyWarpMax;
+    if (G < 32 && !pdl && p.n <= tiny_warp_max) G = 32;
     const uint32_t r_min = kWarpsPerCta * (32u / G);          // one request per lane group per pass
     const uint32_t r_max = G == 32 ? 64u : G == 16 ? 128u : 256u;   // G * (R + 1) <= kPartialSlots
     // enough CTAs to fill the machine (4 per SM resident), then as many requests per CTA as
