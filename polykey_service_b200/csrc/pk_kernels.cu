@@ -49,10 +49,6 @@ namespace {
 
 constexpr int      kWarpsPerCta = 8;
 constexpr int      kThreads     = kWarpsPerCta * 32;
-#ifndef PK_TINY_PRE
-#define PK_TINY_PRE 1      // tiny-payload path: requests whose loads are in flight per lane group (at 32
-                           // registers a deeper prefetch spills: measured C2 8.43 / 8.56 / 8.96 µs for 1 / 2 / 4)
-#endif
 constexpr int      kUnroll      = PK_UNROLL;  // 128-bit loads in flight per lane
 constexpr unsigned kFull        = 0xFFFFFFFFu;
 constexpr int      kPartialSlots = 32 * 65;   // >= G * (R + 1) for every (G, R) launch_route picks
@@ -435,35 +431,33 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
             ptok[lane * ld + i] = (uint16_t)tok;
         }
     } else {
-        // tiny payloads: one block per lane, kPre requests' loads in flight per lane group
-        constexpr uint32_t kPre = PK_TINY_PRE;
+        // tiny payloads: one block per lane.  The NEXT request's length and offset are loaded while
+        // this one is scanned, so an iteration waits for one memory round trip, not two; anything
+        // deeper (payload blocks of several requests in flight) spills at 32 registers and was
+        // slower — occupancy (8 CTAs per SM) does the rest of the latency hiding.
         constexpr uint32_t kStride = kWarpsPerCta * kGroups;
-        for (uint32_t i0 = wid * kGroups + grp; i0 < r_here; i0 += kPre * kStride) {
-            uint32_t len[kPre];
-            uint4 x[kPre];
-#pragma unroll
-            for (uint32_t u = 0; u < kPre; ++u) {
-                const uint32_t i = i0 + u * kStride;
-                len[u] = 0u;
-                x[u] = make_uint4(0u, 0u, 0u, 0u);
-                if (i < r_here) {
-                    len[u] = __ldg(P.pay_len + base_req + i);
-                    const uint32_t nblk = (len[u] >> 4) + ((len[u] & 15u) ? 1u : 0u);
-                    if (lig < nblk)
-                        x[u] = ldg_stream(reinterpret_cast<const uint4*>(P.payload + __ldg(P.pay_off + base_req + i)) + lig);
-                }
+        uint32_t i = wid * kGroups + grp;
+        uint32_t len_next = 0u;
+        uint64_t off_next = 0ull;
+        if (i < r_here) {
+            len_next = __ldg(P.pay_len + base_req + i);
+            off_next = __ldg(P.pay_off + base_req + i);
+        }
+        for (; i < r_here; i += kStride) {
+            const uint32_t len = len_next;
+            const uint8_t* pay = P.payload + off_next;
+            if (i + kStride < r_here) {
+                len_next = __ldg(P.pay_len + base_req + i + kStride);
+                off_next = __ldg(P.pay_off + base_req + i + kStride);
             }
-#pragma unroll
-            for (uint32_t u = 0; u < kPre; ++u) {
-                const uint32_t i = i0 + u * kStride;
-                if (i < r_here) {
-                    uint64_t digest;
-                    uint32_t tok;
-                    scan_tiny(x[u], len[u], lig, P.one, digest, tok);
-                    psum[lig * ld + i] = digest;
-                    ptok[lig * ld + i] = (uint16_t)tok;
-                }
-            }
+            const uint32_t nblk = (len >> 4) + ((len & 15u) ? 1u : 0u);
+            uint4 x = make_uint4(0u, 0u, 0u, 0u);
+            if (lig < nblk) x = ldg_stream(reinterpret_cast<const uint4*>(pay) + lig);
+            uint64_t digest;
+            uint32_t tok;
+            scan_tiny(x, len, lig, P.one, digest, tok);
+            psum[lig * ld + i] = digest;
+            ptok[lig * ld + i] = (uint16_t)tok;
         }
     }
     __syncthreads();
