@@ -417,12 +417,24 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
 
     // ---- phase 1: scan (first segment of) each request ----
     if (G == 32) {
+        // the next request's length and offset are loaded while this one is scanned
+        uint32_t len_next = 0u;
+        uint64_t off_next = 0ull;
+        if (wid < r_here) {
+            len_next = __ldg(P.pay_len + base_req + wid);
+            off_next = __ldg(P.pay_off + base_req + wid);
+        }
         for (uint32_t i = wid; i < r_here; i += kWarpsPerCta) {
             const uint32_t req = base_req + i;
-            const uint32_t len = __ldg(P.pay_len + req);
+            const uint32_t len = len_next;
+            const uint8_t* pay = P.payload + off_next;
+            if (i + kWarpsPerCta < r_here) {
+                len_next = __ldg(P.pay_len + req + kWarpsPerCta);
+                off_next = __ldg(P.pay_off + req + kWarpsPerCta);
+            }
             uint64_t digest;
             uint32_t tok;
-            scan_segment(P.payload + __ldg(P.pay_off + req), len, 0u, lane, P.one, digest, tok);
+            scan_segment(pay, len, 0u, lane, P.one, digest, tok);
             if (len > kSegBytes) {               // warp-uniform: the whole warp owns this request
                 fold_long_segment(P, req, len, digest, tok, lane);
                 continue;
