@@ -390,30 +390,13 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
     constexpr uint32_t kGroups = 32u / G;
     const uint32_t grp = lane / G, lig = lane % G;
 
-    // ---- prologue.  Phase 2 reads the table and the tool names; they are staged in shared
-    //      memory so that its dependent loads are LDS.  Order matters for latency: all
-    //      independent metadata loads are issued first; then (G == 32) each warp pulls the head
-    //      of its first payload towards L2, so that HBM fetch runs while the name bytes — which
-    //      need name_off first — are staged; only then does the scan start. ----
+    // ---- prologue.  Phase 2 reads the table and the tool names out of shared memory.  Only the
+    //      two offsets that bound this CTA's names are REQUESTED here; everything that depends on
+    //      a load — the name bytes, the table rows and their stores — waits until after the scan,
+    //      so no warp stalls on a staging round trip before its first payload load is out. ----
     static_assert(sizeof(DevTable) % 16 == 0, "DevTable is copied as uint4");
     const uint32_t names_lo = __ldg(P.name_off + base_req);
-    const uint32_t names_sz = __ldg(P.name_off + base_req + r_here) - names_lo;
-    uint4 tbl_part = make_uint4(0u, 0u, 0u, 0u);
-    if (threadIdx.x < sizeof(DevTable) / 16)
-        tbl_part = __ldg(reinterpret_cast<const uint4*>(P.table) + threadIdx.x);
-    bool names_staged = false;
-    if (G == 32) {
-        if (wid < r_here) {
-            const uint32_t len0 = __ldg(P.pay_len + base_req + wid);
-            const uint8_t* pay0 = P.payload + __ldg(P.pay_off + base_req + wid);
-            if (lane < 16u && lane * 128u < len0)
-                asm volatile("prefetch.global.L2 [%0];" :: "l"(pay0 + lane * 128u));
-        }
-    }
-    names_staged = names_sz <= kNameStage;
-    if (names_staged)
-        for (uint32_t j = threadIdx.x; j < names_sz; j += kThreads) s_names[j] = __ldg(P.names + names_lo + j);
-    if (threadIdx.x < sizeof(DevTable) / 16) reinterpret_cast<uint4*>(&s_tbl)[threadIdx.x] = tbl_part;
+    const uint32_t names_hi = __ldg(P.name_off + base_req + r_here);
 
     // ---- phase 1: scan (first segment of) each request ----
     if (G == 32) {
@@ -472,6 +455,27 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
             ptok[lig * ld + i] = (uint16_t)tok;
         }
     }
+    // ---- staging for phase 2 (its load latency hides behind the warps still scanning): the table,
+    //      and this CTA's tool names as aligned words (bytes at the two ragged ends, so nothing
+    //      outside [names_lo, names_hi) is read whatever the alignment of the caller's array) ----
+    if (threadIdx.x < sizeof(DevTable) / 16)
+        reinterpret_cast<uint4*>(&s_tbl)[threadIdx.x] = __ldg(reinterpret_cast<const uint4*>(P.table) + threadIdx.x);
+    const uint32_t names_sz = names_hi - names_lo;
+    const uint8_t* names_src = P.names + names_lo;
+    const uint32_t names_head = (uint32_t)(reinterpret_cast<uintptr_t>(names_src) & 3u);   // s_names[names_head] = first name byte
+    const bool names_staged = names_sz + 3u <= kNameStage;
+    if (names_staged) {
+        const uint8_t* al = names_src - names_head;
+        const uint32_t end = names_head + names_sz;
+        for (uint32_t w = threadIdx.x; w * 4u < end; w += kThreads) {
+            if (w * 4u >= names_head && w * 4u + 4u <= end) {
+                reinterpret_cast<uint32_t*>(s_names)[w] = __ldg(reinterpret_cast<const uint32_t*>(al) + w);
+            } else {
+                for (uint32_t b = w * 4u; b < w * 4u + 4u; ++b)
+                    if (b >= names_head && b < end) s_names[b] = __ldg(al + b);
+            }
+        }
+    }
     __syncthreads();
 
     // ---- phase 2: one thread per request ----
@@ -490,7 +494,7 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
         const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
         // table and names both in shared memory (the usual case): decide() inlined on shared-memory
         // operands — LDS instead of generic loads through uniform-register descriptors
-        if (names_staged) decide(&s_tbl, s_names + (noff - names_lo), nlen, len, sum, tok, P.out + req);
+        if (names_staged) decide(&s_tbl, s_names + names_head + (noff - names_lo), nlen, len, sum, tok, P.out + req);
         else              decide_call(&s_tbl, P.names + noff, nlen, len, sum, tok, P.out + req);
     }
 }
