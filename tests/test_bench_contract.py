@@ -60,3 +60,15 @@ def test_product_arm_line(oracle, pk):
     modes = d["issue_modes_ms_per_step"]
     assert {"pdl", "serial", "plain", "plain_pdl", "four_chains"} <= set(modes) and modes["pdl"] == d["ms_per_step"]
     assert d["serial"]["ms_per_step"] == modes["serial"] and 0 < d["serial"]["frac"] <= r["frac"] * 1.25
+
+
+@pytest.mark.gpu
+def test_c4_strong_scaling_line(oracle, pk):
+    """BASELINE configs[4] as a bench workload: one rank's pass over the whole 1M-request stream."""
+    d = run_bench("--workload", "c4", "--no-cpu", "--steps", "500", "--warmup", "5")
+    assert BASE_KEYS <= set(d) and d["scaling"] == "strong" and d["n_gpus"] == 1
+    c = d["config"]
+    assert c["batches_per_shard"] == 245 and c["shard_requests_rank0"] == 1_000_000 and "configs[4]" in c["workload"]
+    assert d["gpu_launches"] == d["steps"] and d["steps"] % 245 == 0
+    assert abs(d["value"] - 1e6 / (d["pass_ms"] / 1e3)) / d["value"] < 1e-9
+    assert 0 < d["e2e"]["value"] < d["value"] and 0 < d["roofline"]["frac"] < 1.2
