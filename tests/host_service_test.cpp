@@ -127,7 +127,7 @@ static void test_logging_interceptor()
 }
 
 static void test_batching(uint32_t n_gpus, uint32_t threads, uint32_t per_thread, uint32_t max_batch,
-                          bool cuda = false)
+                          bool cuda = false, bool hold = false)
 {
     auto inner = NewMockService();
     std::vector<std::unique_ptr<OracleBackend>> owned;
@@ -148,6 +148,7 @@ static void test_batching(uint32_t n_gpus, uint32_t threads, uint32_t per_thread
     cfg.max_batch = max_batch; cfg.max_wait_us = 300; cfg.max_payload_bytes = 1 << 20;
     std::vector<std::string> batch_log;
     cfg.batch_log = &batch_log;
+    cfg.eager_flush = !hold;                     // hold: keep the batch open for max_wait / idle_flush
     BatchingService svc(inner.get(), bes, cfg);
     CHECK(svc.healthy());
     static const char* names[] = {"example_tool", "struct_tool", "file_tool", "nope", "", "example_tool "};
@@ -273,6 +274,7 @@ int main(int argc, char** argv)
         // GPU box: the same batcher checks, answered by libpkroute.so through CudaBackend
         test_batching(1, 16, 120, 64, true);
         test_batching(2, 32, 60, 8, true);
+        test_batching(1, 16, 60, 64, true, true);
         std::printf(g_fail ? "HOST TESTS FAILED (%d)\n" : "HOST CUDA TESTS OK\n", g_fail);
         return g_fail ? 1 : 0;
     }
@@ -284,6 +286,8 @@ int main(int argc, char** argv)
     test_batching(1, 16, 120, 32);
     test_batching(2, 16, 120, 64);
     test_batching(4, 32, 60, 4096);
+    test_batching(1, 16, 60, 32, false, true);
+    test_batching(2, 32, 60, 8, false, true);
     test_async();
     test_device_error_path();
     test_cuda_backend_fails_loudly();
