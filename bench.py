@@ -1,20 +1,29 @@
 #!/usr/bin/env python
 """bench.py — routed requests/s of the batched routing stage on B200, beside the CPU path.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c1|c2|c3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c1|c2|c3|c4]
 
 A "step" is one pass of the hot path over one batch of synthetic requests.  The default
 workload is BASELINE.json configs[1] (C1): 4,096 tool-execution requests x 2 KB payloads,
 8 providers.  One JSON line is printed by rank 0:
 
-  value      whole-job requests/s with the batches already resident in HBM: K launches of the
-             fused kernel issued back to back (one CUDA graph of K kernel nodes) over a ring of
-             resident batches larger than L2, timed with CUDA events on the launching stream
-  e2e        the same metric through the C-ABI call a caller makes (pk_submit/pk_wait with HOST
-             buffers: H2D copies, kernel, D2H copy inside the timed region)
-  roofline   algorithmic bytes per launch / average launch duration, against the measured HBM
-             peak in MEASURED_PEAKS.json
-  cpu_baseline  the CPU oracle (work-equivalent port) timed on this box's host cores
+  value         whole-job requests/s with the batches already resident in HBM: K launches of the
+                fused kernel issued back to back (one CUDA graph of K kernel nodes) over a ring of
+                resident batches larger than L2, timed with CUDA events on the launching stream
+  steady_state  the same issue mode over >= 2,000 launches (fill and drain of the overlapped
+                pipeline amortised) — `value` at the driver's K, this one K-independent
+  e2e           the same metric through the C-ABI call a caller makes (pk_submit/pk_wait with HOST
+                buffers: H2D copies, kernel, D2H copy inside the timed region); e2e.with_pack
+                starts one step earlier, from per-request heap buffers, through the batching
+                front-end at the service.Service seam (producers copy into the pinned arena)
+  roofline      algorithmic bytes per launch / average launch duration, against the measured HBM
+                peak in MEASURED_PEAKS.json
+  workloads     (N=1) compact records for BASELINE configs[2] and [3]: C2 65,536 x 256 B and
+                C3 1,024 x 1 MiB — ms per launch, roofline fraction, e2e, parity gate
+  c4            BASELINE configs[4]: ONE stream of 1,000,000 requests x 2 KB sharded by request id
+                over the N ranks (strong scaling): time of a pass, kernel-only and end to end
+  latency       p50/p99 per-request routing latency through the batching front-end, open loop
+  cpu_baseline  the CPU port (work-equivalent scan+hash+select) timed on this box's host cores
 
 `--impl reference` times the CPU path alone (the oracle port — the Go reference cannot be
 built here: no Go toolchain, un-vendored spounge-proto) on the same workload.
@@ -25,9 +34,11 @@ own batches, no collective on the data path ("scaling": "weak").
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import statistics
+import subprocess
 import sys
 import threading
 import time
@@ -45,6 +56,13 @@ WORKLOADS = {
 }
 L2_BYTES = 126 << 20
 METRIC, UNIT = "routed_requests_per_sec", "requests/s"
+DTYPE = "u8/u32/u64 integer"
+PDL = 0x100                                                        # PK_LAUNCH_PDL, include/pk_route.h
+ISSUE = {"pdl": (1 | PDL, "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch "
+                          "(a kernel may start while its predecessor drains; batches are independent)"),
+         "serial": (1, "one CUDA graph of K kernel nodes in a chain, each starting after its predecessor completed"),
+         "plain": (0, "K plain launches")}
+C4_TOTAL = 1_000_000
 
 
 def log(*a):
@@ -72,11 +90,39 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
 
 
+def config_of(desc: str, n: int, plen: int) -> dict:
+    """The `config` object — the same keys in the product arm and the reference arm."""
+    return {"workload": desc, "batch_requests": n, "payload_bytes": plen, "providers": 8}
+
+
 def algorithmic_bytes(batch) -> int:
     """payload_len + name_len + 12 (offsets read) + 24 (record written) per request,
     the payload counted once."""
     n = int(batch["pay_len"].size)
     return int(batch["pay_len"].sum()) + int(batch["name_off"][-1] - batch["name_off"][0]) + 36 * n
+
+
+def kernel_sources_sha() -> str:
+    """Identifies the kernel code a DRAM-traffic capture belongs to."""
+    h = hashlib.sha256()
+    for f in ("pk_kernels.cu", "pk_kernels.cuh", "pk_spec.cuh"):
+        with open(os.path.join(ROOT, "polykey_service_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic(workload: str):
+    """dram__bytes_read + write per launch from the committed ncu capture — only while that capture
+    was taken from the kernel sources this run uses; otherwise null (never a stale constant)."""
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        t = json.load(open(tpath))
+    except Exception:
+        return None, "no ncu capture on file (profiles/ncu_traffic.json)"
+    if t.get("kernel_sources_sha") != kernel_sources_sha():
+        return None, (f"the ncu capture on file ({t.get('captured_at', 'round 1')}) is of older kernel sources "
+                      f"(sha {t.get('kernel_sources_sha')}): not quoted")
+    return t.get(workload), f"ncu --set full capture, {t.get('captured_at')}, same kernel sources (sha {t['kernel_sources_sha']})"
 
 
 class ClockSampler(threading.Thread):
@@ -163,6 +209,15 @@ def reduce_max(dist, local, x: float) -> float:
     return float(t.item())
 
 
+def reduce_sum(dist, local, x: float) -> float:
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
 def barrier_sync(dist, local):
     import torch
     if dist is not None:
@@ -171,20 +226,52 @@ def barrier_sync(dist, local):
         torch.cuda.synchronize(local)
 
 
+class Ctx:
+    """What every leg of the GPU arm needs."""
+
+    def __init__(self, args):
+        import torch
+        import polykey_service_b200 as pk
+        from oracle import pk_oracle as O            # cpu_baseline leg, parity gates and input generator only
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback "
+                             "(use --impl reference for the CPU arm)")
+        self.args, self.torch, self.pk, self.O = args, torch, pk, O
+        self.world, self.rank, self.local, self.dist = dist_setup(args.gpus)
+        O.build()
+        self.cores = os.cpu_count() or 1
+        self.gen_threads = min(self.cores, 16)
+        self.table = O.default_table()
+        self.peak, self.peak_src = measured_peak()
+        self.windows = []                             # (t0, t1) wall-clock windows of the timed regions
+
+    def max(self, x):
+        return reduce_max(self.dist, self.local, x)
+
+    def barrier(self):
+        barrier_sync(self.dist, self.local)
+
+
 # ------------------------------------------------------------------ CPU arms ------
 def cpu_arm(O, table, batch, threads: int, budget_s: float, switch_only: bool = False, min_reps: int = 2):
-    """Times the oracle over `batch` repeatedly for about budget_s; returns (requests/s, reps)."""
+    """Times the CPU port over `batch` repeatedly for about budget_s; returns (requests/s, reps)."""
     n = int(batch["pay_len"].size)
-    O.route_batch(table, batch, threads=threads, switch_only=switch_only, fast=True)      # warm
+    out = np.zeros(n, dtype=O.DECISION_DTYPE)                       # reused: no allocation in the timed loop
+    O.route_batch(table, batch, threads=threads, switch_only=switch_only, fast=True, out=out)      # warm
     reps, t0 = 0, time.perf_counter()
     while True:
-        rc, _ = O.route_batch(table, batch, threads=threads, switch_only=switch_only, fast=True)
+        rc, _ = O.route_batch(table, batch, threads=threads, switch_only=switch_only, fast=True, out=out)
         assert rc == 0
         reps += 1
         dt = time.perf_counter() - t0
-        if (dt >= budget_s and reps >= min_reps) or reps >= 100000:
+        if (dt >= budget_s and reps >= min_reps) or reps >= 1000000:
             break
     return n * reps / dt, reps
+
+
+def cpu_port_note(O, cores):
+    return (f"oracle/pk_cpu_fast.c: one fused pass (scan+hash+select), {O.fast_impl()} inner loop, "
+            f"persistent pool of {cores} threads, dynamic chunks")
 
 
 def run_reference(args):
@@ -200,74 +287,67 @@ def run_reference(args):
     # bounded sample: for C3 a step is 64 of the 1,024 requests (64 MiB), otherwise the full batch
     n_step = n if n * plen <= (64 << 20) else max(1, (64 << 20) // plen)
     batches = [O.gen_batch(O.SEED_BASE + 1 + i, n_step, plen, mode=0, threads=min(cores, 16)) for i in range(4)]
+    out = np.zeros(n_step, dtype=O.DECISION_DTYPE)
     # the efficient CPU port (oracle/pk_cpu_fast.c) is what is timed; check it against the plain
     # oracle once, outside the timed region
     assert (O.route_batch(table, batches[0], threads=cores, fast=True)[1] ==
             O.route_batch(table, batches[0], threads=cores)[1]).all()
     for w in range(args.warmup):
-        O.route_batch(table, batches[w % 4], threads=cores, fast=True)
+        O.route_batch(table, batches[w % 4], threads=cores, fast=True, out=out)
     t0 = time.perf_counter()
     for k in range(args.steps):
-        rc, _ = O.route_batch(table, batches[k % 4], threads=cores, fast=True)
+        rc, _ = O.route_batch(table, batches[k % 4], threads=cores, fast=True, out=out)
         assert rc == 0
     dt = time.perf_counter() - t0
     value = n_step * args.steps / dt
-    # CPU-A: the reference-faithful work; the threaded form spawns its threads per call, so for a
-    # 4,096-request batch one core is usually faster — report the better of the two
+    v_one, _ = cpu_arm(O, table, batches[0], 1, 1.5)
+    # CPU-A: the reference-faithful work (the switch only) — report the better of all cores / one
     sw_all, _ = cpu_arm(O, table, batches[0], cores, 1.0, switch_only=True)
     sw_one, _ = cpu_arm(O, table, batches[0], 1, 1.0, switch_only=True)
     sw, sw_cores = (sw_all, cores) if sw_all >= sw_one else (sw_one, 1)
-    sample = f"{args.steps} steps x {n_step} requests x {plen} B (oracle/pk_cpu_fast.c port, {cores} threads)"
+    sample = f"{args.steps} steps x {n_step} requests x {plen} B ({cpu_port_note(O, cores)})"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32/u64 integer",
-        "data": "synthetic", "config": {"workload": desc, "batch_requests": n_step, "payload_bytes": plen,
-                                        "providers": 8, "parallelism": "host threads, static partition"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": DTYPE,
+        "data": "synthetic", "config": config_of(desc, n, plen),
+        "parallelism": "host threads (persistent pool), requests in dynamic chunks",
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "one_core": v_one, "scaling_efficiency": value / (v_one * cores), "impl": O.fast_impl(),
+                         "sample_requests_per_step": n_step},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "reference_switch_only": {"value": sw, "unit": UNIT, "cores": sw_cores,
                                   "note": "CPU-A: only the work the Go reference does per request "
                                           "(mock.go:32-64 switch; payload never read)"},
         "note": "Go reference cannot be built on this box (no Go toolchain, un-vendored spounge-proto); "
-                "this is the C oracle port doing the work-equivalent scan+hash+select",
+                "this is the C port doing the work-equivalent scan+hash+select",
     }
     emit(line)
 
 
-# ------------------------------------------------------------------ GPU arm ------
-def run_gpu(args):
-    import torch
-    import polykey_service_b200 as pk
-    from oracle import pk_oracle as O            # cpu_baseline leg + input generator only
-
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback "
-                         "(use --impl reference for the CPU arm)")
-    world, rank, local, dist = dist_setup(args.gpus)
-    O.build()
-    n, plen, desc = WORKLOADS[args.workload]
-    cores = os.cpu_count() or 1
+# ------------------------------------------------------------------ GPU legs ------
+def resident_leg(ctx: Ctx, workload: str, steps: int, warmup: int, issue: str, all_modes: bool,
+                 steady_steps: int, depth: int, prewarm: bool = True):
+    """Stages a ring of batches larger than L2, checks slot 0 bit-exactly against the oracle, then
+    times `steps` launches issued as `issue` (device time, max over ranks).  Returns the router
+    (slots [ring, ring+depth) are left for the e2e leg) and the numbers."""
+    pk, O = ctx.pk, ctx.O
+    n, plen, desc = WORKLOADS[workload]
     batch_bytes = n * ((plen + 15) & ~15)
-
-    # ring of resident batches larger than L2 so every launch streams from HBM
     ring = max(2, min(64, -(-(2 * L2_BYTES + batch_bytes) // batch_bytes)))
     if batch_bytes > L2_BYTES:
         ring = 2
-    depth = 3                                      # e2e pipeline depth (slots in flight)
-    router = pk.Router(device=local, max_requests=n, max_payload_bytes=batch_bytes,
-                       n_slots=ring + depth)
-    log(f"[rank {rank}] workload {args.workload}: n={n} payload={plen} ring={ring} "
+    router = pk.Router(device=ctx.local, max_requests=n, max_payload_bytes=batch_bytes, n_slots=ring + depth)
+    log(f"[rank {ctx.rank}] workload {workload}: n={n} payload={plen} ring={ring} "
         f"({ring * batch_bytes / 2**20:.0f} MiB resident)")
 
     # request ids: rank r owns ids r, r+world, ... (req_id % G sharding); batch j of rank r starts at
     # a disjoint id range, so every rank routes different requests
     def make_batch(j, payload_out=None):
-        first_id = (rank * 1_000_003 + j) * n
-        return O.gen_batch(O.SEED_BASE + 1, n, plen, mode=0, first_id=first_id, threads=min(cores, 16),
+        first_id = (ctx.rank * 1_000_003 + j) * n
+        return O.gen_batch(O.SEED_BASE + 1, n, plen, mode=0, first_id=first_id, threads=ctx.gen_threads,
                            payload_out=payload_out)
 
-    table = O.default_table()
     check_batch = None
     for j in range(ring):
         b = make_batch(j)
@@ -279,60 +359,65 @@ def run_gpu(args):
     # correctness gate before timing anything: slot 0 against the oracle, bit-exact
     router.launch(0)
     got = router.fetch(0, n)
-    rc, want = O.route_batch(table, check_batch, threads=cores)
+    rc, want = O.route_batch(ctx.table, check_batch, threads=ctx.cores)
     assert rc == 0 and (got == want).all(), "GPU records differ from the oracle — refusing to time"
 
-    sampler = ClockSampler(local)
-    sampler.start()
     slots = list(range(ring))
-    PDL = 0x100                                                   # PK_LAUNCH_PDL, include/pk_route.h
-    issue = "plain" if args.no_graph else args.issue
-    ISSUE = {"pdl": (1 | PDL, "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch "
-                              "(a kernel may start while its predecessor drains; batches are independent)"),
-             "serial": (1, "one CUDA graph of K kernel nodes in a chain, each starting after its predecessor completed"),
-             "plain": (0, "K plain launches")}
     use_graph, issue_desc = ISSUE[issue]
-
     # bring clocks up, then the W warm-up steps
-    t_end = time.perf_counter() + (0.0 if args.no_prewarm else 0.4)
+    t_end = time.perf_counter() + (0.4 if prewarm else 0.0)
     while time.perf_counter() < t_end:
         router.launch_many(slots, 512, use_graph=False)
-    router.launch_many(slots, max(3, args.warmup), use_graph=use_graph)
+    router.launch_many(slots, max(3, warmup), use_graph=use_graph)
 
     # ---- timed: K steps, device-resident ----
     launches_before = router.launch_count
-    barrier_sync(dist, local)
+    ctx.barrier()
     w0 = time.perf_counter()
-    ms = router.launch_many(slots, args.steps, use_graph=use_graph)
-    torch.cuda.synchronize(local)
+    ms = router.launch_many(slots, steps, use_graph=use_graph)
+    ctx.torch.cuda.synchronize(ctx.local)
     w1 = time.perf_counter()
-    barrier_sync(dist, local)
+    ctx.barrier()
+    ctx.windows.append((w0, w1))
     launches = router.launch_count - launches_before
-    ms = reduce_max(dist, local, ms)
-    value = world * args.steps * n / (ms / 1e3)
-    per_launch_s = ms / 1e3 / args.steps
-    # the other issue modes, for the record (same K launches, same stream)
+    ms = ctx.max(ms)
+    res = {"n": n, "plen": plen, "desc": desc, "batch_bytes": batch_bytes, "ring": ring, "alg_bytes": alg_bytes,
+           "ms": ms, "steps": steps, "launches": int(launches), "issue": issue, "issue_desc": issue_desc,
+           "check_batch": check_batch, "make_batch": make_batch, "parity": True}
+    # the same issue mode over enough launches that fill and drain of the overlapped pipeline vanish
+    if steady_steps:
+        router.launch_many(slots, 64, use_graph=use_graph)
+        t0 = time.perf_counter()
+        ms_ss = ctx.max(router.launch_many(slots, steady_steps, use_graph=use_graph))
+        ctx.windows.append((t0, time.perf_counter()))
+        res["steady"] = (steady_steps, ms_ss)
     other = {}
-    for name, mode in (("pdl", 1 | PDL), ("serial", 1), ("plain", 0), ("plain_pdl", PDL), ("four_chains", 4)):
+    modes = (("pdl", 1 | PDL), ("serial", 1), ("plain", 0), ("plain_pdl", PDL), ("four_chains", 4)) if all_modes \
+        else (("serial", 1),)
+    for name, mode in modes:
         if mode != use_graph:
-            other[name] = reduce_max(dist, local, router.launch_many(slots, args.steps, use_graph=mode)) / args.steps
-    ms_serial = other.get("serial", ms / args.steps)
+            other[name] = ctx.max(router.launch_many(slots, steps, use_graph=mode)) / steps
+    res["other"] = other
+    return router, res
 
-    # ---- e2e: host buffers through pk_submit / pk_wait, copies inside the timed region ----
-    e2e_batches, host_bufs = [], []
-    for j in range(depth + 1):
+
+def e2e_leg(ctx: Ctx, router, res, depth: int, k_e2e: int, n_arenas: int, both_paths: bool, sync_latency: bool):
+    """pk_submit / pk_wait on HOST buffers, `depth` batches in flight: every step's payload and
+    metadata cross PCIe inside the timed region and its records come back."""
+    pk, O = ctx.pk, ctx.O
+    n, batch_bytes, ring = res["n"], res["batch_bytes"], res["ring"]
+    e2e_batches = []
+    for j in range(n_arenas):
         buf = router.host_alloc(batch_bytes + 64)                 # pinned arena owned by the C side
-        e2e_batches.append(make_batch(100 + j, payload_out=buf))
-        host_bufs.append(buf)
+        e2e_batches.append(res["make_batch"](100 + j, payload_out=buf))
     outs = [np.frombuffer(router.host_alloc(24 * n), dtype=pk.DECISION_DTYPE) for _ in range(depth)]
     e2e_slots = [ring + d for d in range(depth)]
-    meta_bytes = int(check_batch["pay_off"].nbytes + check_batch["pay_len"].nbytes +
-                     check_batch["name_off"].nbytes + check_batch["names"].nbytes)
-    h2d = int(check_batch["pay_off"][n - 1]) + int(check_batch["pay_len"][n - 1]) + meta_bytes
+    cb = res["check_batch"]
+    meta_bytes = int(cb["pay_off"].nbytes + cb["pay_len"].nbytes + cb["name_off"].nbytes + cb["names"].nbytes)
+    h2d = int(cb["pay_off"][n - 1]) + int(cb["pay_len"][n - 1]) + meta_bytes
     d2h = 24 * n
-    k_e2e = max(20, min(args.steps, int(3.0 / max(1e-5, (h2d / 20e9)))))   # ~3 s at a pessimistic 20 GB/s
 
-    def e2e_pipelined(k):
+    def pipelined(k):
         inflight = [False] * depth
         t0 = time.perf_counter()
         for s in range(k):
@@ -346,144 +431,107 @@ def run_gpu(args):
                 router.wait(e2e_slots[d])
         return time.perf_counter() - t0
 
-    e2e_pipelined(max(3, min(10, k_e2e)))                          # warm
-    barrier_sync(dist, local)
+    pipelined(max(3, min(10, k_e2e)))                               # warm
+    ctx.barrier()
     direct_before = router.direct_count
     e0 = time.perf_counter()
-    e2e_s = e2e_pipelined(k_e2e)
+    e2e_s = pipelined(k_e2e)
     e1 = time.perf_counter()
-    barrier_sync(dist, local)
-    used_direct = router.direct_count - direct_before == k_e2e       # the library's own choice for this batch size
-    e2e_s = reduce_max(dist, local, e2e_s)
-    e2e_value = world * k_e2e * n / e2e_s
-    rc, want = O.route_batch(table, e2e_batches[(k_e2e - 1) % len(e2e_batches)], threads=cores)
+    ctx.barrier()
+    ctx.windows.append((e0, e1))
+    used_direct = router.direct_count - direct_before == k_e2e      # the library's own choice for this batch size
+    e2e_s = ctx.max(e2e_s)
+    rc, want = O.route_batch(ctx.table, e2e_batches[(k_e2e - 1) % len(e2e_batches)], threads=ctx.cores)
     assert (outs[(k_e2e - 1) % depth] == want).all(), "e2e records differ from the oracle"
-    # the other transfer path, for the record (same call, same buffers)
-    router.set_direct_bytes(0 if used_direct else 1 << 40)
-    k_alt = max(10, k_e2e // 4)
-    e2e_pipelined(3)
-    barrier_sync(dist, local)
-    e2e_alt_s = reduce_max(dist, local, e2e_pipelined(k_alt)) / k_alt
-    router.set_direct_bytes(16 << 20)
     transfer = {True: "none issued: the kernel reads the page-locked arenas over PCIe and writes the records into the "
                       "caller's page-locked buffer (pk_set_direct_bytes, default for batches up to 16 MiB)",
                 False: "cudaMemcpyAsync H2D (payload, metadata) and D2H (records) around the kernel"}
-
-    # synchronous single-call latency (what one flush costs a waiting request)
-    lat = []
-    for s in range(min(k_e2e, 300)):
-        t0 = time.perf_counter()
-        router.route_batch(e2e_batches[s % len(e2e_batches)], out=outs[0])
-        lat.append((time.perf_counter() - t0) * 1e6)
-    lat.sort()
-    sampler.stop_flag = True
-    sampler.join(timeout=2)
-    clocks = sampler.summary([(w0, w1), (e0, e1)])
-
-    if rank != 0:
-        router.close()
-        return
-
-    # ---- CPU baseline on this box's host cores (rank 0, N=1 only) ----
-    cpu_baseline = None
-    extra_cpu = {}
-    if world == 1 and not args.no_cpu:
-        sample_batch = check_batch if batch_bytes <= (64 << 20) else make_sample(O, plen)
-        v_all, reps = cpu_arm(O, table, sample_batch, cores, 8.0)
-        v_one, _ = cpu_arm(O, table, sample_batch, 1, 4.0)
-        v_sw, _ = cpu_arm(O, table, sample_batch, cores, 1.5, switch_only=True)
-        v_sw1, _ = cpu_arm(O, table, sample_batch, 1, 1.0, switch_only=True)
-        cpu_baseline = {"value": v_all, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": f"{reps} passes over one batch of {int(sample_batch['pay_len'].size)} requests x {plen} B "
-                                  f"(about 8 s), oracle/pk_cpu_fast.c scan+hash+select, {cores} threads"}
-        extra_cpu = {"cpu_baseline_1core": {"value": v_one, "unit": UNIT, "cores": 1},
-                     "cpu_switch_only": {"value": v_sw, "unit": UNIT, "cores": cores,
-                                         "note": "CPU-A: what the Go reference actually does per request "
-                                                 "(mock.go:32-64 switch; never reads the payload)"},
-                     "cpu_switch_only_1core": {"value": v_sw1, "unit": UNIT, "cores": 1}}
-
-    peak, peak_src = measured_peak()
-    achieved = alg_bytes / per_launch_s / 1e9
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
-    if os.path.exists(tpath):
-        try:
-            traffic = json.load(open(tpath)).get(args.workload)
-        except Exception:
-            traffic = None
-    line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32/u64 integer", "data": "synthetic",
-        "config": {"workload": desc, "batch_requests": n, "payload_bytes": plen, "providers": 8,
-                   "parallelism": f"dp{world}: requests sharded by id, no collective",
-                   "l2": f"ring of {ring} resident batches = {ring * batch_bytes / 2**20:.0f} MiB > 126 MiB L2, "
-                         "launch k reads batch k mod ring",
-                   "issue": issue_desc + "; one stream, CUDA events on that stream"},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                     "kernel": "route_kernel (fused scan+hash+select)",
-                     "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_us": per_launch_s * 1e6},
-        "cpu_baseline": cpu_baseline,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": k_e2e, "pipeline_depth": depth, "ms_per_step": e2e_s / k_e2e * 1e3,
-                "api": "pk_submit/pk_wait, pinned host arenas", "copies": transfer[used_direct],
-                "other_path": {"copies": transfer[not used_direct], "ms_per_step": e2e_alt_s * 1e3,
-                               "value": world * n / e2e_alt_s, "unit": UNIT},
-                "sync_call_latency_us": {"p50": lat[len(lat) // 2], "p99": lat[min(len(lat) - 1, int(len(lat) * 0.99))],
-                                         "api": "pk_route_batch, one batch per call"}},
-        "gpu_launches": int(launches),
-        "clocks": clocks,
-        "issue_modes_ms_per_step": dict(other, **{issue: ms / args.steps}),
-        "serial": {"ms_per_step": ms_serial, "value": world * n / (ms_serial / 1e3), "unit": UNIT,
-                   "frac": alg_bytes / (ms_serial / 1e3) / 1e9 / peak,
-                   "note": "the same K launches with every kernel waiting for its predecessor to complete: what ONE "
-                           "batch costs on an idle GPU (launch + two dependent HBM round trips + drain)"},
-    }
-    line.update(extra_cpu)
-    emit(line)
-    router.close()
+    e2e = {"value": ctx.world * k_e2e * n / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "steps": k_e2e, "pipeline_depth": depth, "ms_per_step": e2e_s / k_e2e * 1e3,
+           "host_gbs_per_gpu": (h2d + d2h) / (e2e_s / k_e2e) / 1e9,
+           "api": "pk_submit/pk_wait, pinned host arenas", "copies": transfer[used_direct]}
+    if both_paths:
+        # the other transfer path, for the record (same call, same buffers)
+        router.set_direct_bytes(0 if used_direct else 1 << 40)
+        k_alt = max(10, k_e2e // 4)
+        pipelined(3)
+        ctx.barrier()
+        alt_s = ctx.max(pipelined(k_alt)) / k_alt
+        router.set_direct_bytes(16 << 20)
+        e2e["other_path"] = {"copies": transfer[not used_direct], "ms_per_step": alt_s * 1e3,
+                             "value": ctx.world * n / alt_s, "unit": UNIT}
+    if sync_latency:
+        # synchronous single-call latency (what one flush costs a waiting request)
+        lat = []
+        for s in range(min(k_e2e, 300)):
+            t0 = time.perf_counter()
+            router.route_batch(e2e_batches[s % len(e2e_batches)], out=outs[0])
+            lat.append((time.perf_counter() - t0) * 1e6)
+        lat.sort()
+        e2e["sync_call_latency_us"] = {"p50": lat[len(lat) // 2], "p99": lat[min(len(lat) - 1, int(len(lat) * 0.99))],
+                                       "api": "pk_route_batch, one batch per call"}
+    return e2e
 
 
-def make_sample(O, plen):
-    n_s = max(1, (64 << 20) // plen)
-    return O.gen_batch(O.SEED_BASE + 1, n_s, plen, mode=0, threads=16)
+def pcie_probe(ctx: Ctx, nbytes: int, reps: int = 40):
+    """The host ceiling an end-to-end step runs under: all ranks copy `nbytes` of page-locked host
+    memory to their GPU at the same time with plain cudaMemcpyAsync (and, separately, both
+    directions at once).  Device time, max over ranks."""
+    torch = ctx.torch
+    dev = torch.device("cuda", ctx.local)
+    h_in = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    h_out = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    d_in = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    d_out = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+    h_in.fill_(7)
+    s2 = torch.cuda.Stream(device=dev)
+
+    def timed(duplex):
+        for _ in range(3):
+            d_in.copy_(h_in, non_blocking=True)
+        ctx.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        s2.wait_stream(torch.cuda.current_stream(dev))
+        for _ in range(reps):
+            d_in.copy_(h_in, non_blocking=True)
+            if duplex:
+                with torch.cuda.stream(s2):
+                    h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.current_stream(dev).wait_stream(s2)
+        b.record()
+        torch.cuda.synchronize(dev)
+        return ctx.max(a.elapsed_time(b)) / 1e3
+
+    t_h2d = timed(False)
+    t_dup = timed(True)
+    per_rank = nbytes * reps / t_h2d / 1e9
+    return {"h2d_gbs_per_gpu": per_rank, "h2d_gbs_aggregate": per_rank * ctx.world,
+            "duplex_gbs_per_gpu_each_way": nbytes * reps / t_dup / 1e9,
+            "what": f"{ctx.world} rank(s) at once, {reps} x cudaMemcpyAsync of {nbytes} B from page-locked host memory "
+                    "(duplex: the same with a D2H copy of equal size on a second stream)"}
 
 
-
-# ------------------------------------------------------------------ C4: strong scaling ------
-C4_TOTAL = 1_000_000
-
-
-def run_gpu_c4(args):
+def c4_leg(ctx: Ctx, batch: int, steps: int, warmup: int, e2e_reps: int = 3, prewarm: bool = True):
     """BASELINE configs[4]: ONE stream of 1,000,000 requests x 2 KB sharded by request id over the
     G ranks (rank r owns r, r+G, ...; no exchange), each rank working through its shard in batches
-    of --c4-batch requests.  Strong scaling: the work is fixed, `value` = 1e6 / the slowest rank's
-    time for one pass over its shard.  A step is one batch on every rank."""
-    import torch
-    import polykey_service_b200 as pk
-    from oracle import pk_oracle as O
-
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
-    world, rank, local, dist = dist_setup(args.gpus)
-    O.build()
-    n, plen = args.c4_batch, 2048
-    cores = os.cpu_count() or 1
-    mine = len(range(rank, C4_TOTAL, world))                  # requests of this rank's shard
-    nb = -(-mine // n)                                        # its batches; the last one is ragged
+    of `batch` requests.  Strong scaling: the work is fixed, value = 1e6 / the slowest rank's time
+    for one pass over its shard."""
+    pk, O = ctx.pk, ctx.O
+    n, plen = batch, 2048
+    mine = len(range(ctx.rank, C4_TOTAL, ctx.world))           # requests of this rank's shard
+    nb = -(-mine // n)                                         # its batches; the last one is ragged
     batch_bytes = n * plen
     depth = 3
-    router = pk.Router(device=local, max_requests=n, max_payload_bytes=batch_bytes, n_slots=nb + depth)
-    table = O.default_table()
-    log(f"[rank {rank}] C4: shard of {mine} requests = {nb} batches of {n} ({nb * batch_bytes / 2**20:.0f} MiB resident)")
+    router = pk.Router(device=ctx.local, max_requests=n, max_payload_bytes=batch_bytes, n_slots=nb + depth)
+    log(f"[rank {ctx.rank}] C4: shard of {mine} requests = {nb} batches of {n} ({nb * batch_bytes / 2**20:.0f} MiB resident)")
 
     def shard_batch(j, payload_out=None):
         # rank-local numbering: the shard's k-th request is generated from id rank * 2^32 + k, so
         # shards are disjoint and the same whatever the batch size
         cnt = min(n, mine - j * n)
-        return O.gen_batch(O.SEED_BASE + 4, cnt, plen, mode=0, first_id=(rank << 32) + j * n,
-                           threads=min(cores, 16), payload_out=payload_out)
+        return O.gen_batch(O.SEED_BASE + 4, cnt, plen, mode=0, first_id=(ctx.rank << 32) + j * n,
+                           threads=ctx.gen_threads, payload_out=payload_out)
 
     first = last = None
     for j in range(nb):
@@ -496,28 +544,26 @@ def run_gpu_c4(args):
     for slot, b in ((0, first), (nb - 1, last)):              # correctness gate: full and ragged batch
         router.launch(slot)
         got = router.fetch(slot, int(b["pay_len"].size))
-        assert (got == O.route_batch(table, b, threads=cores)[1]).all(), "GPU records differ from the oracle"
-    alg_bytes = algorithmic_bytes(first) * (mine / n)        # per pass over the shard
+        assert (got == O.route_batch(ctx.table, b, threads=ctx.cores)[1]).all(), "GPU records differ from the oracle"
+    alg_pass = algorithmic_bytes(first) * (mine / n)         # per pass over the shard
 
-    sampler = ClockSampler(local)
-    sampler.start()
     slots = list(range(nb))
-    PDL = 0x100
-    reps = max(3, args.steps // nb)
-    t_end = time.perf_counter() + (0.0 if args.no_prewarm else 0.4)
+    reps = max(3, steps // nb)
+    t_end = time.perf_counter() + (0.4 if prewarm else 0.0)
     while time.perf_counter() < t_end:
         router.launch_many(slots, nb, use_graph=False)
-    router.launch_many(slots, nb * max(1, args.warmup // nb + 1), use_graph=1 | PDL)
+    router.launch_many(slots, nb * max(1, warmup // nb + 1), use_graph=1 | PDL)
     launches_before = router.launch_count
-    barrier_sync(dist, local)
+    ctx.barrier()
     w0 = time.perf_counter()
     ms = router.launch_many(slots, nb * reps, use_graph=1 | PDL)
-    torch.cuda.synchronize(local)
+    ctx.torch.cuda.synchronize(ctx.local)
     w1 = time.perf_counter()
-    barrier_sync(dist, local)
+    ctx.barrier()
+    ctx.windows.append((w0, w1))
     launches = router.launch_count - launches_before
-    pass_s = reduce_max(dist, local, ms) / 1e3 / reps          # slowest rank's time for ONE pass over its shard
-    ms_serial = reduce_max(dist, local, router.launch_many(slots, nb * reps, use_graph=1)) / reps
+    pass_s = ctx.max(ms) / 1e3 / reps                          # slowest rank's time for ONE pass over its shard
+    ms_serial = ctx.max(router.launch_many(slots, nb * reps, use_graph=1)) / reps
 
     # ---- e2e: the shard streamed from page-locked host arenas through pk_submit / pk_wait ----
     host = [shard_batch(j % nb, payload_out=router.host_alloc(batch_bytes + 64)) for j in range(depth + 1)]
@@ -542,50 +588,257 @@ def run_gpu_c4(args):
         return time.perf_counter() - t0
 
     e2e_pass()
-    barrier_sync(dist, local)
+    ctx.barrier()
     e0 = time.perf_counter()
-    e2e_reps = 3
     e2e_s = sum(e2e_pass() for _ in range(e2e_reps)) / e2e_reps
     e1 = time.perf_counter()
-    barrier_sync(dist, local)
-    e2e_s = reduce_max(dist, local, e2e_s)
+    ctx.barrier()
+    ctx.windows.append((e0, e1))
+    e2e_s = ctx.max(e2e_s)
+    meta = int(first["pay_off"].nbytes + first["pay_len"].nbytes + first["name_off"].nbytes + first["names"].nbytes)
+    router.close()
+    return {"first": first, "n": n, "plen": plen, "mine": mine, "nb": nb, "reps": reps, "batch_bytes": batch_bytes,
+            "pass_s": pass_s, "serial_pass_ms": ms_serial, "launches": int(launches), "alg_pass": alg_pass,
+            "e2e_s": e2e_s, "e2e_reps": e2e_reps, "meta": meta, "depth": depth}
+
+
+def c4_record(ctx: Ctx, c):
+    """The compact `c4` sub-record of the default line."""
+    return {"workload": f"C4: one stream of {C4_TOTAL} requests x {c['plen']} B sharded by request id over {ctx.world} GPU(s), "
+                        f"per-GPU batches of {c['n']} (BASELINE configs[4])",
+            "scaling": "strong", "value": C4_TOTAL / c["pass_s"], "unit": UNIT, "pass_ms": c["pass_s"] * 1e3,
+            "batches_per_shard": c["nb"], "shard_requests_rank0": c["mine"],
+            "frac": c["alg_pass"] / c["pass_s"] / 1e9 / ctx.peak,
+            "serial_pass_ms": c["serial_pass_ms"],
+            "e2e": {"value": C4_TOTAL / c["e2e_s"], "unit": UNIT, "pass_ms": c["e2e_s"] * 1e3,
+                    "h2d_bytes_per_step": c["batch_bytes"] + c["meta"], "d2h_bytes_per_step": 24 * c["n"],
+                    "pipeline_depth": c["depth"], "api": "pk_submit/pk_wait, pinned host arenas"},
+            "gpu_launches": c["launches"], "parity_gate": "first and last (ragged) batch of the shard bit-exact vs the oracle"}
+
+
+def frontend_leg(ctx: Ctx, seconds: float = 1.5):
+    """Through the service.Service seam: the C++ batching front-end (host/batching_service.cpp),
+    driven by host/latency_bench.cpp in ONE process with one backend (flusher, table replica) per
+    GPU — the shape of the reference's server (cmd/polykey/main.go:85-89).  Rank 0 runs it while the
+    other ranks wait; open loop, Poisson arrivals of 2 KB prompts that start on the callers' heap
+    (each producer copies its request into the pinned arena inside the measured time)."""
+    if ctx.rank != 0:
+        return None
+    exe = os.path.join(ROOT, "build", "latency_bench")
+    try:
+        from polykey_service_b200 import build as pkbuild
+        exe = pkbuild.build_latency_bench()
+    except Exception as e:                                   # no compiler on this box: say so, invent nothing
+        if not os.path.exists(exe):
+            return {"unavailable": f"host/latency_bench could not be built: {e!r}"}
+    G = ctx.world
+    env = dict(os.environ, PK_BACKENDS=str(G))
+    gens = max(2, min(ctx.cores - 2 * G, 16))
+    out = {"gpus": G, "generators": gens, "payload_bytes": 2048, "max_batch": 4096, "max_wait_us": 200,
+           "api": "BatchingService::EnqueueAsync -> decision (C++ mirror of the Go batcher), open loop, Poisson arrivals",
+           "rates": []}
+    # offered rates per GPU: light load (latency = service time), moderate, heavy, and flat out
+    for per_gpu in (1e5, 1e6, 5e6, 2e7):
+        rate = per_gpu * G
+        try:
+            p = subprocess.run([exe, "open", str(int(rate)), str(seconds), "4096", "200", "2048", str(gens)],
+                               capture_output=True, text=True, timeout=120, env=env)
+            r = json.loads(p.stdout.strip().splitlines()[-1])
+        except Exception as e:
+            out["rates"].append({"offered_per_s": rate, "error": repr(e)[:200]})
+            continue
+        out["rates"].append({"offered_per_s": rate, "completed_per_s": r["completed_per_s"], "dropped": r["dropped"],
+                             "errors": r["errors"], "p50_us": r["latency_us"]["p50"], "p99_us": r["latency_us"]["p99"],
+                             "mean_batch": r["mean_batch"]})
+    ok = [r for r in out["rates"] if "error" not in r]
+    if ok:
+        light = ok[0]
+        out.update({"p50_us": light["p50_us"], "p99_us": light["p99_us"], "rate": light["offered_per_s"]})
+        out["sustained_per_s"] = max(r["completed_per_s"] for r in ok)
+    return out
+
+
+def run_gpu(args):
+    ctx = Ctx(args)
+    O, pk = ctx.O, ctx.pk
+    workload = args.workload
+    depth = args.depth
+    issue = "plain" if args.no_graph else args.issue
+    sampler = ClockSampler(ctx.local)
+    sampler.start()
+
+    steady = 0 if args.steps >= 2000 or args.lean else 4000
+    router, res = resident_leg(ctx, workload, args.steps, args.warmup, issue, all_modes=True, steady_steps=steady,
+                               depth=depth, prewarm=not args.no_prewarm)
+    n, plen, desc, alg_bytes = res["n"], res["plen"], res["desc"], res["alg_bytes"]
+    ms = res["ms"]
+    h2d_guess = res["batch_bytes"]
+    k_e2e = max(20, min(max(args.steps, 200), int(3.0 / max(1e-5, (h2d_guess / 20e9)))))   # <= ~3 s at a pessimistic 20 GB/s
+    e2e = e2e_leg(ctx, router, res, depth, k_e2e, n_arenas=depth + 1 if res["batch_bytes"] <= (64 << 20) else 2,
+                  both_paths=True, sync_latency=True)
+    router.close()
+    if not args.lean:
+        probe = pcie_probe(ctx, e2e["h2d_bytes_per_step"])
+        e2e["pcie_probe"] = probe
+        e2e["pcie_peak_gbs"] = probe["h2d_gbs_per_gpu"]
+        e2e["frac_of_pcie"] = (e2e["h2d_bytes_per_step"] / (e2e["ms_per_step"] / 1e3) / 1e9) / probe["h2d_gbs_per_gpu"]
+
+    per_launch_s = ms / 1e3 / args.steps
+    value = ctx.world * args.steps * n / (ms / 1e3)
+    ms_serial = res["other"].get("serial", ms / args.steps)
+
+    # ---- the other BASELINE configurations, compact ----
+    workloads, c4 = {}, None
+    if not args.lean:
+        if ctx.world == 1 and workload == "c1":
+            for w, k, k_e in (("c2", 2000, 60), ("c3", 60, 8)):
+                r2, s2 = resident_leg(ctx, w, k, 10, "pdl", all_modes=False, steady_steps=0, depth=2)
+                e2 = e2e_leg(ctx, r2, s2, 2, k_e, n_arenas=2, both_paths=False, sync_latency=False)
+                r2.close()
+                workloads[w] = {"workload": s2["desc"], "steps": k, "ms_per_step": s2["ms"] / k,
+                                "value": s2["n"] * k / (s2["ms"] / 1e3), "unit": UNIT,
+                                "frac": s2["alg_bytes"] / (s2["ms"] / 1e3 / k) / 1e9 / ctx.peak,
+                                "algorithmic_bytes_per_launch": s2["alg_bytes"],
+                                "serial_ms_per_step": s2["other"].get("serial"),
+                                "e2e": {k_: e2[k_] for k_ in ("value", "unit", "ms_per_step", "steps", "h2d_bytes_per_step",
+                                                              "d2h_bytes_per_step", "pipeline_depth", "copies")},
+                                "parity_gate": "slot 0 and the last e2e batch bit-exact vs the oracle"}
+        c4 = c4_record(ctx, c4_leg(ctx, args.c4_batch, 245 * 4, 5))
+    latency = None
+    if not (args.lean or args.no_frontend):
+        # rank 0 drives every GPU from one server-shaped process; the other ranks wait on the
+        # rendezvous store — on the CPU, not in an NCCL barrier, whose kernel would spin on their GPUs
+        ctx.barrier()
+        store = None
+        if ctx.dist is not None:
+            from torch.distributed.distributed_c10d import _get_default_store
+            store = _get_default_store()
+        if ctx.rank == 0:
+            latency = frontend_leg(ctx)
+            if store is not None:
+                store.set("pk_frontend_done", "1")
+        elif store is not None:
+            import datetime
+            store.wait(["pk_frontend_done"], datetime.timedelta(seconds=900))
+    ctx.barrier()
+
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    clocks = sampler.summary([(w0, w1), (e0, e1)])
-    if rank != 0:
-        router.close()
+    clocks = sampler.summary(ctx.windows)
+    if ctx.rank != 0:
         return
-    meta = int(first["pay_off"].nbytes + first["pay_len"].nbytes + first["name_off"].nbytes + first["names"].nbytes)
-    peak, peak_src = measured_peak()
-    achieved = alg_bytes / pass_s / 1e9
+
+    # ---- CPU baseline on this box's host cores (rank 0, N=1 only) ----
+    cpu_baseline, extra_cpu = None, {}
+    if ctx.world == 1 and not args.no_cpu:
+        sample_batch = res["check_batch"] if res["batch_bytes"] <= (64 << 20) else make_sample(O, plen)
+        v_all, reps = cpu_arm(O, ctx.table, sample_batch, ctx.cores, 6.0)
+        v_one, _ = cpu_arm(O, ctx.table, sample_batch, 1, 3.0)
+        v_sw, _ = cpu_arm(O, ctx.table, sample_batch, ctx.cores, 1.0, switch_only=True)
+        v_sw1, _ = cpu_arm(O, ctx.table, sample_batch, 1, 1.0, switch_only=True)
+        cpu_baseline = {"value": v_all, "unit": UNIT, "cores": ctx.cores, "kind": "port",
+                        "sample": f"{reps} passes over one batch of {int(sample_batch['pay_len'].size)} requests x {plen} B "
+                                  f"(about 6 s), {cpu_port_note(O, ctx.cores)}",
+                        "one_core": v_one, "scaling_efficiency": v_all / (v_one * ctx.cores), "impl": O.fast_impl()}
+        extra_cpu = {"cpu_baseline_1core": {"value": v_one, "unit": UNIT, "cores": 1},
+                     "cpu_switch_only": {"value": v_sw, "unit": UNIT, "cores": ctx.cores,
+                                         "note": "CPU-A: what the Go reference actually does per request "
+                                                 "(mock.go:32-64 switch; never reads the payload)"},
+                     "cpu_switch_only_1core": {"value": v_sw1, "unit": UNIT, "cores": 1}}
+
+    achieved = alg_bytes / per_launch_s / 1e9
+    traffic, traffic_src = ncu_traffic(workload)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": ctx.world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
+        "config": config_of(desc, n, plen),
+        "parallelism": f"dp{ctx.world}: requests sharded by id, no collective",
+        "l2": f"ring of {res['ring']} resident batches = {res['ring'] * res['batch_bytes'] / 2**20:.0f} MiB > 126 MiB L2; launch k "
+              "reads the batch after the one launch k-1 read, and the walk carries on across calls (warm-up launches "
+              "never pre-load the timed ones)",
+        "issue": res["issue_desc"] + "; one stream, CUDA events on that stream",
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": ctx.peak, "unit": "GB/s",
+                     "frac": achieved / ctx.peak, "traffic": traffic, "traffic_source": traffic_src,
+                     "peak_source": ctx.peak_src, "kernel": "route_kernel (fused scan+hash+select)",
+                     "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_us": per_launch_s * 1e6},
+        "cpu_baseline": cpu_baseline,
+        "e2e": e2e,
+        "gpu_launches": res["launches"],
+        "clocks": clocks,
+        "issue_modes_ms_per_step": dict(res["other"], **{issue: ms / args.steps}),
+        "serial": {"ms_per_step": ms_serial, "value": ctx.world * n / (ms_serial / 1e3), "unit": UNIT,
+                   "frac": alg_bytes / (ms_serial / 1e3) / 1e9 / ctx.peak,
+                   "note": "the same K launches with every kernel waiting for its predecessor to complete: what ONE "
+                           "batch costs on an idle GPU (launch + two dependent HBM round trips + drain)"},
+    }
+    if "steady" in res or args.steps >= 2000:
+        k_ss, ms_ss = res.get("steady", (args.steps, ms))
+        line["steady_state"] = {"steps": k_ss, "ms_per_step": ms_ss / k_ss, "value": ctx.world * k_ss * n / (ms_ss / 1e3),
+                                "unit": UNIT, "frac": alg_bytes / (ms_ss / 1e3 / k_ss) / 1e9 / ctx.peak,
+                                "note": "same issue mode, enough launches that the fill and drain of the overlapped "
+                                        "pipeline (a third of a 20-launch graph) are amortised"}
+    if workloads:
+        line["workloads"] = workloads
+    if c4:
+        line["c4"] = c4
+    if latency:
+        line["latency"] = latency
+        if "sustained_per_s" in latency:
+            e2e["with_pack"] = {"value": latency["sustained_per_s"], "unit": UNIT,
+                                "what": "open-loop arrivals through the batching front-end at the service.Service seam: "
+                                        "per-request heap buffers -> producers copy into the pinned arena -> pk_submit/pk_wait "
+                                        "-> decision read by the caller (see `latency`)"}
+    line.update(extra_cpu)
+    emit(line)
+
+
+def make_sample(O, plen):
+    n_s = max(1, (64 << 20) // plen)
+    return O.gen_batch(O.SEED_BASE + 1, n_s, plen, mode=0, threads=16)
+
+
+def run_gpu_c4(args):
+    """`--workload c4`: BASELINE configs[4] as the headline of its own line (strong scaling)."""
+    ctx = Ctx(args)
+    O = ctx.O
+    sampler = ClockSampler(ctx.local)
+    sampler.start()
+    c = c4_leg(ctx, args.c4_batch, args.steps, args.warmup, prewarm=not args.no_prewarm)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    clocks = sampler.summary(ctx.windows)
+    if ctx.rank != 0:
+        return
+    n, plen, nb, reps, pass_s, first = c["n"], c["plen"], c["nb"], c["reps"], c["pass_s"], c["first"]
+    achieved = c["alg_pass"] / pass_s / 1e9
     cpu_baseline = None
-    if world == 1 and not args.no_cpu:
-        v_all, reps_cpu = cpu_arm(O, table, first, cores, 6.0)
-        cpu_baseline = {"value": v_all, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": f"{reps_cpu} passes over one batch of {n} requests x {plen} B, "
-                                  f"oracle/pk_cpu_fast.c scan+hash+select, {cores} threads"}
+    if ctx.world == 1 and not args.no_cpu:
+        v_all, reps_cpu = cpu_arm(O, ctx.table, first, ctx.cores, 6.0)
+        cpu_baseline = {"value": v_all, "unit": UNIT, "cores": ctx.cores, "kind": "port",
+                        "sample": f"{reps_cpu} passes over one batch of {n} requests x {plen} B, {cpu_port_note(O, ctx.cores)}"}
     emit({
-        "metric": METRIC, "value": C4_TOTAL / pass_s, "unit": UNIT, "n_gpus": world, "steps": nb * reps,
+        "metric": METRIC, "value": C4_TOTAL / pass_s, "unit": UNIT, "n_gpus": ctx.world, "steps": nb * reps,
         "warmup": max(3, args.warmup), "ms_per_step": pass_s * 1e3 / nb, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "u8/u32/u64 integer", "data": "synthetic",
-        "config": {"workload": f"C4: one stream of {C4_TOTAL} requests x {plen} B sharded by request id over {world} GPU(s), "
+        "scaling": "strong", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
+        "config": {"workload": f"C4: one stream of {C4_TOTAL} requests x {plen} B sharded by request id over {ctx.world} GPU(s), "
                                f"per-GPU batches of {n} (BASELINE configs[4])",
-                   "shard_requests_rank0": mine, "batches_per_shard": nb, "batch_requests": n, "payload_bytes": plen,
-                   "parallelism": f"dp{world}: requests sharded by id, no collective",
-                   "l2": f"the shard is resident ({nb * batch_bytes / 2**20:.0f} MiB on rank 0) and each pass walks all of it",
-                   "issue": "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch; one stream, "
-                            "CUDA events on that stream"},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "route_kernel (fused scan+hash+select)",
+                   "shard_requests_rank0": c["mine"], "batches_per_shard": nb, "batch_requests": n, "payload_bytes": plen,
+                   "providers": 8},
+        "parallelism": f"dp{ctx.world}: requests sharded by id, no collective",
+        "l2": f"the shard is resident ({nb * c['batch_bytes'] / 2**20:.0f} MiB on rank 0) and each pass walks all of it",
+        "issue": "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch; one stream, "
+                 "CUDA events on that stream",
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": ctx.peak, "unit": "GB/s", "frac": achieved / ctx.peak,
+                     "traffic": None, "peak_source": ctx.peak_src, "kernel": "route_kernel (fused scan+hash+select)",
                      "algorithmic_bytes_per_launch": algorithmic_bytes(first), "avg_launch_us": pass_s * 1e6 / nb},
         "cpu_baseline": cpu_baseline,
-        "e2e": {"value": C4_TOTAL / e2e_s, "unit": UNIT, "h2d_bytes_per_step": batch_bytes + meta, "d2h_bytes_per_step": 24 * n,
-                "steps": nb * e2e_reps, "pipeline_depth": depth, "ms_per_step": e2e_s * 1e3 / nb,
-                "api": "pk_submit/pk_wait, pinned host arenas", "pass_ms": e2e_s * 1e3},
-        "gpu_launches": int(launches), "clocks": clocks,
-        "pass_ms": pass_s * 1e3, "serial": {"pass_ms": ms_serial, "value": C4_TOTAL / (ms_serial / 1e3), "unit": UNIT},
+        "e2e": {"value": C4_TOTAL / c["e2e_s"], "unit": UNIT, "h2d_bytes_per_step": c["batch_bytes"] + c["meta"],
+                "d2h_bytes_per_step": 24 * n, "steps": nb * c["e2e_reps"], "pipeline_depth": c["depth"],
+                "ms_per_step": c["e2e_s"] * 1e3 / nb, "api": "pk_submit/pk_wait, pinned host arenas", "pass_ms": c["e2e_s"] * 1e3},
+        "gpu_launches": c["launches"], "clocks": clocks,
+        "pass_ms": pass_s * 1e3, "serial": {"pass_ms": c["serial_pass_ms"], "value": C4_TOTAL / (c["serial_pass_ms"] / 1e3), "unit": UNIT},
     })
-    router.close()
 
 
 def main():
@@ -598,8 +851,12 @@ def main():
     ap.add_argument("--c4-batch", type=int, default=4096, help="requests per batch of the C4 stream (4096 / 16384 / 65536)")
     ap.add_argument("--issue", default="pdl", choices=["pdl", "serial", "plain"],
                     help="how the K timed launches are issued on their one stream (default: graph chain + programmatic dependent launch)")
+    ap.add_argument("--depth", type=int, default=3, help="e2e pipeline depth: batches in flight through pk_submit/pk_wait")
     ap.add_argument("--no-graph", action="store_true", help="same as --issue plain")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-frontend", action="store_true", help="skip the latency / with_pack leg (C++ front-end)")
+    ap.add_argument("--lean", action="store_true",
+                    help="headline workload only: no steady_state / workloads / c4 / latency / PCIe probe (for ncu launch lists)")
     ap.add_argument("--no-prewarm", action="store_true",
                     help="skip the 0.4 s clock ramp-up before the W warm-up steps (for ncu launch lists)")
     args = ap.parse_args()

@@ -166,7 +166,9 @@ PK_API int  pk_route_batch(pk_handle* h,
  * cudaHostAlloc / cudaHostRegister'ed block), pk_submit / pk_route_batch launch the kernel
  * directly on the caller's buffers: it reads the bytes over PCIe and writes the records into
  * `out` — one launch instead of copy, copy, launch, copy.  Same records; the buffers must stay
- * untouched until pk_wait returns, as in the copying path.  pk_direct_count: batches so routed. */
+ * untouched until pk_wait returns, as in the copying path.  The path also needs the first byte
+ * the batch uses (payload + pay_off[0]) on a 16-byte boundary and `out` on an 8-byte one; a
+ * batch that is not so aligned is simply copied.  pk_direct_count: batches so routed. */
 PK_API int      pk_set_direct_bytes(pk_handle* h, uint64_t bytes);
 PK_API uint64_t pk_direct_count(const pk_handle* h);
 
@@ -183,8 +185,10 @@ PK_API int  pk_wait(pk_handle* h, uint32_t slot);
 /* Device-resident form (used to time the kernels alone, inputs already in HBM):
  * pk_stage copies a batch into slot `slot` and returns when it is resident;
  * pk_launch runs the kernels over the staged batch (no copies, asynchronous on the
- * slot's stream); pk_launch_many issues `count` launches back to back, launch k
- * using slot slots[k % n_slots_in_list], all on ONE stream (slot slots[0]'s), either
+ * slot's stream); pk_launch_many issues `count` launches back to back, walking the
+ * slot list round robin — launch k uses slots[(p + k) % n_slots_in_list], where p is where
+ * the handle's previous pk_launch_many call stopped, so that a short call does not start on
+ * the batches the call before it left in L2 — all on ONE stream (slot slots[0]'s), either
  * as `count` plain launches or (use_graph == 1) as one CUDA graph of `count` kernel
  * nodes in a chain, or (use_graph = k >= 2) as a graph of k parallel chains, launch j in
  * chain j % k, so that independent batches may overlap on the GPU; it brackets them with
@@ -251,7 +255,9 @@ PK_API void  pk_host_free(pk_handle* h, void* p);
  *                    before reading d_out
  *
  * The first call on each device resolves the static storage's device address
- * (cudaGetSymbolAddress); make that first call outside any stream capture.
+ * (cudaGetSymbolAddress).  Never call this entry point on a stream that is being captured —
+ * not the first call, not a later one: every call copies the table from a variable on its own
+ * stack, which is gone by the time anything recorded would run.
  * All calls share the one static scratch array and table copy: two calls whose GPU work
  * can overlap (different streams, different threads) race on them — serialise them on one
  * stream.  The part of the scratch a call can touch is cleared by that call before its

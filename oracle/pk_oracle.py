@@ -72,6 +72,9 @@ def lib() -> C.CDLL:
                                          C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
         L.pk_ref_route_batch_mt.argtypes = L.pk_ref_route_batch.argtypes + [C.c_uint32, C.c_int]
         L.pk_cpu_route_batch_mt.argtypes = L.pk_ref_route_batch.argtypes + [C.c_uint32]
+        L.pk_cpu_fast_impl.restype = C.c_int
+        L.pk_cpu_fast_reselect.restype = None
+        L.pk_cpu_fast_pool_threads.restype = C.c_uint32
         L.pk_ref_tool_class.argtypes = [C.POINTER(PkTable), C.c_void_p, C.c_uint32, C.POINTER(C.c_int)]
         L.pk_ref_tool_class.restype = C.c_uint32
         L.pk_ref_est_tokens.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_int)]
@@ -124,12 +127,20 @@ def _ptr(a):
     return None if a is None else a.ctypes.data
 
 
+def fast_impl() -> str:
+    """Which inner loop pk_cpu_fast.c uses in this process ("avx512" or "scalar")."""
+    return "avx512" if lib().pk_cpu_fast_impl() else "scalar"
+
+
 def route_batch(table: PkTable, batch, threads: int = 1, switch_only: bool = False,
-                fast: bool = False) -> tuple[int, np.ndarray]:
+                fast: bool = False, out: np.ndarray | None = None) -> tuple[int, np.ndarray]:
     """batch: dict with payload(u8), pay_off(u64 n+1), pay_len(u32 n), names(u8), name_off(u32 n+1).
-    fast=True runs pk_cpu_fast.c (the timed CPU baseline) instead of the plain checker."""
+    fast=True runs pk_cpu_fast.c (the timed CPU baseline) instead of the plain checker.
+    out: a record array to fill (timed loops reuse one instead of allocating per call)."""
     n = int(batch["pay_len"].shape[0])
-    out = np.zeros(n, dtype=DECISION_DTYPE)
+    if out is None:
+        out = np.zeros(n, dtype=DECISION_DTYPE)
+    assert out.dtype == DECISION_DTYPE and out.size >= n
     args = [C.byref(table), _ptr(batch["payload"]), _ptr(batch["pay_off"]), _ptr(batch["pay_len"]),
             _ptr(batch["names"]), _ptr(batch["name_off"]), n, _ptr(out)]
     if fast and not switch_only:

@@ -48,5 +48,21 @@ def build(force: bool = False, verbose: bool = False, defines=(), out: str | Non
     return out
 
 
+def build_latency_bench(force: bool = False) -> str:
+    """g++ build of host/latency_bench.cpp (the load generator that drives the C++ batching
+    front-end; bench.py's `latency` / `e2e.with_pack` legs run it) into build/latency_bench."""
+    root = os.path.dirname(HERE)
+    host = os.path.join(HERE, "host")
+    exe = os.path.join(root, "build", "latency_bench")
+    srcs = [os.path.join(host, f) for f in ("latency_bench.cpp", "batching_service.cpp", "service.cpp")]
+    deps = srcs + [os.path.join(host, f) for f in ("batching_service.hpp", "service.hpp")] + [LIB]
+    if not force and os.path.exists(exe) and all(os.path.getmtime(d) <= os.path.getmtime(exe) for d in deps if os.path.exists(d)):
+        return exe
+    os.makedirs(os.path.dirname(exe), exist_ok=True)
+    subprocess.check_call(["g++", "-std=c++20", "-O2", "-pthread", "-o", exe, *srcs, "-L" + HERE, "-lpkroute",
+                           "-Wl,-rpath," + HERE])
+    return exe
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -49,6 +49,7 @@ struct pk_handle {
     std::vector<Slot> slots;
     int        last_cuda = 0;
     uint64_t   launches = 0;
+    uint64_t   ring_pos = 0;            // pk_launch_many: where the next call continues in its slot list
     uint64_t   direct_batches = 0;      // batches routed straight out of host memory (no copies)
     uint64_t   direct_bytes = 0;        // largest batch (payload + metadata bytes) that takes that path
     std::vector<std::pair<const uint8_t*, size_t>> pinned;   // pk_host_alloc's blocks: known device-readable
@@ -374,7 +375,11 @@ int pk_submit(pk_handle* h, uint32_t slot, const uint8_t* payload, const uint64_
     if (pbytes + meta_bytes <= h->direct_bytes && s.params.n_extra == 0) {
         const uint8_t* d_pay = pbytes ? device_view(h, payload + pb, pbytes) : s.d_payload;
         const uint8_t* d_out = device_view(h, out, (size_t)n * sizeof(pk_decision));
-        if (d_pay && d_out) {
+        // the kernel reads 16-byte vectors at d_pay + pay_off[i] and stores 8-byte words into out:
+        // a buffer at an odd base takes the copying path (which re-bases into aligned device memory)
+        const bool aligned = (reinterpret_cast<uintptr_t>(d_pay) & 15u) == 0 &&
+                             (reinterpret_cast<uintptr_t>(d_out) & 7u) == 0;
+        if (d_pay && d_out && aligned) {
             pk::RouteParams P = s.params;
             // the metadata sections: same offsets, in the host copy of the blob
             auto in_host_blob = [&](const void* q) {
@@ -472,10 +477,16 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
 
     const bool pdl = (use_graph & PK_LAUNCH_PDL) != 0;
     use_graph &= ~PK_LAUNCH_PDL;
+    // The walk through the slot list continues where the previous call stopped: a call never
+    // starts on the batches its predecessor (a warm-up, say) touched last, which would still be
+    // in L2 when the list is larger than L2 but the call is short.
+    const uint64_t pos = h->ring_pos;
+    h->ring_pos = (pos + count) % n_list;
+    auto nth = [&](uint32_t k) -> Slot& { return h->slots[slots[(pos + k) % n_list]]; };
     if (!use_graph) {
         PK_CUDA(h, cudaEventRecord(h->ev0, st));
         for (uint32_t k = 0; k < count; ++k) {
-            int rc = launch_slot(h, h->slots[slots[k % n_list]], st, pdl);
+            int rc = launch_slot(h, nth(k), st, pdl);
             if (rc) return rc;
         }
         PK_CUDA(h, cudaEventRecord(h->ev1, st));
@@ -487,7 +498,7 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
         const uint32_t width = use_graph >= 2 ? (uint32_t)use_graph : 1u;
         if (width == 1 || n_list < width) {
             for (uint32_t k = 0; k < count && rc == PK_OK; ++k)
-                rc = launch_slot(h, h->slots[slots[k % n_list]], st, pdl);
+                rc = launch_slot(h, nth(k), st, pdl);
         } else {
             // fork: chain b runs on the stream of listed slot b (b >= 1) or on st (b == 0)
             cudaError_t fe = cudaEventRecord(h->ev0, st);
@@ -496,7 +507,7 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
             if (fe != cudaSuccess) rc = PK_ERR_CUDA;
             for (uint32_t k = 0; k < count && rc == PK_OK; ++k) {
                 const uint32_t b = k % width;
-                rc = launch_slot(h, h->slots[slots[k % n_list]], b == 0 ? st : h->slots[slots[b]].stream, pdl);
+                rc = launch_slot(h, nth(k), b == 0 ? st : h->slots[slots[b]].stream, pdl);
             }
             // join
             for (uint32_t b = 1; b < width && rc == PK_OK; ++b) {

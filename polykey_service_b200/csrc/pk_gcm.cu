@@ -259,6 +259,8 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
                                             : (in_len[i] >= pkgcm::kOverhead ? in_len[i] - pkgcm::kOverhead : 0);
         if (in_off[i] % 16 || out_off[i] % 16) return PK_GCM_ERR_ALIGN;
         if (in_off[i] < in_end || out_off[i] < out_end) return PK_GCM_ERR_OFFSETS;
+        // checked before the lengths are added, so a huge offset cannot wrap past the capacity test
+        if (in_off[i] > h->max_bytes || out_off[i] > h->max_bytes) return PK_GCM_ERR_CAPACITY;
         in_end = in_off[i] + in_len[i];
         out_end = out_off[i] + need_out;
     }

@@ -100,7 +100,9 @@ extern "C" int pk_route_device_noalloc(const pk_table* table,
     cudaStream_t st = static_cast<cudaStream_t>(stream);
 
     // Table: host -> the static device copy.  The source is pageable stack memory, which
-    // cudaMemcpyAsync stages before it returns, so `dt` may go out of scope afterwards.
+    // cudaMemcpyAsync stages before it returns, so `dt` may go out of scope afterwards.  (This is
+    // also why the header forbids calling under stream capture: a recorded copy would read `dt`
+    // long after this frame is gone.)
     pk::DevTable dt;
     pk::make_dev_table(*table, dt);
     if (cudaMemcpyAsync(ds->table, &dt, sizeof dt, cudaMemcpyHostToDevice, st) != cudaSuccess) {

@@ -92,6 +92,13 @@ def test_key_length_and_argument_errors(G):
             g.seal_arena(np.zeros(64, np.uint8), off, plen, np.zeros(24, np.uint8), np.zeros(256, np.uint8),
                          np.array([0, 48], dtype=np.uint64))
         assert e.value.code == -2
+        # an offset near 2^64: offset + length wraps to a small number — must be refused, not indexed
+        huge = np.array([0, (1 << 64) - 16], dtype=np.uint64)
+        for in_off, out_off in ((huge, np.array([0, 48], dtype=np.uint64)), (np.array([0, 16], dtype=np.uint64), huge)):
+            with pytest.raises(G.GcmError) as e:
+                g.seal_arena(np.zeros(64, np.uint8), in_off, np.array([4, 32], dtype=np.uint32), np.zeros(24, np.uint8),
+                             np.zeros(256, np.uint8), out_off)
+            assert e.value.code == -4
 
 
 def test_large_batch_of_secrets(G):

@@ -260,6 +260,31 @@ def test_small_batches_skip_the_copies(pk, oracle):
         r.close()
 
 
+def test_misaligned_pinned_buffers_take_the_copying_path(pk, oracle):
+    """The in-place path issues 16-byte loads on the caller's payload and 8-byte stores on `out`.
+    A page-locked arena whose base is not so aligned (here +8 and +4) must not reach it — a
+    misaligned device access is a sticky fault — and is copied instead: same records."""
+    t = oracle.default_table()
+    with pk.Router(device=0, max_requests=1024, max_payload_bytes=4 << 20, n_slots=1) as r:
+        arena = r.host_alloc((1 << 20) + 64)
+        outbuf = r.host_alloc(24 * 512 + 64)
+        b = oracle.gen_batch(7200, 300, 0, 3000, mode=0)
+        want = oracle.route_batch(t, b, threads=4)[1]
+        nbytes = b["payload"].size
+        for pay_shift, out_shift, direct in ((0, 0, True), (8, 0, False), (0, 4, False), (8, 4, False)):
+            moved = dict(b)
+            moved["payload"] = arena[pay_shift:pay_shift + nbytes]
+            moved["payload"][:] = b["payload"]
+            out = np.frombuffer(outbuf[out_shift:out_shift + 24 * 300], dtype=pk.DECISION_DTYPE)
+            out[:] = 0
+            seen = r.direct_count
+            got = r.route_batch(moved, out=out)
+            assert_records_equal(got, want, f"payload base +{pay_shift}, out base +{out_shift}")
+            assert r.direct_count == seen + (1 if direct else 0)
+        r.sync()                                       # no sticky error left behind
+        assert_records_equal(r.route_batch(b), want, "afterwards")
+
+
 def test_programmatic_dependent_launch(pk, oracle):
     """PK_LAUNCH_PDL: consecutive launches of one stream may overlap.  Same records as the oracle
     for plain launches and for a graph chain; a slot with long requests (which owns per-request

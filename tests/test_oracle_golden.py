@@ -134,13 +134,31 @@ def test_generator_is_deterministic_and_sliceable(oracle):
             bytes(x["payload"][s:s + l]).decode("utf-8")
 
 
+@pytest.mark.parametrize("impl", ["avx512", "scalar"])
 @pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
-def test_fast_cpu_port_equals_plain_oracle(oracle, mode):
-    """oracle/pk_cpu_fast.c (the timed CPU baseline) against the plain checker."""
-    t = oracle.default_table()
-    for n, lo, hi in [(300, 0, 40000), (3000, 0, 70), (40, 16370, 16400)]:
-        b = oracle.gen_batch(900 + mode, n, lo, hi, mode=mode)
-        plain = oracle.route_batch(t, b, threads=4)[1]
-        for th in (1, 3):
-            rc, fast = oracle.route_batch(t, b, threads=th, fast=True)
-            assert rc == 0 and (fast == plain).all(), (mode, n, th)
+def test_fast_cpu_port_equals_plain_oracle(oracle, mode, impl, monkeypatch):
+    """oracle/pk_cpu_fast.c (the timed CPU baseline: one fused pass, AVX-512 or scalar, persistent
+    thread pool) against the plain checker — both inner loops, 1 / 3 / 8 threads, every length
+    around the 16-byte block, the 64-byte vector, the 512-byte step and the 16 KiB segment."""
+    monkeypatch.setenv("PK_CPU_FAST_IMPL", impl)
+    oracle.lib().pk_cpu_fast_reselect()
+    try:
+        if impl == "avx512" and oracle.fast_impl() != "avx512":
+            pytest.skip("this CPU has no AVX-512 (the scalar loop is what bench.py would time here)")
+        t = oracle.default_table()
+        for n, lo, hi in [(300, 0, 40000), (3000, 0, 70), (40, 16370, 16400), (700, 0, 1100), (64, 32700, 32800)]:
+            b = oracle.gen_batch(900 + mode, n, lo, hi, mode=mode)
+            plain = oracle.route_batch(t, b, threads=4)[1]
+            for th in (1, 3, 8):
+                rc, fast = oracle.route_batch(t, b, threads=th, fast=True)
+                assert rc == 0 and (fast == plain).all(), (mode, n, th, np.nonzero(fast != plain)[0][:4])
+        # a reused output array, as bench.py's timed loop passes it
+        b = oracle.gen_batch(950 + mode, 2000, 0, 3000, mode=mode)
+        out = np.zeros(2000, dtype=oracle.DECISION_DTYPE)
+        for _ in range(3):
+            out[:] = 0
+            rc, got = oracle.route_batch(t, b, threads=8, fast=True, out=out)
+            assert got is out and (out == oracle.route_batch(t, b, threads=2)[1]).all()
+    finally:
+        monkeypatch.delenv("PK_CPU_FAST_IMPL")
+        oracle.lib().pk_cpu_fast_reselect()

@@ -6,8 +6,11 @@ into the device-wide synchronisation cudaMalloc implies.  They hand the library 
 pointers carved out of their own reservation; the scratch the kernel needs for long requests
 is a static array inside the library.  This test plays such a caller (the buffers come from
 torch, standing in for "somebody else's allocator"), calls the entry point through the C ABI
-twice in a row on different batches, and requires its records to be bit-identical to those of
-the ordinary entry point, pk_route_batch, on the same batches (integer work: tolerance 0).
+twice in a row on different batches, and requires its records to be bit-identical both to the
+CPU oracle's and to those of the ordinary entry point, pk_route_batch, on the same batches
+(integer work: tolerance 0).  Two more cases cover what the shared static scratch makes special:
+a call that leaves the scratch dirty must not disturb the next one, and a caller's own
+(non-default) stream works like the default one.
 
 Kept in a file that pytest collects last, so a failure here cannot hide any other test; it
 needs nothing from the other tests and also passes when run alone in a fresh process.
@@ -16,6 +19,8 @@ import ctypes as C
 
 import numpy as np
 import pytest
+
+from helpers import assert_records_equal
 
 pytestmark = pytest.mark.gpu
 
@@ -40,9 +45,13 @@ def to_device(torch, a, pad=0):
     return t
 
 
-def route_noalloc(pk, torch, batch):
+def route_noalloc(pk, torch, batch, extra=None, stream=None):
+    """Plays the caller: places the batch in 'its own' device memory (torch's allocator stands in
+    for it), calls the entry point on `stream` (default: the current stream) and reads the records
+    back.  `extra` overrides the (request, segment) list — used to leave the scratch dirty."""
     n = int(batch["pay_len"].size)
-    extra = extra_segments(batch["pay_len"])
+    if extra is None:
+        extra = extra_segments(batch["pay_len"])
     d = {k: to_device(torch, batch[k], pad=32 if k == "payload" else 0) for k in batch}
     d_extra = to_device(torch, extra)
     d_out = torch.zeros(24 * n, dtype=torch.uint8, device="cuda")
@@ -52,7 +61,7 @@ def route_noalloc(pk, torch, batch):
         C.byref(table), d["payload"].data_ptr(), d["pay_off"].data_ptr(), d["pay_len"].data_ptr(),
         d["names"].data_ptr(), d["name_off"].data_ptr(), d_extra.data_ptr() if len(extra) else None,
         len(extra), n, int(batch["pay_len"].max()), d_out.data_ptr(),
-        torch.cuda.current_stream().cuda_stream)
+        (stream or torch.cuda.current_stream()).cuda_stream)
     assert rc == 0, pk.STATUS.get(rc, rc)
     torch.cuda.synchronize()
     return np.frombuffer(d_out.cpu().numpy().tobytes(), dtype=pk.DECISION_DTYPE), len(extra)
@@ -68,18 +77,51 @@ def test_noalloc_entry_matches_route_batch_twice(pk, oracle):
         # static scratch is used, and the second call reuses entries the first one touched
         first = oracle.gen_batch(8801, 700, 0, 90000, mode=0)
         second = oracle.gen_batch(8802, 1500, 0, 40000, mode=3)
+        table = oracle.default_table()
         for which, batch in (("first call", first), ("second call", second)):
-            want = router.route_batch(batch)
+            rc, want = oracle.route_batch(table, batch, threads=4)        # the checker: the CPU oracle
+            assert rc == 0
             got, n_extra = route_noalloc(pk, torch, batch)
             assert n_extra > 0
-            bad = np.nonzero(got != want)[0]
-            assert bad.size == 0, f"{which}: {bad.size} records differ, first at {bad[:1]}: {got[bad[:1]]} vs {want[bad[:1]]}"
+            assert_records_equal(got, want, f"{which} vs oracle")
+            assert_records_equal(got, router.route_batch(batch), f"{which} vs pk_route_batch")
         # a batch of short requests takes the path that needs no scratch at all
         short = oracle.gen_batch(8803, 3000, 0, 200, mode=0)
         got, n_extra = route_noalloc(pk, torch, short)
-        assert n_extra == 0 and (got == router.route_batch(short)).all()
+        assert n_extra == 0
+        assert_records_equal(got, oracle.route_batch(table, short, threads=4)[1], "short batch vs oracle")
+        assert_records_equal(got, router.route_batch(short), "short batch vs pk_route_batch")
     finally:
         router.close()
+
+
+def test_noalloc_entry_survives_dirty_scratch_and_own_stream(pk, oracle):
+    """Every call shares one static scratch array, and it keeps what the last call left in it.
+    A call whose segment list is incomplete never finishes its long requests, so their scratch
+    entries stay non-zero — the state a failed or interrupted caller leaves behind.  The next call
+    must clear what it is going to use and produce exact records all the same; here it also runs on
+    a stream the caller created, not the default one."""
+    import torch
+    torch.cuda.set_device(0)
+    table = oracle.default_table()
+    dirty = oracle.gen_batch(8811, 400, 40000, 90000, mode=0)           # every request has >= 3 segments
+    full = extra_segments(dirty["pay_len"])
+    # drop the LAST segment of every request: partial sums and arrival counts stay in the scratch
+    keep = np.ones(len(full), dtype=bool)
+    keep[np.r_[np.nonzero(np.diff(full[:, 0]))[0], len(full) - 1]] = False
+    assert 0 < keep.sum() < len(full)
+    route_noalloc(pk, torch, dirty, extra=full[keep])                   # records of this call are unfinished: ignored
+
+    own = torch.cuda.Stream()
+    batch = oracle.gen_batch(8812, 400, 0, 90000, mode=3)               # same request indices, correct list
+    rc, want = oracle.route_batch(table, batch, threads=4)
+    assert rc == 0
+    got, n_extra = route_noalloc(pk, torch, batch, stream=own)
+    assert n_extra > 0
+    assert_records_equal(got, want, "after a call that left the scratch dirty, on the caller's own stream")
+    # and once more on the default stream, now over a scratch the previous launch left clean
+    got, _ = route_noalloc(pk, torch, batch)
+    assert_records_equal(got, want, "repeat on the default stream")
 
 
 def test_noalloc_entry_rejects_oversized_batches(pk):
