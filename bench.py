@@ -473,7 +473,7 @@ def e2e_leg(ctx: Ctx, router, res, depth: int, k_e2e: int, n_arenas: int, both_p
     return e2e
 
 
-def pcie_probe(ctx: Ctx, nbytes: int, reps: int = 40):
+def pcie_probe(ctx: Ctx, router, nbytes: int, reps: int = 40):
     """The host ceiling an end-to-end step runs under: all ranks copy `nbytes` of page-locked host
     memory to their GPU at the same time with plain cudaMemcpyAsync (and, separately, both
     directions at once).  Device time, max over ranks."""
@@ -506,10 +506,22 @@ def pcie_probe(ctx: Ctx, nbytes: int, reps: int = 40):
     t_h2d = timed(False)
     t_dup = timed(True)
     per_rank = nbytes * reps / t_h2d / 1e9
-    return {"h2d_gbs_per_gpu": per_rank, "h2d_gbs_aggregate": per_rank * ctx.world,
-            "duplex_gbs_per_gpu_each_way": nbytes * reps / t_dup / 1e9,
-            "what": f"{ctx.world} rank(s) at once, {reps} x cudaMemcpyAsync of {nbytes} B from page-locked host memory "
-                    "(duplex: the same with a D2H copy of equal size on a second stream)"}
+    # the same bytes pulled by a plain read kernel (128-bit loads of mapped host memory): what the
+    # in-place path of pk_submit runs under — on these boxes faster than one copy engine
+    arena = router.host_alloc((nbytes + 15) & ~15)
+    arena[:] = 7
+    router.probe_host_read(arena, 3)
+    ctx.barrier()
+    t0 = time.perf_counter()
+    kern = router.probe_host_read(arena, reps)
+    kern_min = -ctx.max(-kern)                               # slowest rank
+    ctx.windows.append((t0, time.perf_counter()))
+    return {"memcpy_h2d_gbs_per_gpu": per_rank, "kernel_read_gbs_per_gpu": kern_min,
+            "peak_gbs_per_gpu": max(per_rank, kern_min), "peak_gbs_aggregate": max(per_rank, kern_min) * ctx.world,
+            "memcpy_duplex_gbs_per_gpu_each_way": nbytes * reps / t_dup / 1e9,
+            "what": f"{ctx.world} rank(s) at once, {reps} passes over {nbytes} B of page-locked host memory: "
+                    "cudaMemcpyAsync H2D (one copy engine), the same with a D2H copy of equal size on a second stream, "
+                    "and a plain read kernel (pk_probe_host_read); device time, slowest rank"}
 
 
 def c4_leg(ctx: Ctx, batch: int, steps: int, warmup: int, e2e_reps: int = 3, prewarm: bool = True):
@@ -676,12 +688,12 @@ def run_gpu(args):
     k_e2e = max(20, min(max(args.steps, 200), int(3.0 / max(1e-5, (h2d_guess / 20e9)))))   # <= ~3 s at a pessimistic 20 GB/s
     e2e = e2e_leg(ctx, router, res, depth, k_e2e, n_arenas=depth + 1 if res["batch_bytes"] <= (64 << 20) else 2,
                   both_paths=True, sync_latency=True)
-    router.close()
     if not args.lean:
-        probe = pcie_probe(ctx, e2e["h2d_bytes_per_step"])
+        probe = pcie_probe(ctx, router, e2e["h2d_bytes_per_step"])
         e2e["pcie_probe"] = probe
-        e2e["pcie_peak_gbs"] = probe["h2d_gbs_per_gpu"]
-        e2e["frac_of_pcie"] = (e2e["h2d_bytes_per_step"] / (e2e["ms_per_step"] / 1e3) / 1e9) / probe["h2d_gbs_per_gpu"]
+        e2e["pcie_peak_gbs"] = probe["peak_gbs_per_gpu"]
+        e2e["frac_of_pcie"] = (e2e["h2d_bytes_per_step"] / (e2e["ms_per_step"] / 1e3) / 1e9) / probe["peak_gbs_per_gpu"]
+    router.close()
 
     per_launch_s = ms / 1e3 / args.steps
     value = ctx.world * args.steps * n / (ms / 1e3)

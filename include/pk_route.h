@@ -222,6 +222,13 @@ PK_API uint64_t pk_launch_count(const pk_handle* h);
 PK_API void* pk_host_alloc(pk_handle* h, size_t bytes);
 PK_API void  pk_host_free(pk_handle* h, void* p);
 
+/* Measurement aid (no counterpart in the reference): how fast can THIS GPU pull page-locked host
+ * memory with plain 128-bit loads from a kernel — the ceiling the in-place path of pk_submit
+ * runs under.  `host` must be page-locked, GPU-addressable and 16-byte aligned (pk_host_alloc);
+ * `reps` back-to-back read passes over [host, host + bytes) on slot 0's stream are timed with
+ * CUDA events; *elapsed_ms = their device time.  Slot 0 must be idle.                       */
+PK_API int pk_probe_host_read(pk_handle* h, const void* host, size_t bytes, uint32_t reps, float* elapsed_ms);
+
 /* pk_route_device_noalloc — routing for callers that cannot allocate GPU memory.
  * (No counterpart in the reference: it has no device code at all.)
  *

@@ -101,6 +101,7 @@ def lib() -> C.CDLL:
         L.pk_launch_count.argtypes, L.pk_launch_count.restype = [vp], C.c_uint64
         L.pk_host_alloc.argtypes, L.pk_host_alloc.restype = [vp, C.c_size_t], vp
         L.pk_host_free.argtypes, L.pk_host_free.restype = [vp, vp], None
+        L.pk_probe_host_read.argtypes = [vp, vp, C.c_size_t, u32, C.POINTER(C.c_float)]
         L.pk_last_cuda_error.argtypes = [vp]
         L.pk_route_device_noalloc.argtypes = [C.POINTER(PkTable), vp, vp, vp, vp, vp, vp, u32, u32, u32, vp, vp]
         _lib = L
@@ -263,6 +264,13 @@ class Router:
     def set_direct_bytes(self, nbytes: int):
         """Largest batch (payload + metadata bytes) that takes the no-copy path; 0 = never."""
         self._check(self._L.pk_set_direct_bytes(self._h, int(nbytes)), "pk_set_direct_bytes")
+
+    def probe_host_read(self, host: np.ndarray, reps: int = 20) -> float:
+        """GB/s at which a plain read kernel pulls the page-locked array `host` over PCIe."""
+        ms = C.c_float(0)
+        self._check(self._L.pk_probe_host_read(self._h, host.ctypes.data, host.nbytes, reps, C.byref(ms)),
+                    "pk_probe_host_read")
+        return host.nbytes * reps / (ms.value / 1e3) / 1e9
 
     def host_alloc(self, nbytes: int, dtype=np.uint8) -> np.ndarray:
         """Pinned host array owned by the C side (freed on close)."""

@@ -29,7 +29,7 @@ CudaBackend::CudaBackend(int device, const pk_table& table, uint32_t max_request
     cfg.max_requests = max_requests;
     cfg.n_slots = n_slots;
     cfg.max_payload_bytes = max_payload_bytes;
-    cfg.max_name_bytes = (uint64_t)max_requests * 256u;
+    cfg.max_name_bytes = std::max<uint64_t>((uint64_t)max_requests * 256u, 1u << 20);   // >= the front-end's name arena
     status_ = pk_init(device, &table, &cfg, &h_);
     if (status_ != PK_OK) h_ = nullptr;
 }
@@ -55,25 +55,42 @@ std::string CudaBackend::error_string(int status)
 }
 
 // ---------------------------------------------------------------- BatchingService --------
+using detail::Arena;
+
 BatchingService::BatchingService(Service* inner, std::vector<RouteBackend*> backends, BatchingConfig cfg)
     : inner_(inner), cfg_(cfg)
 {
+    // the packed reservation word bounds what one batch can hold
+    cfg_.max_batch = std::max<uint32_t>(1u, std::min<uint32_t>(cfg_.max_batch, 65536u));
+    cfg_.max_payload_bytes = std::min<uint64_t>(cfg_.max_payload_bytes & ~uint64_t(15), (uint64_t)Arena::kPayMask << 4);
+    cfg_.max_name_bytes_per_request = std::min<uint32_t>(cfg_.max_name_bytes_per_request, 4096u);
+    name_cap_ = (uint32_t)std::min<uint64_t>((uint64_t)cfg_.max_batch * std::max<uint32_t>(cfg_.max_name_bytes_per_request, 64u),
+                                             Arena::kNameMask);
     for (RouteBackend* be : backends) {
         auto s = std::make_unique<Shard>();
         s->be = be;
-        s->arenas.resize(be->slots());
-        for (Arena& a : s->arenas) {
-            a.payload = static_cast<uint8_t*>(be->alloc_host(cfg_.max_payload_bytes + 64));
-            a.out = static_cast<pk_decision*>(be->alloc_host((size_t)cfg_.max_batch * sizeof(pk_decision)));
-            a.pay_off.resize(cfg_.max_batch + 1);
-            a.pay_len.resize(cfg_.max_batch);
-            a.name_off.resize(cfg_.max_batch + 1);
-            a.reqs.reserve(cfg_.max_batch);
-            if (!a.payload || !a.out) healthy_.store(false);
+        // more arenas than device slots: an arena stays taken after its batch has completed until
+        // every caller has picked up its record, and that must not hold a device slot hostage
+        const uint32_t n_arenas = 2u * be->slots() + 1u;
+        for (uint32_t k = 0; k < n_arenas; ++k) {
+            auto a = std::make_unique<Arena>();
+            a->payload = static_cast<uint8_t*>(be->alloc_host(cfg_.max_payload_bytes + 64));
+            a->names = static_cast<uint8_t*>(be->alloc_host((size_t)name_cap_ + 64));
+            a->out = static_cast<pk_decision*>(be->alloc_host((size_t)cfg_.max_batch * sizeof(pk_decision)));
+            a->pay_off.resize(cfg_.max_batch + 1);
+            a->pay_len.resize(cfg_.max_batch);
+            a->rec.assign(cfg_.max_batch, Arena::Rec{0, Arena::kUncommitted, 0, 0});
+            a->name_off.resize(cfg_.max_batch + 1);
+            if (!a->payload || !a->names || !a->out) healthy_.store(false);
+            s->arenas.push_back(std::move(a));
         }
         shards_.push_back(std::move(s));
     }
     if (shards_.empty()) healthy_.store(false);
+    if (!healthy_.load()) {                                  // nothing will be routed: refuse everything
+        for (auto& s : shards_) s->closed.store(true);
+        return;
+    }
     for (auto& s : shards_) s->th = std::thread(&BatchingService::flusher, this, s.get());
 }
 
@@ -81,14 +98,8 @@ BatchingService::~BatchingService() { Shutdown(); }
 
 void BatchingService::Shutdown()
 {
-    if (stopping_.exchange(true)) {
-        for (auto& s : shards_) if (s->th.joinable()) s->th.join();
-        return;
-    }
-    for (auto& s : shards_) {
-        { std::lock_guard<std::mutex> g(s->mu); }
-        s->cv.notify_all();
-    }
+    stopping_.store(true);
+    for (auto& s : shards_) wake_flusher(s.get());
     for (auto& s : shards_) if (s->th.joinable()) s->th.join();
 }
 
@@ -105,52 +116,60 @@ BatchingStats BatchingService::stats() const
     return t;
 }
 
-bool BatchingService::push(Shard* s, Pending* p)
+void BatchingService::wake_flusher(Shard* s)
 {
-    static std::atomic<unsigned> next_stripe{0};
-    static thread_local const unsigned stripe = next_stripe.fetch_add(1) % kInboxes;
-    Inbox& in = s->inbox[stripe];
-    {
-        std::lock_guard<std::mutex> g(in.mu);
-        if (in.closed) return false;
-        in.v.push_back(p);
-    }
-    s->queued.fetch_add(1);                                  // seq_cst: pairs with the flusher's sleeping / queued check
-    if (s->sleeping.load()) {                                // a polling flusher needs no wake-up call
-        { std::lock_guard<std::mutex> g(s->mu); }            // it is either before its predicate check or already waiting
-        s->cv.notify_one();
-    }
-    return true;
+    if (!s->sleeping.load()) return;                        // seq_cst: pairs with the flusher's sleeping / state check
+    { std::lock_guard<std::mutex> g(s->mu); }               // it is either before its predicate check or already waiting
+    s->cv.notify_one();
 }
 
-// Flusher only: move everything the inboxes hold into the backlog.  O(1) per inbox under its lock.
-size_t BatchingService::drain(Shard* s)
+// Producer side: take a record index and byte ranges of the open batch with one CAS, copy the
+// request in, commit.  Callers have checked that the request fits an EMPTY batch, so a batch
+// without room is a full one: it is sealed for the flusher and the producer moves on to the next.
+// When no batch is open (every arena busy) a blocking caller waits for one; the others get kBusy.
+BatchingService::Reserve BatchingService::reserve(Shard* s, const std::string& name, const void* payload, size_t len,
+                                                  Ticket& t, bool block)
 {
-    static thread_local std::vector<Pending*> tmp;
-    size_t got = 0;
-    for (Inbox& in : s->inbox) {
-        {
-            std::lock_guard<std::mutex> g(in.mu);
-            if (in.v.empty()) continue;
-            tmp.swap(in.v);
+    const uint64_t sz16 = round16(len) >> 4;
+    const uint64_t inc = (1ull << Arena::kCountShift) | (sz16 << Arena::kPayShift) | (uint64_t)name.size();
+    const uint64_t cap16 = cfg_.max_payload_bytes >> 4;
+    for (;;) {
+        const uint32_t seq = s->open_seq.load(std::memory_order_acquire);
+        const uint32_t k = s->open.load(std::memory_order_acquire);
+        if (k != kNone) {
+            Arena& a = *s->arenas[k];
+            uint64_t st = a.state.load(std::memory_order_relaxed);
+            while (!(st & Arena::kSealed)) {
+                const uint32_t cnt = Arena::count_of(st);
+                if (cnt >= cfg_.max_batch || Arena::pay16_of(st) + sz16 > cap16 ||
+                    (uint64_t)Arena::names_of(st) + name.size() > name_cap_) {
+                    a.state.fetch_or(Arena::kSealed);       // full: the flusher takes it from here
+                    wake_flusher(s);
+                    break;
+                }
+                if (!a.state.compare_exchange_weak(st, st + inc, std::memory_order_seq_cst, std::memory_order_relaxed))
+                    continue;
+                // the reservation is ours; the arena cannot be recycled before we commit
+                const uint64_t off = Arena::pay16_of(st) << 4;
+                const uint32_t noff = Arena::names_of(st);
+                t.a = &a; t.idx = cnt; t.gen = a.gen;
+                if (len) std::memcpy(a.payload + off, payload, len);
+                if (!name.empty()) std::memcpy(a.names + noff, name.data(), name.size());
+                Arena::Rec& rec = a.rec[cnt];
+                rec.off16 = (uint32_t)(off >> 4);
+                rec.noff = noff;
+                std::atomic_ref<uint32_t>(rec.len).store((uint32_t)len, std::memory_order_release);   // commit
+                if (cnt == 0) wake_flusher(s);              // a batch has been started
+                return Reserve::kOk;
+            }
         }
-        s->backlog.insert(s->backlog.end(), tmp.begin(), tmp.end());
-        got += tmp.size();
-        tmp.clear();
+        if (s->closed.load(std::memory_order_acquire)) return Reserve::kClosed;
+        // every arena is busy, or the open one has just been sealed: wait for the next (back-pressure)
+        for (int spin = 0; spin < 400 && s->open_seq.load(std::memory_order_acquire) == seq; ++spin) cpu_relax();
+        if (s->open_seq.load(std::memory_order_acquire) != seq) continue;
+        if (!block) return Reserve::kBusy;
+        if (!s->closed.load(std::memory_order_acquire)) s->open_seq.wait(seq, std::memory_order_acquire);
     }
-    return got;
-}
-
-// Flusher only, when stopping with nothing left: refuse further pushes.  false = something
-// slipped in meanwhile; drain it and try again.
-bool BatchingService::close_inboxes(Shard* s)
-{
-    for (Inbox& in : s->inbox) {
-        std::lock_guard<std::mutex> g(in.mu);
-        if (!in.v.empty()) return false;
-        in.closed = true;
-    }
-    return true;
 }
 
 Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, const Struct* parameters,
@@ -160,35 +179,46 @@ Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, c
         return Result{nullptr, std::string("routing stage is shut down")};
     if (!healthy_.load())
         return Result{nullptr, std::string("routing stage is unhealthy")};
+    // A name this long equals no table entry: it is the switch's default branch (mock.go:60-64)
+    // whatever the routing stage would say, so answer it without one.
+    if (toolName.size() > cfg_.max_name_bytes_per_request)
+        return inner_->ExecuteTool(ctx, toolName, parameters, secretId, metadata);
 
-    Pending p;
-    p.name = &toolName;
-    if (parameters) p.payload = to_json(*parameters);       // the request's prompt payload bytes
-    if (round16(p.payload.size()) > cfg_.max_payload_bytes)
+    std::string payload;
+    if (parameters) payload = to_json(*parameters);         // the request's prompt payload bytes
+    if (round16(payload.size()) > cfg_.max_payload_bytes || payload.size() >= Arena::kUncommitted)
         return Result{nullptr, std::string("request payload exceeds the routing stage's arena")};
 
-    const uint64_t id = next_id_.fetch_add(1);
+    const uint64_t id = next_id_.fetch_add(1, std::memory_order_relaxed);
     Shard* s = shards_[id % shards_.size()].get();          // shard by request id, no exchange
-    if (!push(s, &p)) return Result{nullptr, std::string("routing stage is shut down")};
-    // Wait for the decision: poll first while few callers are waiting (the batch comes back in
-    // tens of µs), then sleep.  `done` is the flusher's last access to p, so returning on it is safe.
+    Ticket t;
+    if (reserve(s, toolName, payload.data(), payload.size(), t, true) != Reserve::kOk)
+        return Result{nullptr, std::string("routing stage is shut down")};
+    // Wait for the batch: poll first while few callers are waiting (it comes back in tens of µs),
+    // then sleep on the arena's generation word.
+    Arena& a = *t.a;
     const uint32_t ahead = s->waiting.fetch_add(1, std::memory_order_relaxed);
     if (ahead < cfg_.caller_spin_max_waiters && cfg_.caller_spin_us) {
         const auto until = Clock::now() + std::chrono::microseconds(cfg_.caller_spin_us);
-        while (!p.done.load(std::memory_order_acquire) && Clock::now() < until) cpu_relax();
+        while (a.gen_done.load(std::memory_order_acquire) != t.gen && Clock::now() < until) cpu_relax();
     }
-    if (!p.done.load(std::memory_order_acquire)) {
-        std::unique_lock<std::mutex> w(s->done_mu);         // block this RPC's thread only
-        s->done_cv.wait(w, [&] { return p.done.load(std::memory_order_acquire); });
+    for (;;) {
+        const uint32_t g = a.gen_done.load(std::memory_order_acquire);
+        if (g == t.gen) break;
+        a.gen_done.wait(g, std::memory_order_acquire);       // block this RPC's thread only
     }
     s->waiting.fetch_sub(1, std::memory_order_relaxed);
+    const int rc = a.rc;
+    pk_decision decision{};
+    if (rc == 0) decision = a.out[t.idx];
+    std::atomic_ref<uint32_t>(a.rec[t.idx].len).store(Arena::kUncommitted, std::memory_order_release);   // picked up: our last access
 
-    if (p.rc != 0) {
+    if (rc != 0) {
         // plain error: server.go:37-40 returns it verbatim (gRPC Unknown)
-        return Result{nullptr, "routing failed: " + s->be->error_string(p.rc)};
+        return Result{nullptr, "routing failed: " + s->be->error_string(rc)};
     }
     Result r = inner_->ExecuteTool(ctx, toolName, parameters, secretId, metadata);
-    if (r.resp) r.resp->decision = p.decision;
+    if (r.resp) r.resp->decision = decision;
     return r;
 }
 
@@ -203,14 +233,14 @@ void BatchingService::log_batch(const Shard* s, const Arena& a, int rc)
     size_t gpu = 0;
     while (gpu < shards_.size() && shards_[gpu].get() != s) ++gpu;
     std::string line = std::string("{\"level\":\"") + (rc ? "ERROR" : "INFO") + "\",\"msg\":\"routed batch\",\"gpu\":" +
-                       std::to_string(gpu) + ",\"requests\":" + std::to_string(a.reqs.size()) + ",\"payload_bytes\":" +
+                       std::to_string(gpu) + ",\"requests\":" + std::to_string(a.n) + ",\"payload_bytes\":" +
                        std::to_string(a.bytes) + ",\"trigger\":\"" + a.trigger + "\",\"duration\":\"" +
                        LoggingInterceptor::format_duration(now - a.t_submit_ns) + "\"";
     if (rc) {
         line += ",\"error\":\"routing failed: " + s->be->error_string(rc) + "\"";
     } else {
         uint64_t cls[4] = {0, 0, 0, 0}, none = 0;
-        for (size_t i = 0; i < a.reqs.size(); ++i) {
+        for (size_t i = 0; i < a.n; ++i) {
             ++cls[a.out[i].tool_class & 3u];
             if (a.out[i].flags & PK_FLAG_NO_PROVIDER) ++none;
         }
@@ -222,171 +252,237 @@ void BatchingService::log_batch(const Shard* s, const Arena& a, int rc)
     cfg_.batch_log->push_back(std::move(line));
 }
 
-bool BatchingService::EnqueueAsync(AsyncRequest& r, std::string toolName, std::string payload)
+BatchingService::Enqueue BatchingService::EnqueueAsync(AsyncRequest& r, const std::string& toolName, const std::string& payload)
 {
-    if (stopping_.load() || shards_.empty() || !healthy_.load()) return false;
-    if (round16(payload.size()) > cfg_.max_payload_bytes) return false;
-    r.name_ = std::move(toolName);
-    r.payload_ = std::move(payload);
-    r.rc_ = 0;
-    r.done_.store(false, std::memory_order_relaxed);
-    Pending* p = new Pending;
-    p->name = &r.name_;
-    p->payload.swap(r.payload_);
-    p->async = &r;
-    const uint64_t id = next_id_.fetch_add(1);
+    if (r.arena_) return Enqueue::kRefused;                  // still in flight
+    if (stopping_.load() || shards_.empty() || !healthy_.load()) return Enqueue::kRefused;
+    if (round16(payload.size()) > cfg_.max_payload_bytes || payload.size() >= Arena::kUncommitted) return Enqueue::kRefused;
+    if (toolName.size() > cfg_.max_name_bytes_per_request) return Enqueue::kRefused;
+    // the id (hence the shard) is taken only once the request is in: a busy shard must not skew the others
+    const uint64_t id = next_id_.load(std::memory_order_relaxed);
     Shard* s = shards_[id % shards_.size()].get();
-    if (!push(s, p)) { r.payload_.swap(p->payload); delete p; r.done_.store(true); return false; }
+    Ticket t;
+    switch (reserve(s, toolName, payload.data(), payload.size(), t, false)) {
+    case Reserve::kBusy:   return Enqueue::kBusy;
+    case Reserve::kClosed: return Enqueue::kRefused;
+    case Reserve::kOk:     break;
+    }
+    next_id_.fetch_add(1, std::memory_order_relaxed);
+    r.rc_ = 0;
+    r.idx_ = t.idx;
+    r.gen_ = t.gen;
+    r.arena_ = t.a;
+    return Enqueue::kAccepted;
+}
+
+bool AsyncRequest::done()
+{
+    Arena* a = arena_;
+    if (!a) return true;
+    if (a->gen_done.load(std::memory_order_acquire) != gen_) return false;
+    rc_ = a->rc;
+    if (rc_ == 0) decision_ = a->out[idx_];
+    arena_ = nullptr;
+    std::atomic_ref<uint32_t>(a->rec[idx_].len).store(Arena::kUncommitted, std::memory_order_release);   // picked up: our last access
     return true;
 }
 
+AsyncRequest::~AsyncRequest()
+{
+    while (!done()) std::this_thread::yield();
+}
+
+// Flusher only.  The batch's records are in a.out (or rc says why not): publish the whole batch
+// with one store; its callers pick their records up themselves.
 void BatchingService::complete(Shard* s, Arena& a, int rc)
 {
-    if (rc == 0) rc = s->be->wait((uint32_t)(&a - s->arenas.data()));
     log_batch(s, a, rc);
     if (rc != 0) {
-        healthy_.store(false);
+        if (s->be->is_device_failure(rc)) healthy_.store(false);
         std::lock_guard<std::mutex> g(s->mu);
         ++s->st.errors;
     }
-    {
-        std::lock_guard<std::mutex> w(s->done_mu);
-        for (size_t i = 0; i < a.reqs.size(); ++i) {
-            Pending* p = a.reqs[i];
-            if (AsyncRequest* r = p->async) {
-                r->rc_ = rc;
-                if (rc == 0) r->decision_ = a.out[i];
-                r->payload_.swap(p->payload);                // hand the buffer back for reuse
-                delete p;
-                r->done_.store(true, std::memory_order_release);   // r may be reused from here on
-                continue;
-            }
-            p->rc = rc;
-            if (rc == 0) p->decision = a.out[i];
-            p->done.store(true, std::memory_order_release);  // p may be gone from here on
-        }
-    }
-    s->done_cv.notify_all();
-    a.reqs.clear();
-    a.inflight = false;
+    a.rc = rc;
+    a.picked_up = 0;
+    a.gen_done.store(a.gen, std::memory_order_release);
+    a.gen_done.notify_all();
+}
+
+// Flusher only: make arena `slot` the one producers reserve in.
+void BatchingService::open_arena(Shard* s, uint32_t slot)
+{
+    Arena& a = *s->arenas[slot];                             // every rec[i].len reads kUncommitted again: its callers saw to that
+    a.n = 0;
+    ++a.gen;
+    a.state.store(0, std::memory_order_seq_cst);             // publishes gen and the reset lengths
+    s->open.store(slot, std::memory_order_release);
+    s->open_seq.fetch_add(1, std::memory_order_release);
+    s->open_seq.notify_all();
 }
 
 void BatchingService::flusher(Shard* s)
 {
-    const size_t depth = s->arenas.size();
-    std::deque<size_t> inflight;                            // submitted slots, oldest first
-    std::vector<size_t> free_slots;
-    for (size_t i = depth; i-- > 0;) free_slots.push_back(i);
+    struct Flight { uint32_t arena, be_slot; };
+    std::deque<Flight> inflight;                            // submitted, oldest first
+    std::deque<uint32_t> draining;                          // completed; callers are still picking records up
+    std::vector<uint32_t> free_arenas, free_be;
+    for (uint32_t i = (uint32_t)s->arenas.size(); i-- > 0;) free_arenas.push_back(i);
+    for (uint32_t i = s->be->slots(); i-- > 0;) free_be.push_back(i);
 
+    auto reap = [&] {
+        for (size_t k = 0; k < draining.size();) {
+            Arena& d = *s->arenas[draining[k]];
+            while (d.picked_up < d.n &&
+                   std::atomic_ref<uint32_t>(d.rec[d.picked_up].len).load(std::memory_order_acquire) == Arena::kUncommitted)
+                ++d.picked_up;
+            if (d.picked_up == d.n) {
+                free_arenas.push_back(draining[k]);
+                draining.erase(draining.begin() + (ptrdiff_t)k);
+            } else {
+                ++k;
+            }
+        }
+    };
     auto finish_oldest = [&] {
-        const size_t slot = inflight.front();
+        const Flight f = inflight.front();
         inflight.pop_front();
-        complete(s, s->arenas[slot], 0);
-        free_slots.push_back(slot);
+        Arena& a = *s->arenas[f.arena];
+        complete(s, a, s->be->wait(f.be_slot));
+        free_be.push_back(f.be_slot);
+        draining.push_back(f.arena);
+    };
+    // An arena nobody is reading any more.  Finishes batches (blocks on the device) if that is what
+    // it takes; producers keep filling the open batch meanwhile.
+    auto take_free_arena = [&]() -> uint32_t {
+        for (;;) {
+            reap();
+            if (!free_arenas.empty()) { const uint32_t k = free_arenas.back(); free_arenas.pop_back(); return k; }
+            if (!inflight.empty()) { finish_oldest(); continue; }
+            cpu_relax();                                    // all completed, some records not yet picked up
+        }
     };
 
+    uint32_t open = take_free_arena();
+    open_arena(s, open);
+    auto first_seen = Clock::time_point{};                  // when the flusher first saw the open batch non-empty
+    bool have_first = false;
     for (;;) {
-        drain(s);
-        if (s->backlog.empty()) {
+        Arena& a = *s->arenas[open];
+        uint64_t st = a.state.load(std::memory_order_seq_cst);
+        if (Arena::count_of(st) == 0 && !(st & Arena::kSealed)) {
+            have_first = false;
             if (!inflight.empty()) { finish_oldest(); continue; }   // nothing new: finish the oldest batch now
-            // closed-loop callers come back within microseconds of their last answer: poll for
-            // them before paying for a futex sleep and its wake-up
-            const auto spin_until = Clock::now() + std::chrono::microseconds(cfg_.flusher_spin_us);
-            while (s->queued.load(std::memory_order_acquire) == 0 && !stopping_.load() && Clock::now() < spin_until)
-                cpu_relax();
-            if (s->queued.load() == 0) {
-                if (stopping_.load()) {
-                    if (close_inboxes(s)) return;
-                    continue;
+            reap();
+            if (stopping_.load()) {
+                // shut the door; a producer that slipped in first still gets its batch
+                st = a.state.fetch_or(Arena::kSealed) | Arena::kSealed;
+                if (Arena::count_of(st) == 0) break;
+            } else {
+                // closed-loop callers come back within microseconds of their last answer: poll for
+                // them before paying for a futex sleep and its wake-up
+                const auto spin_until = Clock::now() + std::chrono::microseconds(cfg_.flusher_spin_us);
+                while (a.state.load(std::memory_order_acquire) == 0 && !stopping_.load() && Clock::now() < spin_until)
+                    cpu_relax();
+                if (a.state.load() == 0 && !stopping_.load()) {
+                    std::unique_lock<std::mutex> lk(s->mu);
+                    s->sleeping.store(true);                 // seq_cst, then the predicate: see wake_flusher()
+                    s->cv.wait(lk, [&] { return a.state.load() != 0 || stopping_.load(); });
+                    s->sleeping.store(false);
                 }
-                std::unique_lock<std::mutex> lk(s->mu);
-                s->sleeping.store(true);                     // seq_cst, then the predicate: see push()
-                s->cv.wait(lk, [&] { return s->queued.load() != 0 || stopping_.load(); });
-                s->sleeping.store(false);
+                continue;
             }
+        }
+        if (!have_first) { first_seen = Clock::now(); have_first = true; }
+        // a batch is open: take it now (work-conserving), or hold it for more / the deadline of its first request
+        bool full = (st & Arena::kSealed) != 0 || Arena::count_of(st) >= cfg_.max_batch, went_idle = false;
+        const bool eager = cfg_.eager_flush && !full;       // a busy GPU makes the next batch bigger by itself
+        if (!eager && !full && !stopping_.load()) {
+            const auto deadline = first_seen + std::chrono::microseconds(cfg_.max_wait_us);
+            const auto idle = std::chrono::microseconds(cfg_.idle_flush_us ? cfg_.idle_flush_us : cfg_.max_wait_us);
+            for (;;) {
+                const uint64_t seen = a.state.load(std::memory_order_acquire);
+                const auto until = std::min(deadline, Clock::now() + idle);
+                if (idle <= std::chrono::microseconds(100)) {
+                    // a short window is polled: a timed futex wait of 20 µs returns after 70 (timer slack)
+                    while (a.state.load(std::memory_order_acquire) == seen && Clock::now() < until) cpu_relax();
+                } else {
+                    std::unique_lock<std::mutex> lk(s->mu);
+                    s->sleeping.store(true);
+                    s->cv.wait_until(lk, until, [&] {
+                        const uint64_t v = a.state.load();
+                        return (v & Arena::kSealed) != 0 || Arena::count_of(v) >= cfg_.max_batch || stopping_.load();
+                    });
+                    s->sleeping.store(false);
+                }
+                st = a.state.load(std::memory_order_acquire);
+                full = (st & Arena::kSealed) != 0 || Arena::count_of(st) >= cfg_.max_batch;
+                if (full || stopping_.load()) break;
+                const auto now = Clock::now();
+                if (now >= deadline) break;
+                if (st == seen && now >= until) { went_idle = true; break; }   // nothing new arrived
+            }
+        }
+        // the arena the NEXT batch opens in, before this one is sealed: producers never find the door shut
+        // for longer than it takes to swap two words
+        const uint32_t next = take_free_arena();
+        st = a.state.fetch_or(Arena::kSealed);
+        const uint32_t n = Arena::count_of(st);
+        full = full || n >= cfg_.max_batch;
+        open_arena(s, next);                                // producers carry on in the next arena
+        have_first = false;
+        if (n == 0) {                                       // sealed empty (shutdown race): nothing to route
+            free_arenas.push_back(open);
+            open = next;
             continue;
         }
-        // a batch is open: take it now (work-conserving), or hold it for more / the deadline of its first request
-        const auto deadline = Clock::now() + std::chrono::microseconds(cfg_.max_wait_us);
-        const auto idle = std::chrono::microseconds(cfg_.idle_flush_us ? cfg_.idle_flush_us : cfg_.max_wait_us);
-        bool full = s->backlog.size() >= cfg_.max_batch, went_idle = false;
-        const bool eager = cfg_.eager_flush && !full;       // a busy GPU makes the next batch bigger by itself
-        while (!eager && !full && !stopping_.load()) {
-            const size_t before = s->backlog.size();
-            const uint32_t seen = s->queued.load(std::memory_order_acquire);
-            const auto until = std::min(deadline, Clock::now() + idle);
-            if (idle <= std::chrono::microseconds(100)) {
-                // a short window is polled: a timed futex wait of 20 µs returns after 70 (timer slack)
-                while (s->queued.load(std::memory_order_acquire) == seen && Clock::now() < until) cpu_relax();
-            } else {
-                std::unique_lock<std::mutex> lk(s->mu);
-                s->sleeping.store(true);
-                s->cv.wait_until(lk, until, [&] { return s->queued.load() != seen || stopping_.load(); });
-                s->sleeping.store(false);
-            }
-            drain(s);
-            full = s->backlog.size() >= cfg_.max_batch;
-            if (full) break;
-            const auto now = Clock::now();
-            if (now >= deadline) break;
-            if (s->backlog.size() == before && now >= until) { went_idle = true; break; }   // nothing new arrived
-        }
-        if (free_slots.empty()) {                           // free the slot we are about to reuse
-            finish_oldest();
-            drain(s);                                       // and take along what arrived meanwhile
-        }
-        const size_t slot = free_slots.back();
-        free_slots.pop_back();
-        Arena& a = s->arenas[slot];
-        uint64_t at = 0;
-        uint32_t n = 0;
+        // the last producers may still be copying: wait for their commits
+        // and spread the records into the arrays the C ABI takes
         a.bytes = 0;
-        while (!s->backlog.empty() && n < cfg_.max_batch) {
-            Pending* p = s->backlog.front();
-            const uint64_t sz = round16(p->payload.size());
-            if (at + sz > cfg_.max_payload_bytes) break;    // arena full: the rest goes to the next batch
-            s->backlog.pop_front();
-            a.pay_off[n] = at;
-            a.pay_len[n] = (uint32_t)p->payload.size();
-            a.bytes += p->payload.size();
-            a.reqs.push_back(p);
-            at += sz;
-            ++n;
+        for (uint32_t i = 0; i < n; ++i) {
+            Arena::Rec& rec = a.rec[i];
+            uint32_t len;
+            while ((len = std::atomic_ref<uint32_t>(rec.len).load(std::memory_order_acquire)) == Arena::kUncommitted) cpu_relax();
+            a.pay_off[i] = (uint64_t)rec.off16 << 4;
+            a.pay_len[i] = len;
+            a.name_off[i] = rec.noff;
+            a.bytes += len;
         }
-        s->queued.fetch_sub(n);
-        const bool was_full = n >= cfg_.max_batch;          // (an eager batch may have filled while a slot was awaited)
-        a.trigger = (full || was_full) ? "full" : eager ? "eager" : went_idle ? "idle" : "deadline";
+        a.pay_off[n] = Arena::pay16_of(st) << 4;
+        a.name_off[n] = Arena::names_of(st);
+        a.n = n;
+        a.trigger = full ? "full" : eager ? "eager" : went_idle ? "idle" : "deadline";
         a.t_submit_ns = std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now().time_since_epoch()).count();
         {
             std::lock_guard<std::mutex> g(s->mu);
             ++s->st.batches;
             s->st.requests += n;
-            if (full || was_full) ++s->st.flush_full; else if (eager) ++s->st.flush_eager;
+            if (full) ++s->st.flush_full; else if (eager) ++s->st.flush_eager;
             else if (went_idle) ++s->st.flush_idle; else ++s->st.flush_deadline;
             if (n > s->st.max_batch_seen) s->st.max_batch_seen = n;
         }
-
-        // pack outside the lock: one memcpy per request into the (pinned) arena — gRPC buffers
-        // live on the caller's heap and cannot be DMA sources
-        a.names.clear();
-        for (uint32_t i = 0; i < n; ++i) {
-            const Pending* p = a.reqs[i];
-            if (!p->payload.empty()) std::memcpy(a.payload + a.pay_off[i], p->payload.data(), p->payload.size());
-            a.name_off[i] = (uint32_t)a.names.size();
-            a.names.insert(a.names.end(), p->name->begin(), p->name->end());
-        }
-        a.pay_off[n] = at;
-        a.name_off[n] = (uint32_t)a.names.size();
-        const int rc = s->be->submit((uint32_t)slot, a.payload, a.pay_off.data(), a.pay_len.data(),
-                                     a.names.data(), a.name_off.data(), n, a.out);
+        if (free_be.empty()) finish_oldest();               // a device slot for this batch
+        const uint32_t be_slot = free_be.back();
+        free_be.pop_back();
+        const int rc = s->be->submit(be_slot, a.payload, a.pay_off.data(), a.pay_len.data(), a.names,
+                                     a.name_off.data(), n, a.out);
         if (rc != 0) {
             complete(s, a, rc);                             // fail exactly this batch's requests
-            free_slots.push_back(slot);
+            free_be.push_back(be_slot);
+            draining.push_back(open);
         } else {
-            a.inflight = true;
-            inflight.push_back(slot);
+            inflight.push_back(Flight{open, be_slot});
         }
+        open = next;
     }
+    // stopping, the open batch sealed empty: refuse further reservations, finish what is in flight
+    s->closed.store(true, std::memory_order_release);
+    s->open.store(kNone, std::memory_order_release);
+    s->open_seq.fetch_add(1, std::memory_order_release);
+    s->open_seq.notify_all();
+    while (!inflight.empty()) finish_oldest();
+    // give callers a moment to pick their last records up (an abandoned AsyncRequest must not hang shutdown)
+    const auto give_up = Clock::now() + std::chrono::seconds(5);
+    for (reap(); !draining.empty() && Clock::now() < give_up; reap()) std::this_thread::yield();
 }
 
 }  // namespace polykey

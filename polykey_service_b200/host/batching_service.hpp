@@ -9,18 +9,24 @@
 //     srv     := server.NewServer(batched)
 //
 // grpc-go calls ExecuteTool from one goroutine (here: thread) per in-flight RPC, concurrently
-// and without a limit (main.go:74-77), so this is a multi-producer / single-consumer design:
-// callers enqueue and block on their own request; ONE flusher thread per GPU coalesces the
-// queue into the flat arenas of include/pk_route.h (size- or deadline-triggered), crosses the
-// C ABI once per batch (pk_submit / pk_wait, `pipeline_depth` batches in flight), hands each
-// caller its 24-byte decision, and the caller then delegates to the inner service for the
-// response body — so the gRPC surface and mock.go stay unchanged.
+// and without a limit (main.go:74-77).  Every caller packs ITS OWN request: it reserves a
+// record index and a byte range of the open batch with one compare-and-swap on a packed
+// (count, payload bytes, name bytes) word, copies its payload and tool name straight into the
+// page-locked arenas of include/pk_route.h, and commits by storing its length.  The ONE flusher
+// thread per GPU never touches request bytes: it seals the open batch (size-, deadline- or
+// work-conserving trigger), opens the next arena so producers carry on, waits for the last
+// commits, crosses the C ABI once (pk_submit / pk_wait, `pipeline_depth` batches in flight) and
+// publishes the whole batch with one store; each caller then reads its own 24-byte decision
+// out of the record array and delegates to the inner service for the response body — so the
+// gRPC surface and mock.go stay unchanged.  (Round 1 packed on the flusher thread: one memcpy
+// per request on one core capped the seam at 3e6 requests/s.)
 //
 // Requests shard across GPUs by request id (id % n_gpus); there is no exchange between GPUs.
 // A device error is returned to every request of the failed batch as a plain error (surfaced
-// verbatim by server.go:37-40, i.e. gRPC Unknown) and flips healthy() to false so main can
-// set health to NOT_SERVING (main.go:93-94).  Shutdown() drains the queues before
-// GracefulStop (main.go:118-119).
+// verbatim by server.go:37-40, i.e. gRPC Unknown); a CUDA / device failure also flips healthy()
+// to false so main can set health to NOT_SERVING (main.go:93-94) — a rejected batch (bad
+// argument, capacity) fails its own requests only.  Shutdown() drains before GracefulStop
+// (main.go:118-119).
 #pragma once
 #include <atomic>
 #include <condition_variable>
@@ -37,13 +43,16 @@ class RouteBackend {
 public:
     virtual ~RouteBackend() = default;
     virtual uint32_t slots() const = 0;
-    // memory the flusher packs batches into (pinned for the CUDA backend)
+    // memory the producers pack batches into (pinned for the CUDA backend)
     virtual void* alloc_host(size_t bytes) = 0;
     virtual int submit(uint32_t slot, const uint8_t* payload, const uint64_t* pay_off,
                        const uint32_t* pay_len, const uint8_t* names, const uint32_t* name_off,
                        uint32_t n, pk_decision* out) = 0;
     virtual int wait(uint32_t slot) = 0;
     virtual std::string error_string(int status) = 0;
+    // is this status a failure of the device (health goes NOT_SERVING), as opposed to a batch
+    // the device refused (only its requests fail)?
+    virtual bool is_device_failure(int status) const { return status == PK_ERR_CUDA || status == PK_ERR_NO_DEVICE; }
 };
 
 // libpkroute.so through its C ABI (include/pk_route.h).  No CPU fallback: construction
@@ -68,7 +77,7 @@ private:
 };
 
 struct BatchingConfig {
-    uint32_t max_batch = 4096;             // requests per flush
+    uint32_t max_batch = 4096;             // requests per flush (<= 65536)
     uint32_t max_wait_us = 200;            // deadline from the first queued request
     uint32_t idle_flush_us = 20;           // flush earlier once no request has arrived for this long
                                            // (a closed population of callers is all queued by then)
@@ -80,12 +89,16 @@ struct BatchingConfig {
     bool eager_flush = true;
     // Waiting without the kernel's help.  A futex sleep costs 10-70 µs to get out of (wake-up
     // latency, timer slack) — more than the GPU takes to route a small batch — so short waits poll:
-    uint32_t flusher_spin_us = 100;        // an idle flusher polls its queue this long before it sleeps
+    uint32_t flusher_spin_us = 100;        // an idle flusher polls its open batch this long before it sleeps
     uint32_t caller_spin_us = 150;         // a caller polls for its decision this long before it sleeps ...
     uint32_t caller_spin_max_waiters = 8;  // ... unless more callers than this are already waiting (they would
                                            // only steal cores from each other and from the flusher)
-    uint64_t max_payload_bytes = 32u << 20;
-    uint32_t max_name_bytes_per_request = 64;
+    uint64_t max_payload_bytes = 32u << 20;   // payload arena per batch (<= 1 GiB)
+    // A request's tool name may be at most this long to be ROUTED.  A longer name cannot equal any
+    // table entry (PK_MAX_TOOL_NAME is 64), so it is the switch's default branch whatever its
+    // bytes (mock.go:60-64): ExecuteTool answers it through the inner service without a routing
+    // decision instead of letting one client's oversized name fail a whole batch.
+    uint32_t max_name_bytes_per_request = 256;
     // One summary record per routed batch: the reference writes three
     // synchronous log lines per REQUEST (main.go:33, 44-48; server.go:28-33), which dominate its
     // CPU path; a batching front-end can say the same once per flush.  JSON lines in the style of
@@ -100,20 +113,69 @@ struct BatchingStats {
 
 class BatchingService;
 
+namespace detail {
+// One batch under construction / in flight: the flat arrays of include/pk_route.h in memory the
+// backend allocated, plus the words producers and the flusher meet on.  One per backend slot.
+struct Arena {
+    // ---- written by producers ----
+    uint8_t* payload = nullptr;            // page-locked; request i at payload[16 * rec[i].off16 ..)
+    uint8_t* names = nullptr;
+    pk_decision* out = nullptr;            // page-locked; the device's records
+    // What a producer says about its request, in ONE 16-byte record (four to a cache line) rather
+    // than in the three arrays the C ABI takes: a request then dirties one shared line, not three.
+    // len == kUncommitted until the producer has copied its bytes, and again once the caller has
+    // picked its record up (each caller marks its own word: no counter every caller of a batch
+    // would fight over).  The flusher spreads the records into pay_off / pay_len / name_off.
+    struct Rec { uint32_t off16, len, noff, reserved; };
+    std::vector<Rec> rec;
+    // ---- written by the flusher (the arrays of include/pk_route.h) ----
+    std::vector<uint64_t> pay_off;
+    std::vector<uint32_t> pay_len;
+    std::vector<uint32_t> name_off;
+    // ---- reservation: [sealed:1][count:17][payload bytes / 16 : 26][name bytes : 20] ----
+    alignas(64) std::atomic<uint64_t> state{kSealed};
+    // ---- completion ----
+    alignas(64) std::atomic<uint32_t> gen_done{0};   // generation whose records are in `out`
+    int rc = 0;                            // status of generation gen_done (written before gen_done)
+    uint32_t gen = 0;                      // generation being filled / in flight (flusher writes, before opening)
+    // ---- flusher-private ----
+    uint32_t n = 0;
+    uint32_t picked_up = 0;                // records [0, picked_up) of the completed batch have been picked up
+    uint64_t bytes = 0;
+    const char* trigger = "";              // "full" | "idle" | "deadline" | "eager"
+    int64_t t_submit_ns = 0;
+
+    static constexpr uint64_t kSealed = 1ull << 63;
+    static constexpr uint32_t kUncommitted = 0xFFFFFFFFu;
+    static constexpr unsigned kCountShift = 46, kPayShift = 20;
+    static constexpr uint64_t kCountMask = (1ull << 17) - 1, kPayMask = (1ull << 26) - 1, kNameMask = (1ull << 20) - 1;
+    static uint32_t count_of(uint64_t st) { return (uint32_t)((st >> kCountShift) & kCountMask); }
+    static uint64_t pay16_of(uint64_t st) { return (st >> kPayShift) & kPayMask; }
+    static uint32_t names_of(uint64_t st) { return (uint32_t)(st & kNameMask); }
+};
+}  // namespace detail
+
 // One request handed to the routing stage without blocking (BatchingService::EnqueueAsync): an
 // event-loop server — or the open-loop load generator of latency_bench — owns the storage, polls
-// done(), then reads rc() / decision().  Reusable once done.  Must not move or die while in flight.
+// done() until it is true, then reads rc() / decision().  Reusable once done.  The owner MUST poll
+// an accepted request to completion (the destructor does, if need be): the batch's arena is
+// recycled only after every request of it has picked up its record.  Must not move while in flight,
+// and must be done before the service is destroyed.
 class AsyncRequest {
 public:
-    bool done() const { return done_.load(std::memory_order_acquire); }
+    AsyncRequest() = default;
+    AsyncRequest(const AsyncRequest&) = delete;
+    AsyncRequest& operator=(const AsyncRequest&) = delete;
+    ~AsyncRequest();
+    bool done();                                            // polls; picks the record up the first time it is there
     int rc() const { return rc_; }                          // valid once done(): 0 or a PK_ERR_* / backend status
     const pk_decision& decision() const { return decision_; }
 private:
     friend class BatchingService;
-    std::string name_, payload_;
+    detail::Arena* arena_ = nullptr;                        // set while in flight
+    uint32_t idx_ = 0, gen_ = 0;
     pk_decision decision_{};
     int rc_ = 0;
-    std::atomic<bool> done_{true};
 };
 
 class BatchingService final : public Service {
@@ -125,73 +187,48 @@ public:
     Result ExecuteTool(Context& ctx, const std::string& toolName, const Struct* parameters,
                        const std::string* secretId, const Metadata* metadata) override;
 
-    // Non-blocking form of the routing half of ExecuteTool: queues (toolName, payload) on the shard
-    // its request id selects and returns.  false = not accepted (shut down, unhealthy, too large).
-    bool EnqueueAsync(AsyncRequest& r, std::string toolName, std::string payload);
+    // Non-blocking form of the routing half of ExecuteTool: copies (toolName, payload) into the open
+    // batch of the shard its request id selects and returns at once.
+    //   kAccepted  poll r.done()
+    //   kBusy      every arena of the shard is in flight or still holds records nobody has picked up:
+    //              poll your outstanding requests (that is what frees arenas) and try again —
+    //              back-pressure, never a wait inside this call
+    //   kRefused   shut down, unhealthy, r still in flight, or payload / name too large
+    enum class Enqueue { kAccepted, kBusy, kRefused };
+    Enqueue EnqueueAsync(AsyncRequest& r, const std::string& toolName, const std::string& payload);
 
     void Shutdown();                        // drain + join; further calls fail with an error
     bool healthy() const { return healthy_.load(); }
     BatchingStats stats() const;
 
 private:
-    struct Pending {
-        const std::string* name;
-        std::string payload;
-        pk_decision decision{};
-        int rc = 0;
-        std::atomic<bool> done{false};      // set (release) under Shard::done_mu as the flusher's LAST access
-        AsyncRequest* async = nullptr;      // set: the result goes there and this Pending is the service's to delete
-    };
-    struct Arena {                          // one per backend slot
-        uint8_t* payload = nullptr;
-        pk_decision* out = nullptr;
-        std::vector<uint64_t> pay_off;
-        std::vector<uint32_t> pay_len, name_off;
-        std::vector<uint8_t> names;
-        std::vector<Pending*> reqs;
-        bool inflight = false;
-        uint64_t bytes = 0;                 // payload bytes of the batch in flight
-        const char* trigger = "";           // "full" | "idle" | "deadline" | "eager"
-        int64_t t_submit_ns = 0;
-    };
-    // Producers never meet the flusher on a lock: a caller appends to ONE of kInboxes small
-    // vectors (picked per thread), the flusher swaps each out in O(1) into its private backlog.
-    // With one queue and one mutex, a few hundred thousand enqueues per second from several
-    // threads starved the flusher (and each other) on the futex behind that mutex.
-    struct Inbox {
-        std::mutex mu;
-        std::vector<Pending*> v;
-        bool closed = false;                // set by the exiting flusher: pushes are refused from then on
-    };
-    static constexpr unsigned kInboxes = 8;
+    using Arena = detail::Arena;
+    struct Ticket { Arena* a = nullptr; uint32_t idx = 0, gen = 0; };
+    static constexpr uint32_t kNone = 0xFFFFFFFFu;
     struct Shard {
         RouteBackend* be = nullptr;
-        Inbox inbox[kInboxes];
-        std::deque<Pending*> backlog;       // flusher-private: drained, not yet in a batch
-        std::atomic<uint32_t> queued{0};    // pushed and not yet in a batch (inboxes + backlog)
-        std::atomic<uint32_t> waiting{0};   // callers blocked in ExecuteTool on this shard
-        std::atomic<bool> sleeping{false};  // the flusher is (about to be) in its futex sleep
-        std::mutex mu;                      // guards st, and the flusher's sleep
+        std::vector<std::unique_ptr<Arena>> arenas;
+        alignas(64) std::atomic<uint32_t> open{kNone};      // index of the arena accepting reservations
+        std::atomic<uint32_t> open_seq{0};                  // bumped at every change of `open` (producers wait on it)
+        std::atomic<bool> closed{false};                    // the flusher has exited: reservations are refused
+        alignas(64) std::atomic<uint32_t> waiting{0};       // callers blocked in ExecuteTool on this shard
+        std::atomic<bool> sleeping{false};                  // the flusher is (about to be) in its futex sleep
+        std::mutex mu;                                      // guards st, and the flusher's sleep
         std::condition_variable cv;
-        std::vector<Arena> arenas;
         std::thread th;
         BatchingStats st;
-        // Completion: a whole batch is marked done under done_mu and announced with ONE
-        // notify_all (a futex broadcast) instead of one wake-up call per request.  The waiter,
-        // whose stack owns the Pending, re-checks under done_mu, so it cannot return and destroy
-        // the object while the flusher still touches it.
-        std::mutex done_mu;
-        std::condition_variable done_cv;
     };
-    bool push(Shard* s, Pending* p);        // false: the shard is closed
-    size_t drain(Shard* s);
-    bool close_inboxes(Shard* s);
+    enum class Reserve { kOk, kBusy, kClosed };
+    Reserve reserve(Shard* s, const std::string& name, const void* payload, size_t len, Ticket& t, bool block);
+    void wake_flusher(Shard* s);
     void flusher(Shard* s);
+    void open_arena(Shard* s, uint32_t slot);
     void complete(Shard* s, Arena& a, int rc);
     void log_batch(const Shard* s, const Arena& a, int rc);
 
     Service* inner_;
     BatchingConfig cfg_;
+    uint32_t name_cap_ = 0;                 // name arena bytes per batch
     std::vector<std::unique_ptr<Shard>> shards_;
     std::atomic<uint64_t> next_id_{0};
     std::atomic<bool> stopping_{false}, healthy_{true};

@@ -125,12 +125,19 @@ static OpenResult run_open(BatchingService& svc, double rate, double seconds, si
         for (;;) {
             const auto now = Clock::now();
             if (now >= end && tail == head) break;
-            while (now < end && next <= now) {                        // every arrival that is due
-                ++out.offered;
-                if (head - tail == kRing) { ++out.dropped; next += gap(); continue; }   // generator out of tickets
+            // every arrival that is due — in bursts of at most 32, so that a generator that has fallen
+            // behind still picks records up between bursts (which is what frees arenas) instead of
+            // enqueueing until the front-end pushes back
+            for (int burst = 0; burst < 32 && now < end && next <= now; ++burst) {
+                if (head - tail == kRing) { ++out.offered; ++out.dropped; next += gap(); continue; }   // generator out of tickets
                 AsyncRequest& r = ring[head % kRing];
                 due[head % kRing] = next;
-                if (svc.EnqueueAsync(r, names[head & 3], json)) ++head; else ++out.errors;
+                // the producer's copy of its request into the pinned arena happens in here
+                const BatchingService::Enqueue e = svc.EnqueueAsync(r, names[head & 3], json);
+                if (e == BatchingService::Enqueue::kBusy) break;      // back-pressure: the arrival stays due (its latency keeps
+                                                                      // counting from its scheduled time); go pick records up
+                ++out.offered;
+                if (e == BatchingService::Enqueue::kAccepted) ++head; else ++out.errors;
                 next += gap();
             }
             while (tail < head && ring[tail % kRing].done()) {        // completions, in arrival order
@@ -165,7 +172,11 @@ static int main_open(int argc, char** argv)
     pk_table table;
     pk_default_table(&table);
     // PK_BACKENDS=N: one backend (flusher, table replica) per GPU 0..N-1; requests shard by id
-    const unsigned nb = std::getenv("PK_BACKENDS") ? (unsigned)std::max(1, std::atoi(std::getenv("PK_BACKENDS"))) : 1u;
+    // PK_SHARDS_PER_GPU=K: K backends (handle, flusher thread, arenas) on every GPU — K open batches per GPU
+    // take reservations in parallel, which is what the front-end scales with once one batch's
+    // reservation word is the bottleneck
+    const unsigned per_gpu = std::getenv("PK_SHARDS_PER_GPU") ? (unsigned)std::max(1, std::atoi(std::getenv("PK_SHARDS_PER_GPU"))) : 1u;
+    const unsigned nb = per_gpu * (std::getenv("PK_BACKENDS") ? (unsigned)std::max(1, std::atoi(std::getenv("PK_BACKENDS"))) : 1u);
     std::vector<std::unique_ptr<RouteBackend>> devs;
     std::vector<RouteBackend*> bes;
     for (unsigned g = 0; g < nb; ++g) {
@@ -173,7 +184,7 @@ static int main_open(int argc, char** argv)
             devs.emplace_back(new NullBackend(std::atof(e)));
             if (g == 0) std::fprintf(stderr, "NULL backend: front-end measurement only, nothing is routed\n");
         } else {
-            auto* cb = new CudaBackend((int)g, table, cfg.max_batch, cfg.max_payload_bytes, 3);
+            auto* cb = new CudaBackend((int)(g / per_gpu), table, cfg.max_batch, cfg.max_payload_bytes, 3);
             devs.emplace_back(cb);
             if (!cb->ok()) { std::fprintf(stderr, "no CUDA backend on device %u (status %d): there is no CPU fallback\n", g, cb->status()); return 1; }
         }
@@ -188,10 +199,10 @@ static int main_open(int argc, char** argv)
     svc.Shutdown();
     const double n = (double)r.lat_us.size();
     const uint64_t batches = st.batches - before.batches, reqs = st.requests - before.requests;
-    std::printf("{\"mode\": \"open-loop\", \"backends\": %u, \"offered_per_s\": %.0f, \"generators\": %u, \"max_batch\": %u, \"max_wait_us\": %u, \"idle_flush_us\": %u, \"eager\": %d, "
+    std::printf("{\"mode\": \"open-loop\", \"shards_per_gpu\": %u, \"backends\": %u, \"offered_per_s\": %.0f, \"generators\": %u, \"max_batch\": %u, \"max_wait_us\": %u, \"idle_flush_us\": %u, \"eager\": %d, "
                 "\"payload_bytes\": %zu, \"completed_per_s\": %.1f, \"dropped\": %llu, \"errors\": %llu, "
                 "\"latency_us\": {\"p50\": %.1f, \"p90\": %.1f, \"p99\": %.1f, \"p999\": %.1f, \"max\": %.1f}, \"batches\": %llu, \"mean_batch\": %.1f}\n",
-                nb, rate, gens, cfg.max_batch, cfg.max_wait_us, cfg.idle_flush_us, (int)cfg.eager_flush, payload_bytes, n / r.seconds,
+                per_gpu, nb, rate, gens, cfg.max_batch, cfg.max_wait_us, cfg.idle_flush_us, (int)cfg.eager_flush, payload_bytes, n / r.seconds,
                 (unsigned long long)r.dropped, (unsigned long long)r.errors,
                 pct(r.lat_us, 0.50), pct(r.lat_us, 0.90), pct(r.lat_us, 0.99), pct(r.lat_us, 0.999),
                 r.lat_us.empty() ? 0.0 : *std::max_element(r.lat_us.begin(), r.lat_us.end()),

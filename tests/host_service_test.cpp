@@ -213,30 +213,93 @@ static void test_async()
     BatchingConfig cfg; cfg.max_batch = 64; cfg.max_wait_us = 200; cfg.max_payload_bytes = 1 << 20;
     BatchingService svc(inner.get(), {&be0, &be1}, cfg);
     static const char* names[] = {"example_tool", "struct_tool", "file_tool", "nope"};
+    using Enq = BatchingService::Enqueue;
     std::vector<AsyncRequest> ring(512);
     std::vector<std::string> payloads(ring.size());
-    uint32_t bad = 0;
+    uint32_t bad = 0, busy = 0;
     for (int round = 0; round < 3; ++round) {                                        // requests are reusable
+        size_t polled = 0;                                                           // [0, polled) have been picked up
+        auto poll_one = [&] {
+            while (!ring[polled].done()) std::this_thread::yield();
+            const pk_decision want = oracle_one(be0.table_, names[polled & 3], payloads[polled]);
+            if (ring[polled].rc() != 0 || std::memcmp(&want, &ring[polled].decision(), sizeof want) != 0) ++bad;
+            ++polled;
+        };
         for (size_t i = 0; i < ring.size(); ++i) {
             payloads[i] = "{\"prompt\":\"";
             for (size_t k = 0; k < (i * 7 + round) % 90; ++k) payloads[i] += "tok" + std::to_string(k) + " ";
             payloads[i] += "\"}";
             CHECK(ring[i].done());
-            CHECK(svc.EnqueueAsync(ring[i], names[i & 3], payloads[i]));
+            for (;;) {
+                const Enq e = svc.EnqueueAsync(ring[i], names[i & 3], payloads[i]);
+                if (e == Enq::kAccepted) break;
+                CHECK(e == Enq::kBusy);                                              // never refused
+                if (e != Enq::kBusy) break;
+                ++busy;
+                if (polled < i) poll_one();                                          // picking records up is what frees arenas
+                else std::this_thread::yield();                                      // (busy for a moment: the flusher is between two batches)
+            }
         }
-        for (size_t i = 0; i < ring.size(); ++i) {
-            while (!ring[i].done()) std::this_thread::yield();
-            const pk_decision want = oracle_one(be0.table_, names[i & 3], payloads[i]);
-            if (ring[i].rc() != 0 || std::memcmp(&want, &ring[i].decision(), sizeof want) != 0) ++bad;
-        }
+        while (polled < ring.size()) poll_one();
     }
     CHECK(bad == 0);
     CHECK(be0.requests > 0 && be1.requests > 0 && be0.requests + be1.requests == 3 * ring.size());
+    std::printf("async: 3 x %zu requests, %u enqueue attempts met back-pressure\n", ring.size(), busy);
     AsyncRequest big;
-    CHECK(!svc.EnqueueAsync(big, "example_tool", std::string((2 << 20), 'x')) && big.done());   // over the arena: refused
+    CHECK(svc.EnqueueAsync(big, "example_tool", std::string((2 << 20), 'x')) == Enq::kRefused && big.done());   // over the arena: refused
+    AsyncRequest longname;
+    CHECK(svc.EnqueueAsync(longname, std::string(300, 'n'), "{}") == Enq::kRefused && longname.done());
     svc.Shutdown();
     AsyncRequest late;
-    CHECK(!svc.EnqueueAsync(late, "example_tool", "{}") && late.done());                       // after Shutdown: refused
+    CHECK(svc.EnqueueAsync(late, "example_tool", "{}") == Enq::kRefused && late.done());                       // after Shutdown: refused
+}
+
+// One client's oversized tool name must not take the service down (it did: the device rejected the
+// whole batch and health went NOT_SERVING for good).  A name longer than the routing stage accepts
+// equals no table entry, so it is the reference's default branch — 200, "Unknown tool: ..." —
+// answered by the inner service without a decision; every other request is routed as usual.
+static void test_oversized_name()
+{
+    auto inner = NewMockService();
+    OracleBackend be(2);
+    BatchingConfig cfg; cfg.max_batch = 16; cfg.max_wait_us = 100;
+    BatchingService svc(inner.get(), {&be}, cfg);
+    Context ctx; ctx.now_unix = 1;
+    const std::string huge(100000, 'x');
+    Result r = svc.ExecuteTool(ctx, huge, nullptr, nullptr, nullptr);
+    CHECK(!r.error && r.resp && r.resp->status.code == 200 && !r.resp->decision.has_value());
+    CHECK(std::get<std::string>(r.resp->output) == "Unknown tool: " + huge);            // mock.go:60-64
+    const std::string edge(cfg.max_name_bytes_per_request, 'y');                        // the longest routed name
+    r = svc.ExecuteTool(ctx, edge, nullptr, nullptr, nullptr);
+    CHECK(!r.error && r.resp && r.resp->decision.has_value() && (r.resp->decision->flags & PK_FLAG_UNKNOWN_TOOL));
+    r = svc.ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr);
+    CHECK(!r.error && r.resp && r.resp->decision.has_value() && r.resp->decision->tool_class == 0);
+    CHECK(svc.healthy() && svc.stats().errors == 0);
+}
+
+// A batch the device REFUSES (argument / capacity) fails its own requests and nothing else:
+// health stays SERVING and the next batch is routed.
+static void test_rejected_batch_keeps_health()
+{
+    struct Picky final : RouteBackend {
+        OracleBackend inner{2};
+        int reject_next = 1;
+        uint32_t slots() const override { return 2; }
+        void* alloc_host(size_t b) override { return inner.alloc_host(b); }
+        int submit(uint32_t s, const uint8_t* p, const uint64_t* po, const uint32_t* pl, const uint8_t* nm, const uint32_t* no,
+                   uint32_t n, pk_decision* out) override
+        { if (reject_next > 0) { --reject_next; return PK_ERR_CAPACITY; } return inner.submit(s, p, po, pl, nm, no, n, out); }
+        int wait(uint32_t) override { return PK_OK; }
+        std::string error_string(int s) override { return "picky " + std::to_string(s); }
+    } be;
+    auto inner = NewMockService();
+    BatchingConfig cfg; cfg.max_batch = 8;
+    BatchingService svc(inner.get(), {&be}, cfg);
+    Context ctx;
+    Result r = svc.ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr);
+    CHECK(r.error && !r.resp && svc.healthy());                                         // this request failed, the service did not
+    r = svc.ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr);
+    CHECK(!r.error && r.resp && r.resp->decision.has_value() && svc.healthy() && svc.stats().errors == 1);
 }
 
 static void test_device_error_path()
@@ -289,6 +352,8 @@ int main(int argc, char** argv)
     test_batching(1, 16, 60, 32, false, true);
     test_batching(2, 32, 60, 8, false, true);
     test_async();
+    test_oversized_name();
+    test_rejected_batch_keeps_health();
     test_device_error_path();
     test_cuda_backend_fails_loudly();
     std::printf(g_fail ? "HOST TESTS FAILED (%d)\n" : "HOST TESTS OK\n", g_fail);
