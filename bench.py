@@ -253,14 +253,45 @@ class Ctx:
 
 
 # ------------------------------------------------------------------ CPU arms ------
-def cpu_arm(O, table, batch, threads: int, budget_s: float, switch_only: bool = False, min_reps: int = 2):
-    """Times the CPU port over `batch` repeatedly for about budget_s; returns (requests/s, reps)."""
-    n = int(batch["pay_len"].size)
+def llc_bytes() -> int:
+    """Size of the last-level cache of cpu0 (sysfs), 0 if unknown."""
+    best = 0
+    base = "/sys/devices/system/cpu/cpu0/cache"
+    try:
+        for d in os.listdir(base):
+            try:
+                txt = open(os.path.join(base, d, "size")).read().strip()
+                mult = {"K": 1 << 10, "M": 1 << 20, "G": 1 << 30}.get(txt[-1], 1)
+                best = max(best, int(txt.rstrip("KMG")) * mult)
+            except (OSError, ValueError):
+                continue
+    except OSError:
+        pass
+    return best
+
+
+def cpu_ring(O, n: int, plen: int, threads: int, seed_shift: int = 0):
+    """The CPU arm's inputs: a ring of distinct batches larger than the last-level cache, so that —
+    like the GPU arm, whose ring is larger than L2 and whose end-to-end leg pulls every byte out of
+    host DRAM — each pass streams its payload from memory instead of re-reading one cached batch."""
+    batch_bytes = n * ((plen + 15) & ~15)
+    target = max(256 << 20, 2 * llc_bytes())
+    k = max(2, min(64, -(-target // batch_bytes)))
+    return [O.gen_batch(O.SEED_BASE + 1 + seed_shift, n, plen, mode=0, first_id=(7_000_003 + j) * n, threads=min(threads, 16))
+            for j in range(k)]
+
+
+def cpu_arm(O, table, batches, threads: int, budget_s: float, switch_only: bool = False, min_reps: int = 2):
+    """Times the CPU port over the ring `batches` (a list; one batch = one step) for about budget_s;
+    returns (requests/s, steps)."""
+    if isinstance(batches, dict):
+        batches = [batches]
+    n = int(batches[0]["pay_len"].size)
     out = np.zeros(n, dtype=O.DECISION_DTYPE)                       # reused: no allocation in the timed loop
-    O.route_batch(table, batch, threads=threads, switch_only=switch_only, fast=True, out=out)      # warm
+    O.route_batch(table, batches[-1], threads=threads, switch_only=switch_only, fast=True, out=out)      # warm
     reps, t0 = 0, time.perf_counter()
     while True:
-        rc, _ = O.route_batch(table, batch, threads=threads, switch_only=switch_only, fast=True, out=out)
+        rc, _ = O.route_batch(table, batches[reps % len(batches)], threads=threads, switch_only=switch_only, fast=True, out=out)
         assert rc == 0
         reps += 1
         dt = time.perf_counter() - t0
@@ -286,26 +317,30 @@ def run_reference(args):
     table = O.default_table()
     # bounded sample: for C3 a step is 64 of the 1,024 requests (64 MiB), otherwise the full batch
     n_step = n if n * plen <= (64 << 20) else max(1, (64 << 20) // plen)
-    batches = [O.gen_batch(O.SEED_BASE + 1 + i, n_step, plen, mode=0, threads=min(cores, 16)) for i in range(4)]
+    batches = cpu_ring(O, n_step, plen, cores)                   # larger than the last-level cache
+    nr = len(batches)
     out = np.zeros(n_step, dtype=O.DECISION_DTYPE)
     # the efficient CPU port (oracle/pk_cpu_fast.c) is what is timed; check it against the plain
     # oracle once, outside the timed region
     assert (O.route_batch(table, batches[0], threads=cores, fast=True)[1] ==
             O.route_batch(table, batches[0], threads=cores)[1]).all()
     for w in range(args.warmup):
-        O.route_batch(table, batches[w % 4], threads=cores, fast=True, out=out)
+        O.route_batch(table, batches[(nr - 1 - w) % nr], threads=cores, fast=True, out=out)
     t0 = time.perf_counter()
     for k in range(args.steps):
-        rc, _ = O.route_batch(table, batches[k % 4], threads=cores, fast=True, out=out)
+        rc, _ = O.route_batch(table, batches[k % nr], threads=cores, fast=True, out=out)
         assert rc == 0
     dt = time.perf_counter() - t0
     value = n_step * args.steps / dt
-    v_one, _ = cpu_arm(O, table, batches[0], 1, 1.5)
+    v_one, _ = cpu_arm(O, table, batches, 1, 1.5)
+    v_hot, _ = cpu_arm(O, table, batches[:1], cores, 1.0)            # one batch over and over: cache-resident
     # CPU-A: the reference-faithful work (the switch only) — report the better of all cores / one
-    sw_all, _ = cpu_arm(O, table, batches[0], cores, 1.0, switch_only=True)
-    sw_one, _ = cpu_arm(O, table, batches[0], 1, 1.0, switch_only=True)
+    sw_all, _ = cpu_arm(O, table, batches, cores, 1.0, switch_only=True)
+    sw_one, _ = cpu_arm(O, table, batches, 1, 1.0, switch_only=True)
     sw, sw_cores = (sw_all, cores) if sw_all >= sw_one else (sw_one, 1)
-    sample = f"{args.steps} steps x {n_step} requests x {plen} B ({cpu_port_note(O, cores)})"
+    sample = (f"{args.steps} steps x {n_step} requests x {plen} B over a ring of {nr} distinct batches "
+              f"({nr * n_step * plen >> 20} MiB > last-level cache {llc_bytes() >> 20} MiB: payloads stream from DRAM) "
+              f"({cpu_port_note(O, cores)})")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
@@ -314,7 +349,7 @@ def run_reference(args):
         "parallelism": "host threads (persistent pool), requests in dynamic chunks",
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
                          "one_core": v_one, "scaling_efficiency": value / (v_one * cores), "impl": O.fast_impl(),
-                         "sample_requests_per_step": n_step},
+                         "sample_requests_per_step": n_step, "cache_resident_value": v_hot},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "reference_switch_only": {"value": sw, "unit": UNIT, "cores": sw_cores,
                                   "note": "CPU-A: only the work the Go reference does per request "
@@ -645,12 +680,12 @@ def frontend_leg(ctx: Ctx, seconds: float = 1.5):
             return {"unavailable": f"host/latency_bench could not be built: {e!r}"}
     G = ctx.world
     env = dict(os.environ, PK_BACKENDS=str(G))
-    gens = max(2, min(ctx.cores - 2 * G, 16))
+    gens = max(2, min(ctx.cores - 2 * G - 2, 12))          # leave cores for the flushers and this process
     out = {"gpus": G, "generators": gens, "payload_bytes": 2048, "max_batch": 4096, "max_wait_us": 200,
            "api": "BatchingService::EnqueueAsync -> decision (C++ mirror of the Go batcher), open loop, Poisson arrivals",
            "rates": []}
     # offered rates per GPU: light load (latency = service time), moderate, heavy, and flat out
-    for per_gpu in (1e5, 1e6, 5e6, 2e7):
+    for per_gpu in (1e5, 1e6, 5e6, 1e7):
         rate = per_gpu * G
         try:
             p = subprocess.run([exe, "open", str(int(rate)), str(seconds), "4096", "200", "2048", str(gens)],
@@ -743,15 +778,19 @@ def run_gpu(args):
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only) ----
     cpu_baseline, extra_cpu = None, {}
     if ctx.world == 1 and not args.no_cpu:
-        sample_batch = res["check_batch"] if res["batch_bytes"] <= (64 << 20) else make_sample(O, plen)
-        v_all, reps = cpu_arm(O, ctx.table, sample_batch, ctx.cores, 6.0)
-        v_one, _ = cpu_arm(O, ctx.table, sample_batch, 1, 3.0)
-        v_sw, _ = cpu_arm(O, ctx.table, sample_batch, ctx.cores, 1.0, switch_only=True)
-        v_sw1, _ = cpu_arm(O, ctx.table, sample_batch, 1, 1.0, switch_only=True)
+        n_s = n if res["batch_bytes"] <= (64 << 20) else max(1, (64 << 20) // plen)
+        ring_cpu = cpu_ring(O, n_s, plen, ctx.cores)
+        v_all, reps = cpu_arm(O, ctx.table, ring_cpu, ctx.cores, 6.0)
+        v_one, _ = cpu_arm(O, ctx.table, ring_cpu, 1, 3.0)
+        v_hot, _ = cpu_arm(O, ctx.table, ring_cpu[:1], ctx.cores, 1.0)
+        v_sw, _ = cpu_arm(O, ctx.table, ring_cpu, ctx.cores, 1.0, switch_only=True)
+        v_sw1, _ = cpu_arm(O, ctx.table, ring_cpu, 1, 1.0, switch_only=True)
         cpu_baseline = {"value": v_all, "unit": UNIT, "cores": ctx.cores, "kind": "port",
-                        "sample": f"{reps} passes over one batch of {int(sample_batch['pay_len'].size)} requests x {plen} B "
-                                  f"(about 6 s), {cpu_port_note(O, ctx.cores)}",
-                        "one_core": v_one, "scaling_efficiency": v_all / (v_one * ctx.cores), "impl": O.fast_impl()}
+                        "sample": f"{reps} steps of {n_s} requests x {plen} B (about 6 s) over a ring of {len(ring_cpu)} distinct "
+                                  f"batches ({len(ring_cpu) * n_s * plen >> 20} MiB > last-level cache {llc_bytes() >> 20} MiB: "
+                                  f"payloads stream from DRAM), {cpu_port_note(O, ctx.cores)}",
+                        "one_core": v_one, "scaling_efficiency": v_all / (v_one * ctx.cores), "impl": O.fast_impl(),
+                        "cache_resident_value": v_hot}
         extra_cpu = {"cpu_baseline_1core": {"value": v_one, "unit": UNIT, "cores": 1},
                      "cpu_switch_only": {"value": v_sw, "unit": UNIT, "cores": ctx.cores,
                                          "note": "CPU-A: what the Go reference actually does per request "

@@ -253,10 +253,13 @@ static void route_one(const pk_table* t, const uint8_t* p, uint32_t len, const u
     uint32_t tok;
     uint64_t s;
     g_scan_hash(p, len, &tok, &s);
-    for (uint32_t j = 0; j < nlen; ++j) {
-        uint32_t x = ((j << 8) | name[j]) + 1u;
-        x *= P1; x ^= x >> 15; x *= P2; x ^= x >> 13;
-        s += (uint64_t)x * NAME_MUL;
+    for (uint32_t j = 0; 4u * j < nlen; ++j) {                        /* name as 32-bit words, zero padded */
+        uint32_t w = 0;
+        const uint32_t left = nlen - 4u * j;
+        memcpy(&w, name + 4u * j, left < 4u ? left : 4u);
+        uint64_t x = ((uint64_t)(j + 1u) << 32) | w;
+        x *= NAME_MUL; x ^= x >> 32; x *= FMIX_C1;
+        s += x;
     }
     uint64_t h = fmix64(s + ((uint64_t)nlen << 32) + len);
     uint64_t total = 0;

@@ -147,16 +147,19 @@ uint64_t pk_ref_payload_sum(const uint8_t* p, uint64_t len)
     return sum;
 }
 
+/* The tool name's share: the name as little-endian 32-bit words n_j (the last zero padded), word j
+ * contributing mixn((j + 1) << 32 | n_j); mixn(x): x *= NAME_MUL; x ^= x >> 32; x *= FMIX_C1. */
 uint64_t pk_ref_name_sum(const uint8_t* name, uint32_t len)
 {
     uint64_t sum = 0;
-    for (uint32_t j = 0; j < len; ++j) {
-        uint32_t t = (((uint32_t)j << 8) | name[j]) + 1u;
-        t *= SPEC_P1;
-        t ^= t >> 15;
-        t *= SPEC_P2;
-        t ^= t >> 13;
-        sum += (uint64_t)t * SPEC_NAME_MUL;
+    for (uint32_t j = 0; 4u * j < len; ++j) {
+        uint32_t w = 0;
+        for (uint32_t k = 0; k < 4u && 4u * j + k < len; ++k) w |= (uint32_t)name[4u * j + k] << (8u * k);
+        uint64_t x = ((uint64_t)(j + 1u) << 32) | w;
+        x *= SPEC_NAME_MUL;
+        x ^= x >> 32;
+        x *= SPEC_FMIX_C1;
+        sum += x;
     }
     return sum;
 }

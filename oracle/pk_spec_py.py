@@ -9,6 +9,7 @@ M32 = 0xFFFFFFFF
 M64 = 0xFFFFFFFFFFFFFFFF
 P1, P2, P5 = 0x9E3779B1, 0x85EBCA77, 0x165667B1
 NAME_MUL = 0xD6E8FEB86659FD93
+FMIX_C1 = 0xFF51AFD7ED558CCD
 
 
 def rotl(x, r):
@@ -73,14 +74,15 @@ def payload_sum(p: bytes):
 
 
 def name_sum(name: bytes):
+    """Name as little-endian 32-bit words (last one zero padded); word j adds mixn((j+1) << 32 | word)."""
     total = 0
-    for j, b in enumerate(name):
-        t = (((j << 8) | b) + 1) & M32
-        t = (t * P1) & M32
-        t ^= t >> 15
-        t = (t * P2) & M32
-        t ^= t >> 13
-        total = (total + t * NAME_MUL) & M64
+    for j in range((len(name) + 3) // 4):
+        w = int.from_bytes(name[4 * j:4 * j + 4].ljust(4, b"\0"), "little")
+        x = ((j + 1) << 32) | w
+        x = (x * NAME_MUL) & M64
+        x ^= x >> 32
+        x = (x * FMIX_C1) & M64
+        total = (total + x) & M64
     return total
 
 

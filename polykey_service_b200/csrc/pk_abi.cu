@@ -44,6 +44,7 @@ struct pk_handle {
     int        num_sms = 0;
     pk_config  cfg{};
     pk::DevTable* d_table = nullptr;
+    pk::DevTable  table{};              // the same table on the host: it also travels with every launch as a kernel parameter
     size_t     meta_cap = 0;
     uint64_t   max_extra = 0;
     std::vector<Slot> slots;
@@ -186,7 +187,7 @@ int enqueue_uploads(pk_handle* h, Slot& s, const uint8_t* payload, size_t meta_b
 int launch_slot(pk_handle* h, const Slot& s, cudaStream_t stream, bool pdl = false)
 {
     if (s.params.n == 0) return PK_OK;
-    PK_CUDA(h, pk::launch_route(s.params, s.max_len, h->num_sms, stream, pdl));
+    PK_CUDA(h, pk::launch_route(s.params, h->table, s.max_len, h->num_sms, stream, pdl));
     ++h->launches;
     return PK_OK;
 }
@@ -283,10 +284,9 @@ int pk_init(int device, const pk_table* tbl, const pk_config* cfg, pk_handle** o
     PK_INIT_CUDA(cudaSetDevice(device));
     PK_INIT_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device));
     {
-        pk::DevTable dt;
-        pk::make_dev_table(*tbl, dt);
+        pk::make_dev_table(*tbl, h->table);
         PK_INIT_CUDA(cudaMalloc(&h->d_table, sizeof(pk::DevTable)));
-        PK_INIT_CUDA(cudaMemcpy(h->d_table, &dt, sizeof(pk::DevTable), cudaMemcpyHostToDevice));
+        PK_INIT_CUDA(cudaMemcpy(h->d_table, &h->table, sizeof(pk::DevTable), cudaMemcpyHostToDevice));
     }
     PK_INIT_CUDA(cudaEventCreate(&h->ev0));
     PK_INIT_CUDA(cudaEventCreate(&h->ev1));
@@ -347,9 +347,8 @@ int pk_update_table(pk_handle* h, const pk_table* tbl)
     if (rc) return rc;
     rc = pk_sync(h);
     if (rc) return rc;
-    pk::DevTable dt;
-    pk::make_dev_table(*tbl, dt);
-    PK_CUDA(h, cudaMemcpy(h->d_table, &dt, sizeof(pk::DevTable), cudaMemcpyHostToDevice));
+    pk::make_dev_table(*tbl, h->table);
+    PK_CUDA(h, cudaMemcpy(h->d_table, &h->table, sizeof(pk::DevTable), cudaMemcpyHostToDevice));
     return PK_OK;
 }
 
@@ -391,7 +390,7 @@ int pk_submit(pk_handle* h, uint32_t slot, const uint8_t* payload, const uint64_
             P.name_off = reinterpret_cast<const uint32_t*>(in_host_blob(P.name_off));
             P.names    = in_host_blob(P.names);
             P.out      = reinterpret_cast<pk_decision*>(const_cast<uint8_t*>(d_out));
-            PK_CUDA(h, pk::launch_route(P, s.max_len, h->num_sms, s.stream));
+            PK_CUDA(h, pk::launch_route(P, h->table, s.max_len, h->num_sms, s.stream));
             ++h->launches;
             ++h->direct_batches;
             PK_CUDA(h, cudaEventRecord(s.done, s.stream));

@@ -55,7 +55,7 @@ constexpr int      kPartialSlots = 32 * 65;   // >= G * (R + 1) for every (G, R)
 constexpr uint32_t kTinyWarpMax = 8192;       // launch_route: batches of tiny payloads up to this size take a warp per request
                                               // (serial µs, packed vs warp each: 1 request 4.3 / 2.2, 1,024: 6.1 / 2.9,
                                               // 4,096: 6.3 / 3.8, 8,192: 6.5 / 5.6, 16,384: 7.7 / 13.2)
-constexpr uint32_t kNameStage   = 4096;       // bytes of tool names a CTA stages in shared memory
+constexpr uint32_t kNameStage   = 3072;       // bytes of tool names a CTA stages in shared memory
 
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p)
 {
@@ -190,23 +190,30 @@ __device__ __forceinline__ void scan_segment(const uint8_t* __restrict__ pay, ui
     tok    = tok128 >> 7;
 }
 
-// A payload of at most G blocks scanned by a group of G lanes: one block per lane, one step.
-// x is the lane's (already loaded) block; lanes past the payload's last block hold zeros.
-__device__ __forceinline__ void scan_tiny(uint4 x, uint32_t len, uint32_t lig, uint32_t one,
+// A payload of at most G * B blocks scanned by a group of G lanes: lane `lig` owns blocks
+// lig, lig + G, ... (B of them at most), each block its own stripe (block k of a payload this
+// short is stripe k).  x[] are the lane's (already loaded) blocks; blocks past the payload's last
+// hold zeros and are skipped.
+template <int G, int B>
+__device__ __forceinline__ void scan_tiny(const uint4 (&x)[B], uint32_t len, uint32_t lig, uint32_t one,
                                           uint64_t& digest, uint32_t& tok)
 {
-    const uint32_t nblk = (len >> 4) + ((len & 15u) ? 1u : 0u);       // <= G
+    const uint32_t nblk = (len + 15u) >> 4;                            // <= G * B
     uint32_t tok128 = 0;
     digest = 0ull;
-    if (lig < nblk) {
-        Words4 w = {{x.x, x.y, x.z, x.w}};
-        const uint32_t valid = len - lig * kBlockBytes;
-        if (valid < kBlockBytes) mask_tail(w, valid);
-        Stripe st;
-        stripe_init(st, lig);
-        stripe_round(st, w);
-        digest = stripe_digest(st);
-        scan_block(w, one, tok128);
+#pragma unroll
+    for (int b = 0; b < B; ++b) {
+        const uint32_t k = lig + (uint32_t)b * G;
+        if (k < nblk) {
+            Words4 w = {{x[b].x, x[b].y, x[b].z, x[b].w}};
+            const uint32_t valid = len - k * kBlockBytes;
+            if (valid < kBlockBytes) mask_tail(w, valid);
+            Stripe st;
+            stripe_init(st, k);
+            stripe_round(st, w);
+            digest += stripe_digest(st);
+            scan_block(w, one, tok128);
+        }
     }
     tok = tok128 >> 7;
 }
@@ -250,26 +257,33 @@ __device__ __forceinline__ WarpPrologue warp_prologue(const RouteParams& P, uint
     uint4 row = make_uint4(0u, 0u, 0u, 0u);
     if (lane < np) row = __ldg(reinterpret_cast<const uint4*>(&tbl->t.providers[lane]));
     const uint32_t my_tool_len = lane < nt ? __ldg(&tbl->t.tools[lane].name_len) : 0xFFFFFFFFu;
-    const uint32_t c0 = lane < nlen ? (uint32_t)__ldg(nm + lane) : 0u;
-    const uint32_t c1 = lane + 32u < nlen ? (uint32_t)__ldg(nm + lane + 32u) : 0u;
+    // lane j holds word j of the name (bytes 4j .. 4j+3, zero padded): the same register feeds the
+    // hash term and the comparison with the table's (word-aligned, zero-padded) names
+    const uint32_t nwords = (nlen + 3u) >> 2;
+    uint32_t wj = 0u;
+    if (lane < nwords) {
+#pragma unroll
+        for (uint32_t k = 0; k < 4; ++k)
+            if (4u * lane + k < nlen) wj |= (uint32_t)__ldg(nm + 4u * lane + k) << (8u * k);
+    }
     w.max_tokens = row.x; w.weight = row.y; w.tool_mask = row.z;
 
     uint64_t d = 0;
-    if (lane < nlen)       d += name_term(lane, c0);
-    if (lane + 32u < nlen) d += name_term(lane + 32u, c1);
-    for (uint32_t j = lane + 64u; j < nlen; j += 32) d += name_term(j, __ldg(nm + j));
+    if (lane < nwords) d = name_term(lane, wj);
+    for (uint32_t j = lane + 32u; j < nwords; j += 32) d += name_term(j, name_word(nm, nlen, j));   // names over 128 bytes
     w.name_digest = d;
 
     // tool switch (mock.go:32-64): whole-name byte equality, first match wins.  Lane t holds
-    // entry t's length; candidates are the entries of the request's length, in table order.
+    // entry t's length; candidates are the entries of the request's length, in table order
+    // (a table name has at most 64 bytes = 16 words, so lanes 0..15 decide).
     uint32_t unknown = 0x80000000u;
     uint32_t cand = __ballot_sync(kFull, my_tool_len == nlen);
     while (cand != 0u) {
         const uint32_t t = (uint32_t)__ffs((int)cand) - 1u;
         cand &= cand - 1u;
         bool ok = true;
-        if (lane < nlen)       ok = (__ldg(&tbl->t.tools[t].name[lane]) == c0);
-        if (lane + 32u < nlen) ok = ok && (__ldg(&tbl->t.tools[t].name[lane + 32u]) == c1);
+        if (lane < nwords && lane < PK_MAX_TOOL_NAME / 4u)
+            ok = __ldg(reinterpret_cast<const uint32_t*>(tbl->t.tools[t].name) + lane) == wj;
         if (__all_sync(kFull, ok)) { cls = __ldg(&tbl->t.tools[t].class_id); unknown = 0u; break; }
     }
     w.cls = cls | unknown;
@@ -334,21 +348,28 @@ __device__ __forceinline__ void fold_long_segment(const RouteParams& P, uint32_t
     decide_call(P.table, P.names + noff, P.name_off[req + 1] - noff, len, total, ttok, P.out + req);
 }
 
-template <int G, bool kWarpFinal>
-__device__ __forceinline__ void route_body(const RouteParams& P)
+// T is the routing table as a kernel parameter (constant bank: every thread reads the same rows, so
+// its loads are uniform LDCs that cost no shared memory, no staging and no LSU slot); P.table is
+// the same table in global memory for the few places that index it per lane.
+template <int G, bool kWarpFinal, int B>
+__device__ __forceinline__ void route_body(const RouteParams& P, const DevTable& T)
 {
     static_assert(!kWarpFinal || G == 32, "latency mode finalises with the full warp");
+    static_assert(G < 32 || B == 1, "B: blocks per lane of the lane-group kernels");
+    constexpr uint32_t kRmax = G == 32 ? 64u : G == 16 ? 128u : 256u;   // launch_route's r_max
+    static_assert(kRmax <= (uint32_t)kThreads, "one thread per request stages its offsets and finalises it");
     __shared__ uint64_t psum[kPartialSlots];     // [k][R+1]: lane-in-group k's digest for request i
     __shared__ uint16_t ptok[kPartialSlots];      // a lane sees at most 512 bytes of a segment: its count fits 16 bits
-    __shared__ DevTable s_tbl;                   // the routing table, staged once per CTA
-    __shared__ __align__(16) uint8_t s_names[kNameStage];   // this CTA's tool names, when they fit
+    __shared__ __align__(16) uint8_t s_names[kNameStage + 8];   // this CTA's tool names, when they fit (+8: decide reads whole words)
+    __shared__ uint32_t s_noff[kRmax + 1];       // this CTA's name offsets
+    __shared__ uint64_t s_meta[G < 32 ? kRmax : 1u];   // lane-group kernels: (payload offset / 16) << 12 | length, per request
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t wid  = threadIdx.x >> 5;
     const uint32_t R    = P.reqs_per_cta;
     const uint32_t n_req_ctas = (P.n + R - 1u) / R;
 
-    if (blockIdx.x >= n_req_ctas) {
+    if (G == 32 && blockIdx.x >= n_req_ctas) {       // (a lane-group batch has no request longer than 256 bytes)
         // ---- extra segments (>= 1) of long requests: one warp per (request, segment) ----
         const uint32_t task = (blockIdx.x - n_req_ctas) * kWarpsPerCta + wid;
         if (task >= P.n_extra) return;
@@ -390,13 +411,21 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
     constexpr uint32_t kGroups = 32u / G;
     const uint32_t grp = lane / G, lig = lane % G;
 
-    // ---- prologue.  Phase 2 reads the table and the tool names out of shared memory.  Only the
-    //      two offsets that bound this CTA's names are REQUESTED here; everything that depends on
-    //      a load — the name bytes, the table rows and their stores — waits until after the scan,
-    //      so no warp stalls on a staging round trip before its first payload load is out. ----
-    static_assert(sizeof(DevTable) % 16 == 0, "DevTable is copied as uint4");
-    const uint32_t names_lo = __ldg(P.name_off + base_req);
-    const uint32_t names_hi = __ldg(P.name_off + base_req + r_here);
+    // ---- prologue.  Phase 2 reads the name offsets and the tool names out of shared memory; the
+    //      offsets are requested here (consumed after the barrier that follows the scan), the name
+    //      bytes after the scan, so no warp stalls on a staging round trip before its first payload
+    //      load is out. ----
+    if (threadIdx.x < r_here) s_noff[threadIdx.x + 1] = __ldg(P.name_off + base_req + threadIdx.x + 1);
+    if (threadIdx.x == 0) s_noff[0] = __ldg(P.name_off + base_req);
+    if (G < 32) {
+        // lane-group kernels: every request's length and offset in one coalesced sweep, so the scan
+        // loop below reads them with one LDS instead of two dependent global loads and 64-bit
+        // address arithmetic per request (every payload here is at most 256 bytes: 12 bits)
+        if (threadIdx.x < r_here)
+            s_meta[threadIdx.x] = ((__ldg(P.pay_off + base_req + threadIdx.x) >> 4) << 12) |
+                                  (uint64_t)__ldg(P.pay_len + base_req + threadIdx.x);
+        __syncthreads();
+    }
 
     // ---- phase 1: scan (first segment of) each request ----
     if (G == 32) {
@@ -426,63 +455,50 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
             ptok[lane * ld + i] = (uint16_t)tok;
         }
     } else {
-        // tiny payloads: one block per lane.  The NEXT request's length and offset are loaded while
-        // this one is scanned, so an iteration waits for one memory round trip, not two; anything
-        // deeper (payload blocks of several requests in flight) spills at 32 registers and was
-        // slower — occupancy (8 CTAs per SM) does the rest of the latency hiding.
+        // tiny payloads: B blocks per lane (all loaded before any is used), one request per lane
+        // group per pass.  Occupancy (8 CTAs per SM) hides the rest of the payload loads' latency.
         constexpr uint32_t kStride = kWarpsPerCta * kGroups;
-        uint32_t i = wid * kGroups + grp;
-        uint32_t len_next = 0u;
-        uint64_t off_next = 0ull;
-        if (i < r_here) {
-            len_next = __ldg(P.pay_len + base_req + i);
-            off_next = __ldg(P.pay_off + base_req + i);
-        }
-        for (; i < r_here; i += kStride) {
-            const uint32_t len = len_next;
-            const uint8_t* pay = P.payload + off_next;
-            if (i + kStride < r_here) {
-                len_next = __ldg(P.pay_len + base_req + i + kStride);
-                off_next = __ldg(P.pay_off + base_req + i + kStride);
+        const uint4* const arena = reinterpret_cast<const uint4*>(P.payload);
+#pragma unroll 1
+        for (uint32_t i = wid * kGroups + grp; i < r_here; i += kStride) {
+            const uint64_t m = s_meta[i];
+            const uint32_t len = (uint32_t)m & 0xFFFu;
+            const uint32_t nblk = (len + 15u) >> 4;
+            const uint4* const src = arena + (m >> 12) + lig;
+            uint4 x[B];
+#pragma unroll
+            for (int b = 0; b < B; ++b) {
+                x[b] = make_uint4(0u, 0u, 0u, 0u);
+                if (lig + (uint32_t)b * G < nblk) x[b] = ldg_stream(src + b * G);
             }
-            const uint32_t nblk = (len >> 4) + ((len & 15u) ? 1u : 0u);
-            uint4 x = make_uint4(0u, 0u, 0u, 0u);
-            if (lig < nblk) x = ldg_stream(reinterpret_cast<const uint4*>(pay) + lig);
             uint64_t digest;
             uint32_t tok;
-            scan_tiny(x, len, lig, P.one, digest, tok);
+            scan_tiny<G, B>(x, len, lig, P.one, digest, tok);
             psum[lig * ld + i] = digest;
             ptok[lig * ld + i] = (uint16_t)tok;
         }
     }
-    // ---- staging for phase 2 (its load latency hides behind the warps still scanning): the table,
-    //      and this CTA's tool names as aligned words (bytes at the two ragged ends, so nothing
-    //      outside [names_lo, names_hi) is read whatever the alignment of the caller's array) ----
-    if (threadIdx.x < sizeof(DevTable) / 16)
-        reinterpret_cast<uint4*>(&s_tbl)[threadIdx.x] = __ldg(reinterpret_cast<const uint4*>(P.table) + threadIdx.x);
+    // ---- staging for phase 2 (its load latency hides behind the warps still scanning): this CTA's
+    //      tool names as aligned words ----
+    const uint32_t names_lo = __ldg(P.name_off + base_req), names_hi = __ldg(P.name_off + base_req + r_here);
     const uint32_t names_sz = names_hi - names_lo;
     const uint8_t* names_src = P.names + names_lo;
     const uint32_t names_head = (uint32_t)(reinterpret_cast<uintptr_t>(names_src) & 3u);   // s_names[names_head] = first name byte
     const bool names_staged = names_sz + 3u <= kNameStage;
     if (names_staged) {
-        const uint8_t* al = names_src - names_head;
-        const uint32_t end = names_head + names_sz;
-        for (uint32_t w = threadIdx.x; w * 4u < end; w += kThreads) {
-            if (w * 4u >= names_head && w * 4u + 4u <= end) {
-                reinterpret_cast<uint32_t*>(s_names)[w] = __ldg(reinterpret_cast<const uint32_t*>(al) + w);
-            } else {
-                for (uint32_t b = w * 4u; b < w * 4u + 4u; ++b)
-                    if (b >= names_head && b < end) s_names[b] = __ldg(al + b);
-            }
-        }
+        // whole aligned words, including the up to three bytes before the first and after the last
+        // name that share a word with them (same word, same page: always readable, never used)
+        const uint32_t* al = reinterpret_cast<const uint32_t*>(names_src - names_head);
+        const uint32_t nw = (names_head + names_sz + 3u) >> 2;
+        for (uint32_t w = threadIdx.x; w < nw; w += kThreads) reinterpret_cast<uint32_t*>(s_names)[w] = __ldg(al + w);
     }
     __syncthreads();
 
     // ---- phase 2: one thread per request ----
-    for (uint32_t t = threadIdx.x; t < r_here; t += kThreads) {
+    if (const uint32_t t = threadIdx.x; t < r_here) {
         const uint32_t req = base_req + t;
-        const uint32_t len = __ldg(P.pay_len + req);
-        if (G == 32 && len > kSegBytes) continue;        // finalised by its last segment
+        const uint32_t len = G < 32 ? ((uint32_t)s_meta[t] & 0xFFFu) : __ldg(P.pay_len + req);
+        if (G == 32 && len > kSegBytes) return;          // finalised by its last segment
         uint64_t sum = 0;
         uint32_t tok = 0;
 #pragma unroll
@@ -490,12 +506,12 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
             sum += psum[k * ld + t];
             tok += ptok[k * ld + t];
         }
-        const uint32_t noff = __ldg(P.name_off + req);
-        const uint32_t nlen = __ldg(P.name_off + req + 1) - noff;
-        // table and names both in shared memory (the usual case): decide() inlined on shared-memory
-        // operands — LDS instead of generic loads through uniform-register descriptors
-        if (names_staged) decide(&s_tbl, s_names + names_head + (noff - names_lo), nlen, len, sum, tok, P.out + req);
-        else              decide_call(&s_tbl, P.names + noff, nlen, len, sum, tok, P.out + req);
+        const uint32_t noff = s_noff[t];
+        const uint32_t nlen = s_noff[t + 1] - noff;
+        // names in shared memory (the usual case): decide() inlined, the name read as whole words,
+        // the table out of the constant bank
+        if (names_staged) decide<true>(&T, s_names + names_head + (noff - names_lo), nlen, len, sum, tok, P.out + req);
+        else              decide_call(P.table, P.names + noff, nlen, len, sum, tok, P.out + req);
     }
 }
 
@@ -508,11 +524,12 @@ __device__ __forceinline__ void route_body(const RouteParams& P)
 // complete) without holding anything back.  What two launches of the SAME slot share is that
 // slot's long-request scratch, so launch_route never sets pdl for a batch with long requests —
 // those are bandwidth-bound launches of hundreds of µs that have nothing to gain from overlap.
-template <int G, bool kWarpFinal>
-__global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : PK_MIN_CTAS_TINY) route_kernel(const RouteParams P)
+template <int G, bool kWarpFinal, int B>
+__global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : PK_MIN_CTAS_TINY)
+route_kernel(const RouteParams P, const __grid_constant__ DevTable T)
 {
     if (P.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    route_body<G, kWarpFinal>(P);
+    route_body<G, kWarpFinal, B>(P, T);
     if (P.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
@@ -557,8 +574,8 @@ uint32_t pow2_floor(uint32_t x)
 }  // namespace
 
 namespace {
-template <int G, bool kWarpFinal>
-cudaError_t launch_one(const RouteParams& p, uint32_t ctas, cudaStream_t stream)
+template <int G, bool kWarpFinal, int B = 1>
+cudaError_t launch_one(const RouteParams& p, const DevTable& table, uint32_t ctas, cudaStream_t stream)
 {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(ctas);
@@ -569,16 +586,22 @@ cudaError_t launch_one(const RouteParams& p, uint32_t ctas, cudaStream_t stream)
     attr.val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = &attr;
     cfg.numAttrs = p.pdl ? 1u : 0u;
-    return cudaLaunchKernelEx(&cfg, route_kernel<G, kWarpFinal>, p);
+    return cudaLaunchKernelEx(&cfg, route_kernel<G, kWarpFinal, B>, p, table);
 }
 }  // namespace
 
-cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl)
+cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl)
 {
     if (p.n == 0) return cudaSuccess;
     pdl = pdl && p.n_extra == 0u;       // long requests share their slot's scratch between launches: no overlap
     // lanes per request: a full warp, or a half / quarter warp when every payload fits one step
-    int G = max_len <= 8u * kBlockBytes ? 8 : max_len <= 16u * kBlockBytes ? 16 : 32;
+    // Up to 128 bytes: 8 lanes, a block each.  Up to 256 bytes: 8 lanes, TWO blocks each — against 16
+    // lanes with one block each, a warp pass then covers four requests instead of two for the same
+    // loop overhead, both loads of a lane are in flight together, and phase 2 adds 8 partials per
+    // request instead of 16 (PK_TINY_SHAPE=16 selects the old shape, for comparison).
+    static const char* const t_env = std::getenv("PK_TINY_SHAPE");
+    int G = max_len <= 16u * kBlockBytes ? 8 : 32, B = max_len <= 8u * kBlockBytes ? 1 : 2;
+    if (G == 8 && B == 2 && t_env && std::atoi(t_env) == 16) { G = 16; B = 1; }
     // Few tiny requests: a warp each (latency mode below) beats packing them 2 or 4 to a warp —
     // the packed path pays a CTA barrier and a second phase that only pay off when warps are scarce.
     static const char* const g_env = std::getenv("PK_TINY_WARP_MAX");      // tuning aid: largest such batch
@@ -612,9 +635,9 @@ cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStrea
     if (m_env && G == 32) warp_final = std::atoi(m_env) != 0;
     cudaError_t le;
     switch (G) {
-    case 8:  le = launch_one<8, false>(p, ctas, stream); break;
-    case 16: le = launch_one<16, false>(p, ctas, stream); break;
-    default: le = warp_final ? launch_one<32, true>(p, ctas, stream) : launch_one<32, false>(p, ctas, stream); break;
+    case 8:  le = B == 2 ? launch_one<8, false, 2>(p, table, ctas, stream) : launch_one<8, false, 1>(p, table, ctas, stream); break;
+    case 16: le = launch_one<16, false>(p, table, ctas, stream); break;
+    default: le = warp_final ? launch_one<32, true>(p, table, ctas, stream) : launch_one<32, false>(p, table, ctas, stream); break;
     }
     if (le != cudaSuccess) return le;
 #if PK_TMA

@@ -26,7 +26,7 @@ struct RouteParams {
     const uint8_t*  names;
     const uint32_t* name_off;    // n+1
     const uint2*    extra;       // (request, segment) for segments >= 1 of long requests
-    const DevTable* table;       // device-resident routing table (+ tool-name sums)
+    const DevTable* table;       // the routing table in global memory (launch_route also passes it by value)
     SegScratch*     scratch;     // n entries, zero
     pk_decision*    out;         // n
     uint32_t        n;
@@ -40,6 +40,7 @@ struct RouteParams {
 // scan+hash+select kernel on `stream`.  max_len: the longest payload of the batch.
 // pdl: launch with programmatic stream serialization (programmatic dependent launch) — the grid
 // may start while the previous kernel of the stream is still running; see route_kernel.
-cudaError_t launch_route(RouteParams p, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl = false);
+// table: the host copy of *p.table — it also travels as a kernel parameter (constant bank).
+cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl = false);
 
 }  // namespace pk

@@ -131,7 +131,7 @@ extern "C" int pk_route_device_noalloc(const pk_table* table,
     P.out      = d_out;
     P.n        = n;
     P.n_extra  = n_extra;
-    if (pk::launch_route(P, max_payload_len, ds->num_sms, st) != cudaSuccess) {
+    if (pk::launch_route(P, dt, max_payload_len, ds->num_sms, st) != cudaSuccess) {
         (void)cudaGetLastError();
         return PK_ERR_CUDA;
     }

@@ -181,14 +181,28 @@ PK_HD uint64_t stripe_digest(const Stripe& s)
     return fmix64(((uint64_t)hi << 32) | lo);
 }
 
-PK_HD uint64_t name_term(uint32_t j, uint32_t byte)
+// SPEC §C, the tool name's share of the hash.  The name is read as little-endian 32-bit words
+// (the last one zero padded; the true length enters route_hash_final); word j contributes
+// mixn((j + 1) << 32 | word) — an injective 64-bit input, two multiplications — and the terms
+// add up mod 2^64 like the payload's stripe digests, in any order.
+PK_HD uint64_t name_term(uint32_t j, uint32_t word)
 {
-    uint32_t t = ((j << 8) | byte) + 1u;
-    t *= kP1;
-    t ^= t >> 15;
-    t *= kP2;
-    t ^= t >> 13;
-    return (uint64_t)t * kNameMul;
+    uint64_t x = ((uint64_t)(j + 1u) << 32) | word;
+    x *= kNameMul;
+    x ^= x >> 32;
+    x *= kFmixC1;
+    return x;
+}
+
+// word j of a name: bytes 4j .. 4j+3, little endian, zero past name_len.  Byte loads: any
+// pointer, any alignment.
+PK_HD uint32_t name_word(const uint8_t* name, uint32_t name_len, uint32_t j)
+{
+    uint32_t w = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < 4; ++k)
+        if (4u * j + k < name_len) w |= (uint32_t)name[4u * j + k] << (8u * k);
+    return w;
 }
 
 PK_HD uint64_t route_hash_final(uint64_t sum, uint32_t pay_len, uint32_t name_len)
@@ -208,7 +222,7 @@ struct alignas(16) DevTable {
 PK_HD uint64_t name_sum(const uint8_t* name, uint32_t len)
 {
     uint64_t s = 0;
-    for (uint32_t j = 0; j < len; ++j) s += name_term(j, name[j]);
+    for (uint32_t j = 0; 4u * j < len; ++j) s += name_term(j, name_word(name, len, j));
     return s;
 }
 
@@ -246,65 +260,91 @@ PK_HD bool provider_eligible(const pk_provider& e, uint32_t cls, uint32_t tok)
 // the top 32 bits of the route hash: x = (hi32(hash) * W) >> 32, first provider whose
 // cumulative weight exceeds x.
 //
-// Written for latency, since one thread walks it alone: the first 16 name bytes are read once,
-// in one batch of independent loads, and kept packed in four registers — they feed the hash
-// terms and the comparison against the table (whose names are word-aligned) four bytes at a
-// time; longer names fall back to byte loops for the remainder.  The provider loops are
-// unrolled by four so that their table loads are in flight together.
+// Written for instruction count, since 32 of these run per warp-instruction and the whole batch
+// pays for them: the name is handled as 32-bit words (the hash terms and the comparison with the
+// table, whose names are word-aligned and zero padded, use the same four registers); provider
+// eligibility is evaluated ONCE per provider into a 32-bit mask that the pick then replays
+// (the "first p whose running weight exceeds x" is the number of running weights <= x, since
+// they only grow); rows past n_providers are zero in the device table and need no test.
+//   kWordLoads   the name may be read as aligned 32-bit words, up to 7 bytes past its end (true
+//                for names staged in shared memory, which is padded); otherwise byte loads
+template <bool kWordLoads = false>
 PK_HD void decide(const DevTable* __restrict__ tbl, const uint8_t* __restrict__ name,
                   uint32_t name_len, uint32_t pay_len, uint64_t payload_sum, uint32_t tok,
                   pk_decision* __restrict__ out)
 {
-    uint32_t nw[4] = {0u, 0u, 0u, 0u};               // name bytes 0..15, little endian, zero padded
+    const uint32_t nwords = (name_len + 3u) >> 2;
+    auto word = [&](uint32_t j) -> uint32_t {
+#if defined(__CUDA_ARCH__)
+        if (kWordLoads) {
+            const uintptr_t a = reinterpret_cast<uintptr_t>(name);
+            const uint32_t* al = reinterpret_cast<const uint32_t*>(a & ~uintptr_t(3)) + j;
+            const uint32_t w = __funnelshift_r(al[0], al[1], (uint32_t)(a & 3u) * 8u);
+            const uint32_t valid = name_len - 4u * j;                 // > 0: callers ask for j < nwords only
+            return valid >= 4u ? w : (w & ((1u << (8u * valid)) - 1u));
+        }
+#endif
+        return name_word(name, name_len, j);
+    };
+    uint32_t nw[4] = {0u, 0u, 0u, 0u};               // name bytes 0..15 as words, zero padded
     uint64_t nsum = 0;
 #pragma unroll
-    for (uint32_t j = 0; j < 16; ++j) {
-        if (j < name_len) {
-            const uint32_t b = name[j];
-            nw[j >> 2] |= b << (8u * (j & 3u));
-            nsum += name_term(j, b);
+    for (uint32_t j = 0; j < 4; ++j) {
+        if (j < nwords) {
+            nw[j] = word(j);
+            nsum += name_term(j, nw[j]);
         }
     }
-    for (uint32_t j = 16; j < name_len; ++j) nsum += name_term(j, name[j]);
+    for (uint32_t j = 4; j < nwords; ++j) nsum += name_term(j, word(j));
 
     uint32_t cls = tbl->t.default_class;
     uint32_t unknown = 1;
     const uint32_t nt = tbl->t.n_tools;
     for (uint32_t t = 0; t < nt; ++t) {
         const pk_tool& e = tbl->t.tools[t];
-        if (e.name_len != name_len || tbl->tool_name_sum[t] != nsum) continue;
-        // confirm: the switch is exact byte equality.  pk_tool::name is 4-byte aligned and zero
-        // padded past name_len (pk_init / pk_update_table check that), so the head compares as words.
+        if (e.name_len != name_len) continue;
+        // the switch is exact byte equality.  pk_tool::name is 4-byte aligned and zero padded past
+        // name_len (pk_init / pk_update_table see to that), so equal lengths and equal words are equal bytes.
         const uint32_t* tw = reinterpret_cast<const uint32_t*>(e.name);
         bool same = (tw[0] == nw[0]) & (tw[1] == nw[1]) & (tw[2] == nw[2]) & (tw[3] == nw[3]);
-        for (uint32_t j = 16; same && j < name_len; ++j) same = e.name[j] == name[j];
+        for (uint32_t j = 4; same && j < nwords; ++j) same = tw[j] == word(j);      // names of 17..64 bytes
         if (same) { cls = e.class_id; unknown = 0; break; }
     }
 
     const uint64_t h = route_hash_final(payload_sum + nsum, pay_len, name_len);
 
+    // pass 1: which providers are eligible (one bit each — there are at most 32) and their total weight
     const uint32_t np = tbl->t.n_providers;
-    uint32_t total = 0;
-    for (uint32_t p0 = 0; p0 < np; p0 += 4) {
+    uint32_t elig = 0, total = 0;
 #pragma unroll
-        for (uint32_t u = 0; u < 4; ++u) {
-            // rows past n_providers are zero (weight 0 = not eligible): safe to read, add nothing
-            const pk_provider& e = tbl->t.providers[(p0 + u) & (PK_MAX_PROVIDERS - 1u)];
-            total += (p0 + u < np && provider_eligible(e, cls, tok)) ? e.weight : 0u;
-        }
+    for (uint32_t u = 0; u < 8; ++u) {
+        const pk_provider& e = tbl->t.providers[u];           // rows past n_providers: weight 0, not eligible
+        const bool ok = provider_eligible(e, cls, tok);
+        elig |= ok ? (1u << u) : 0u;
+        total += ok ? e.weight : 0u;
     }
+    for (uint32_t p = 8; p < np; ++p) {
+        const pk_provider& e = tbl->t.providers[p];
+        const bool ok = provider_eligible(e, cls, tok);
+        elig |= ok ? (1u << p) : 0u;
+        total += ok ? e.weight : 0u;
+    }
+    // pass 2: the first provider whose running eligible weight exceeds x = the number of running
+    // weights <= x (they only grow)
     uint32_t prov = PK_PROVIDER_NONE;
     if (total != 0u) {
-        const uint32_t x = (uint32_t)(((uint64_t)(uint32_t)(h >> 32) * (uint64_t)total) >> 32);
-        uint32_t cum = 0;
-        for (uint32_t p0 = 0; p0 < np && prov == PK_PROVIDER_NONE; p0 += 4) {
+        const uint32_t x = (uint32_t)(((uint64_t)(uint32_t)(h >> 32) * (uint64_t)total) >> 32);   // < total
+        uint32_t cum = 0, before = 0;
 #pragma unroll
-            for (uint32_t u = 0; u < 4; ++u) {
-                const pk_provider& e = tbl->t.providers[(p0 + u) & (PK_MAX_PROVIDERS - 1u)];
-                cum += (p0 + u < np && provider_eligible(e, cls, tok)) ? e.weight : 0u;
-                if (cum > x && prov == PK_PROVIDER_NONE) prov = p0 + u;
-            }
+        for (uint32_t u = 0; u < 8; ++u) {
+            cum += ((elig >> u) & 1u) ? tbl->t.providers[u].weight : 0u;
+            before += cum <= x ? 1u : 0u;
         }
+        for (uint32_t p = 8; before == p && p < np; ++p) {    // not among the first eight
+            cum += ((elig >> p) & 1u) ? tbl->t.providers[p].weight : 0u;
+            before += cum <= x ? 1u : 0u;
+        }
+        prov = before;                                        // < np: the running weight reaches total > x
     }
 
     const uint32_t flags = (prov == PK_PROVIDER_NONE ? PK_FLAG_NO_PROVIDER : 0u) |
