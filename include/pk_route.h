@@ -160,9 +160,9 @@ PK_API int  pk_route_batch(pk_handle* h,
                     const uint8_t* names, const uint32_t* name_off /* n+1 */,
                     uint32_t n, pk_decision* out /* n */);
 
-/* Batches up to a size skip the copies.  When a batch's payload + metadata come to at most
- * `bytes` (default 16 MiB; 0 turns the path off), it has no request longer than 16 KiB, and
- * `payload` and `out` are page-locked host memory the GPU can address (pk_host_alloc, or any
+/* Batches up to a size skip the copies.  When the bytes of a batch's payloads (gaps between
+ * requests not counted) + its metadata come to at most `bytes` (default 16 MiB; 0 turns the path
+ * off), and `payload` and `out` are page-locked host memory the GPU can address (pk_host_alloc, or any
  * cudaHostAlloc / cudaHostRegister'ed block), pk_submit / pk_route_batch launch the kernel
  * directly on the caller's buffers: it reads the bytes over PCIe and writes the records into
  * `out` — one launch instead of copy, copy, launch, copy.  Same records; the buffers must stay

@@ -86,7 +86,7 @@ int validate_table(const pk_table* t)
 // and the payload byte range to copy in *pay_begin / *pay_bytes.
 int prepare(pk_handle* h, Slot& s, const uint64_t* pay_off, const uint32_t* pay_len,
             const uint8_t* names, const uint32_t* name_off, uint32_t n, size_t* meta_bytes,
-            uint64_t* pay_begin, uint64_t* pay_bytes)
+            uint64_t* pay_begin, uint64_t* pay_bytes, uint64_t* read_bytes = nullptr)
 {
     if (n > h->cfg.max_requests) return PK_ERR_CAPACITY;
     if (!pay_off || !pay_len || !name_off) return PK_ERR_ARG;
@@ -105,6 +105,7 @@ int prepare(pk_handle* h, Slot& s, const uint64_t* pay_off, const uint32_t* pay_
     const uint32_t nbase = name_off[0];
     uint64_t n_extra = 0;
     uint64_t end = base;
+    uint64_t touched = 0;               // bytes the kernel will read: whole 16-byte blocks of every payload, no gaps
     uint32_t max_len = 0;
     for (uint32_t i = 0; i < n; ++i) {
         const uint64_t o = pay_off[i], nx = pay_off[i + 1];
@@ -128,7 +129,9 @@ int prepare(pk_handle* h, Slot& s, const uint64_t* pay_off, const uint32_t* pay_
             }
         }
         end = o + l;
+        touched += ((uint64_t)l + 15u) & ~uint64_t(15);
     }
+    if (read_bytes) *read_bytes = touched;
     m_off[n]  = pay_off[n] - base;
     m_noff[n] = name_off[n] - nbase;
     const uint64_t name_bytes = (uint64_t)name_off[n] - nbase;
@@ -363,15 +366,18 @@ int pk_submit(pk_handle* h, uint32_t slot, const uint8_t* payload, const uint64_
     if (!out) return PK_ERR_ARG;
     PK_CUDA(h, cudaSetDevice(h->device));
     size_t meta_bytes = 0;
-    uint64_t pb = 0, pbytes = 0;
+    uint64_t pb = 0, pbytes = 0, touched = 0;
     s.staged = false;
-    int rc = prepare(h, s, pay_off, pay_len, names, name_off, n, &meta_bytes, &pb, &pbytes);
+    int rc = prepare(h, s, pay_off, pay_len, names, name_off, n, &meta_bytes, &pb, &pbytes, &touched);
     if (rc) return rc;
     // Small batch in page-locked memory: no copies at all.  The kernel reads the payload and the
     // metadata blob straight out of host memory and writes its records straight into `out`, so the
     // call is ONE launch instead of copy, copy, launch, copy — each of which costs a few µs of
     // submission and completion latency that a small batch cannot amortise.
-    if (pbytes + meta_bytes <= h->direct_bytes && s.params.n_extra == 0) {
+    // (What counts against the threshold is what the kernel will read, not the span of the arena:
+    // a caller that gives every request a fixed slot leaves gaps that cost nothing here, where a
+    // copy would move them.)
+    if (touched + meta_bytes <= h->direct_bytes) {
         const uint8_t* d_pay = pbytes ? device_view(h, payload + pb, pbytes) : s.d_payload;
         const uint8_t* d_out = device_view(h, out, (size_t)n * sizeof(pk_decision));
         // the kernel reads 16-byte vectors at d_pay + pay_off[i] and stores 8-byte words into out:
@@ -388,6 +394,7 @@ int pk_submit(pk_handle* h, uint32_t slot, const uint8_t* payload, const uint64_
             P.pay_off  = reinterpret_cast<const uint64_t*>(in_host_blob(P.pay_off));
             P.pay_len  = reinterpret_cast<const uint32_t*>(in_host_blob(P.pay_len));
             P.name_off = reinterpret_cast<const uint32_t*>(in_host_blob(P.name_off));
+            P.extra    = reinterpret_cast<const uint2*>(in_host_blob(P.extra));
             P.names    = in_host_blob(P.names);
             P.out      = reinterpret_cast<pk_decision*>(const_cast<uint8_t*>(d_out));
             PK_CUDA(h, pk::launch_route(P, h->table, s.max_len, h->num_sms, s.stream));

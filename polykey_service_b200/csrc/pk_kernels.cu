@@ -618,6 +618,10 @@ cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len,
     // R = 8; alone, the R = 64 batch takes 15 µs).
     // No more than 256 KiB of payload per CTA, so long payloads keep the thin shape.
     if (pdl) R = std::min(pow2_floor(p.n / 16u + 1u), pow2_floor((256u << 10) / (max_len ? max_len : 1u) + 1u));
+    // ... and no more than 128 requests per CTA for the lane-group kernels: with 256 the grid of a
+    // 65,536-request batch is 256 CTAs whose second phase runs one request per thread with nothing
+    // left to overlap it (65,536 x 256 B: 5.25 µs per batch at 128, 5.65 at 256, 5.89 at 64).
+    if (pdl && G < 32) R = std::min(R, 128u);
     static const char* const r_env = std::getenv("PK_REQS_PER_CTA");     // tuning aid (power of two)
     if (r_env && std::atoi(r_env) > 0) R = pow2_floor((uint32_t)std::atoi(r_env));
     R = R < r_min ? r_min : R > r_max ? r_max : R;

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 
 namespace polykey {
@@ -60,12 +61,11 @@ using detail::Arena;
 BatchingService::BatchingService(Service* inner, std::vector<RouteBackend*> backends, BatchingConfig cfg)
     : inner_(inner), cfg_(cfg)
 {
-    // the packed reservation word bounds what one batch can hold
     cfg_.max_batch = std::max<uint32_t>(1u, std::min<uint32_t>(cfg_.max_batch, 65536u));
-    cfg_.max_payload_bytes = std::min<uint64_t>(cfg_.max_payload_bytes & ~uint64_t(15), (uint64_t)Arena::kPayMask << 4);
-    cfg_.max_name_bytes_per_request = std::min<uint32_t>(cfg_.max_name_bytes_per_request, 4096u);
-    name_cap_ = (uint32_t)std::min<uint64_t>((uint64_t)cfg_.max_batch * std::max<uint32_t>(cfg_.max_name_bytes_per_request, 64u),
-                                             Arena::kNameMask);
+    cfg_.max_name_bytes_per_request = std::max<uint32_t>(64u, std::min<uint32_t>(cfg_.max_name_bytes_per_request, 4096u));
+    slot_bytes_ = std::max<uint64_t>(16u, (cfg_.max_payload_bytes / cfg_.max_batch) & ~uint64_t(15));
+    cfg_.max_payload_bytes = slot_bytes_ * cfg_.max_batch;   // what a single request can be, too (it then takes every slot)
+    name_stride_ = (cfg_.max_name_bytes_per_request + 15u) & ~15u;
     for (RouteBackend* be : backends) {
         auto s = std::make_unique<Shard>();
         s->be = be;
@@ -75,13 +75,15 @@ BatchingService::BatchingService(Service* inner, std::vector<RouteBackend*> back
         for (uint32_t k = 0; k < n_arenas; ++k) {
             auto a = std::make_unique<Arena>();
             a->payload = static_cast<uint8_t*>(be->alloc_host(cfg_.max_payload_bytes + 64));
-            a->names = static_cast<uint8_t*>(be->alloc_host((size_t)name_cap_ + 64));
             a->out = static_cast<pk_decision*>(be->alloc_host((size_t)cfg_.max_batch * sizeof(pk_decision)));
+            a->long_names = static_cast<uint8_t*>(std::malloc((size_t)cfg_.max_batch * name_stride_));
             a->pay_off.resize(cfg_.max_batch + 1);
             a->pay_len.resize(cfg_.max_batch);
-            a->rec.assign(cfg_.max_batch, Arena::Rec{0, Arena::kUncommitted, 0, 0});
             a->name_off.resize(cfg_.max_batch + 1);
-            if (!a->payload || !a->names || !a->out) healthy_.store(false);
+            a->names.resize((size_t)cfg_.max_batch * cfg_.max_name_bytes_per_request);
+            a->rec.resize(cfg_.max_batch);
+            for (Arena::Rec& r : a->rec) { r.len = Arena::kUncommitted; r.name_len = 0; }
+            if (!a->payload || !a->out || !a->long_names) healthy_.store(false);
             s->arenas.push_back(std::move(a));
         }
         shards_.push_back(std::move(s));
@@ -94,7 +96,12 @@ BatchingService::BatchingService(Service* inner, std::vector<RouteBackend*> back
     for (auto& s : shards_) s->th = std::thread(&BatchingService::flusher, this, s.get());
 }
 
-BatchingService::~BatchingService() { Shutdown(); }
+BatchingService::~BatchingService()
+{
+    Shutdown();
+    for (auto& s : shards_)
+        for (auto& a : s->arenas) std::free(a->long_names);
+}
 
 void BatchingService::Shutdown()
 {
@@ -123,44 +130,60 @@ void BatchingService::wake_flusher(Shard* s)
     s->cv.notify_one();
 }
 
-// Producer side: take a record index and byte ranges of the open batch with one CAS, copy the
-// request in, commit.  Callers have checked that the request fits an EMPTY batch, so a batch
-// without room is a full one: it is sealed for the flusher and the producer moves on to the next.
-// When no batch is open (every arena busy) a blocking caller waits for one; the others get kBusy.
+// Producer side: take the next record index of the open batch (k of them when the payload spans k
+// slots) with one fetch_add, copy the request in, commit.  Callers have checked that the request
+// fits an EMPTY batch.  When no batch is open (every arena busy) a blocking caller waits for one;
+// the others get kBusy.
+//
+// A fetch_add cannot be taken back, so a request that does not fit has still moved the counter.
+// That is harmless because nothing fits after it either (the counter only grows), and because the
+// number of slots that WERE taken is published once, by exactly one party: the producer whose
+// request was the first not to fit (it alone sees a counter still within the batch), or, if the
+// batch never overflowed, whoever set the sealed bit first (it sees the counter at that instant).
 BatchingService::Reserve BatchingService::reserve(Shard* s, const std::string& name, const void* payload, size_t len,
                                                   Ticket& t, bool block)
 {
-    const uint64_t sz16 = round16(len) >> 4;
-    const uint64_t inc = (1ull << Arena::kCountShift) | (sz16 << Arena::kPayShift) | (uint64_t)name.size();
-    const uint64_t cap16 = cfg_.max_payload_bytes >> 4;
+    const uint64_t k = len <= slot_bytes_ ? 1u : (len + slot_bytes_ - 1u) / slot_bytes_;
+    const uint64_t cap = cfg_.max_batch;
     for (;;) {
         const uint32_t seq = s->open_seq.load(std::memory_order_acquire);
-        const uint32_t k = s->open.load(std::memory_order_acquire);
-        if (k != kNone) {
-            Arena& a = *s->arenas[k];
-            uint64_t st = a.state.load(std::memory_order_relaxed);
-            while (!(st & Arena::kSealed)) {
-                const uint32_t cnt = Arena::count_of(st);
-                if (cnt >= cfg_.max_batch || Arena::pay16_of(st) + sz16 > cap16 ||
-                    (uint64_t)Arena::names_of(st) + name.size() > name_cap_) {
-                    a.state.fetch_or(Arena::kSealed);       // full: the flusher takes it from here
-                    wake_flusher(s);
-                    break;
+        const uint32_t slot = s->open.load(std::memory_order_acquire);
+        if (slot != kNone) {
+            Arena& a = *s->arenas[slot];
+            const uint64_t seen = a.state.load(std::memory_order_relaxed);
+            if (!(seen & Arena::kSealed) && seen + k <= cap) {           // do not touch a batch that cannot take us
+                const uint64_t old = a.state.fetch_add(k);               // seq_cst: see wake_flusher()
+                if (!(old & Arena::kSealed)) {
+                    if (old + k <= cap) {
+                        // slots [old, old + k) are ours; the arena cannot be recycled before we commit
+                        const uint32_t i = (uint32_t)old;
+                        t.a = &a; t.idx = i; t.gen = a.gen; t.slots = (uint32_t)k;
+                        if (len) std::memcpy(a.payload + (uint64_t)i * slot_bytes_, payload, len);
+                        Arena::Rec& r = a.rec[i];
+                        r.name_len = (uint32_t)name.size();
+                        if (!name.empty())
+                            std::memcpy(name.size() <= Arena::kInlineName ? r.name : a.long_names + (size_t)i * name_stride_,
+                                        name.data(), name.size());
+                        for (uint64_t j = 1; j < k; ++j) {                 // the indices our payload runs over: empty requests
+                            a.rec[i + j].name_len = Arena::kPlaceholder;
+                            std::atomic_ref<uint32_t>(a.rec[i + j].len).store(0u, std::memory_order_release);
+                        }
+                        std::atomic_ref<uint32_t>(r.len).store((uint32_t)len, std::memory_order_release);   // commit
+                        if (i == 0) wake_flusher(s);                      // a batch has been started
+                        return Reserve::kOk;
+                    }
+                    if (old <= cap) {
+                        // the first request that did not fit: `old` slots were taken, close the batch
+                        a.final_n.store((uint32_t)old, std::memory_order_release);
+                        a.state.fetch_or(Arena::kSealed);
+                        wake_flusher(s);
+                    }
                 }
-                if (!a.state.compare_exchange_weak(st, st + inc, std::memory_order_seq_cst, std::memory_order_relaxed))
-                    continue;
-                // the reservation is ours; the arena cannot be recycled before we commit
-                const uint64_t off = Arena::pay16_of(st) << 4;
-                const uint32_t noff = Arena::names_of(st);
-                t.a = &a; t.idx = cnt; t.gen = a.gen;
-                if (len) std::memcpy(a.payload + off, payload, len);
-                if (!name.empty()) std::memcpy(a.names + noff, name.data(), name.size());
-                Arena::Rec& rec = a.rec[cnt];
-                rec.off16 = (uint32_t)(off >> 4);
-                rec.noff = noff;
-                std::atomic_ref<uint32_t>(rec.len).store((uint32_t)len, std::memory_order_release);   // commit
-                if (cnt == 0) wake_flusher(s);              // a batch has been started
-                return Reserve::kOk;
+            } else if (!(seen & Arena::kSealed) && seen <= cap) {
+                // no room for this request in what is left of the batch: close it for the flusher
+                const uint64_t old = a.state.fetch_or(Arena::kSealed);
+                if (!(old & Arena::kSealed) && old <= cap) a.final_n.store((uint32_t)old, std::memory_order_release);
+                wake_flusher(s);
             }
         }
         if (s->closed.load(std::memory_order_acquire)) return Reserve::kClosed;
@@ -211,7 +234,8 @@ Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, c
     const int rc = a.rc;
     pk_decision decision{};
     if (rc == 0) decision = a.out[t.idx];
-    std::atomic_ref<uint32_t>(a.rec[t.idx].len).store(Arena::kUncommitted, std::memory_order_release);   // picked up: our last access
+    for (uint32_t j = t.slots; j-- > 0;)                     // picked up (placeholders too): our last access
+        std::atomic_ref<uint32_t>(a.rec[t.idx + j].len).store(Arena::kUncommitted, std::memory_order_release);
 
     if (rc != 0) {
         // plain error: server.go:37-40 returns it verbatim (gRPC Unknown)
@@ -232,8 +256,10 @@ void BatchingService::log_batch(const Shard* s, const Arena& a, int rc)
     const int64_t now = std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now().time_since_epoch()).count();
     size_t gpu = 0;
     while (gpu < shards_.size() && shards_[gpu].get() != s) ++gpu;
+    uint64_t requests = 0;
+    for (size_t i = 0; i < a.n; ++i) requests += a.rec[i].name_len != Arena::kPlaceholder;
     std::string line = std::string("{\"level\":\"") + (rc ? "ERROR" : "INFO") + "\",\"msg\":\"routed batch\",\"gpu\":" +
-                       std::to_string(gpu) + ",\"requests\":" + std::to_string(a.n) + ",\"payload_bytes\":" +
+                       std::to_string(gpu) + ",\"requests\":" + std::to_string(requests) + ",\"payload_bytes\":" +
                        std::to_string(a.bytes) + ",\"trigger\":\"" + a.trigger + "\",\"duration\":\"" +
                        LoggingInterceptor::format_duration(now - a.t_submit_ns) + "\"";
     if (rc) {
@@ -241,6 +267,7 @@ void BatchingService::log_batch(const Shard* s, const Arena& a, int rc)
     } else {
         uint64_t cls[4] = {0, 0, 0, 0}, none = 0;
         for (size_t i = 0; i < a.n; ++i) {
+            if (a.rec[i].name_len == Arena::kPlaceholder) continue;      // an index a bigger payload runs over
             ++cls[a.out[i].tool_class & 3u];
             if (a.out[i].flags & PK_FLAG_NO_PROVIDER) ++none;
         }
@@ -270,6 +297,7 @@ BatchingService::Enqueue BatchingService::EnqueueAsync(AsyncRequest& r, const st
     next_id_.fetch_add(1, std::memory_order_relaxed);
     r.rc_ = 0;
     r.idx_ = t.idx;
+    r.slots_ = t.slots;
     r.gen_ = t.gen;
     r.arena_ = t.a;
     return Enqueue::kAccepted;
@@ -283,7 +311,8 @@ bool AsyncRequest::done()
     rc_ = a->rc;
     if (rc_ == 0) decision_ = a->out[idx_];
     arena_ = nullptr;
-    std::atomic_ref<uint32_t>(a->rec[idx_].len).store(Arena::kUncommitted, std::memory_order_release);   // picked up: our last access
+    for (uint32_t j = slots_; j-- > 0;)                      // picked up (placeholders too): our last access
+        std::atomic_ref<uint32_t>(a->rec[idx_ + j].len).store(Arena::kUncommitted, std::memory_order_release);
     return true;
 }
 
@@ -314,7 +343,8 @@ void BatchingService::open_arena(Shard* s, uint32_t slot)
     Arena& a = *s->arenas[slot];                             // every rec[i].len reads kUncommitted again: its callers saw to that
     a.n = 0;
     ++a.gen;
-    a.state.store(0, std::memory_order_seq_cst);             // publishes gen and the reset lengths
+    a.final_n.store(Arena::kUnset, std::memory_order_relaxed);
+    a.state.store(0, std::memory_order_seq_cst);             // publishes gen and final_n
     s->open.store(slot, std::memory_order_release);
     s->open_seq.fetch_add(1, std::memory_order_release);
     s->open_seq.notify_all();
@@ -362,6 +392,18 @@ void BatchingService::flusher(Shard* s)
         }
     };
 
+    // Close batch `a` to further reservations; returns how many slots were taken (see reserve()).
+    auto seal = [&](Arena& a) -> uint32_t {
+        const uint64_t old = a.state.fetch_or(Arena::kSealed);
+        if (!(old & Arena::kSealed) && Arena::count_of(old) <= cfg_.max_batch) {
+            a.final_n.store((uint32_t)old, std::memory_order_relaxed);          // we closed it, and it had not overflowed
+            return (uint32_t)old;
+        }
+        uint32_t n;                                         // closed (or overflowed) by a producer, who says how many
+        while ((n = a.final_n.load(std::memory_order_acquire)) == Arena::kUnset) cpu_relax();
+        return n;
+    };
+
     uint32_t open = take_free_arena();
     open_arena(s, open);
     auto first_seen = Clock::time_point{};                  // when the flusher first saw the open batch non-empty
@@ -375,8 +417,8 @@ void BatchingService::flusher(Shard* s)
             reap();
             if (stopping_.load()) {
                 // shut the door; a producer that slipped in first still gets its batch
-                st = a.state.fetch_or(Arena::kSealed) | Arena::kSealed;
-                if (Arena::count_of(st) == 0) break;
+                if (seal(a) == 0) break;
+                st = a.state.load();
             } else {
                 // closed-loop callers come back within microseconds of their last answer: poll for
                 // them before paying for a futex sleep and its wake-up
@@ -425,8 +467,7 @@ void BatchingService::flusher(Shard* s)
         // the arena the NEXT batch opens in, before this one is sealed: producers never find the door shut
         // for longer than it takes to swap two words
         const uint32_t next = take_free_arena();
-        st = a.state.fetch_or(Arena::kSealed);
-        const uint32_t n = Arena::count_of(st);
+        const uint32_t n = seal(a);
         full = full || n >= cfg_.max_batch;
         open_arena(s, next);                                // producers carry on in the next arena
         have_first = false;
@@ -435,35 +476,47 @@ void BatchingService::flusher(Shard* s)
             open = next;
             continue;
         }
-        // the last producers may still be copying: wait for their commits
-        // and spread the records into the arrays the C ABI takes
+        // The last producers may still be copying: wait for their commits, spreading the records into
+        // the arrays the C ABI takes as they come: request i sits in slot i of the payload arena (an
+        // index a bigger payload runs over starts where that payload ends, with length 0), names packed.
         a.bytes = 0;
+        uint32_t real = 0, names_at = 0;
+        uint64_t prev_end = 0;
         for (uint32_t i = 0; i < n; ++i) {
             Arena::Rec& rec = a.rec[i];
             uint32_t len;
             while ((len = std::atomic_ref<uint32_t>(rec.len).load(std::memory_order_acquire)) == Arena::kUncommitted) cpu_relax();
-            a.pay_off[i] = (uint64_t)rec.off16 << 4;
+            const uint64_t off = std::max<uint64_t>((uint64_t)i * slot_bytes_, prev_end);
+            a.pay_off[i] = off;
             a.pay_len[i] = len;
-            a.name_off[i] = rec.noff;
+            a.name_off[i] = names_at;
+            prev_end = off + round16(len);
             a.bytes += len;
+            if (rec.name_len == Arena::kPlaceholder) continue;
+            ++real;
+            if (rec.name_len) {
+                std::memcpy(a.names.data() + names_at,
+                            rec.name_len <= Arena::kInlineName ? rec.name : a.long_names + (size_t)i * name_stride_, rec.name_len);
+                names_at += rec.name_len;
+            }
         }
-        a.pay_off[n] = Arena::pay16_of(st) << 4;
-        a.name_off[n] = Arena::names_of(st);
+        a.pay_off[n] = std::max<uint64_t>((uint64_t)n * slot_bytes_, prev_end);
+        a.name_off[n] = names_at;
         a.n = n;
         a.trigger = full ? "full" : eager ? "eager" : went_idle ? "idle" : "deadline";
         a.t_submit_ns = std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now().time_since_epoch()).count();
         {
             std::lock_guard<std::mutex> g(s->mu);
             ++s->st.batches;
-            s->st.requests += n;
+            s->st.requests += real;
             if (full) ++s->st.flush_full; else if (eager) ++s->st.flush_eager;
             else if (went_idle) ++s->st.flush_idle; else ++s->st.flush_deadline;
-            if (n > s->st.max_batch_seen) s->st.max_batch_seen = n;
+            if (real > s->st.max_batch_seen) s->st.max_batch_seen = real;
         }
         if (free_be.empty()) finish_oldest();               // a device slot for this batch
         const uint32_t be_slot = free_be.back();
         free_be.pop_back();
-        const int rc = s->be->submit(be_slot, a.payload, a.pay_off.data(), a.pay_len.data(), a.names,
+        const int rc = s->be->submit(be_slot, a.payload, a.pay_off.data(), a.pay_len.data(), a.names.data(),
                                      a.name_off.data(), n, a.out);
         if (rc != 0) {
             complete(s, a, rc);                             // fail exactly this batch's requests

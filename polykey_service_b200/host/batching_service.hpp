@@ -9,17 +9,17 @@
 //     srv     := server.NewServer(batched)
 //
 // grpc-go calls ExecuteTool from one goroutine (here: thread) per in-flight RPC, concurrently
-// and without a limit (main.go:74-77).  Every caller packs ITS OWN request: it reserves a
-// record index and a byte range of the open batch with one compare-and-swap on a packed
-// (count, payload bytes, name bytes) word, copies its payload and tool name straight into the
-// page-locked arenas of include/pk_route.h, and commits by storing its length.  The ONE flusher
-// thread per GPU never touches request bytes: it seals the open batch (size-, deadline- or
-// work-conserving trigger), opens the next arena so producers carry on, waits for the last
-// commits, crosses the C ABI once (pk_submit / pk_wait, `pipeline_depth` batches in flight) and
-// publishes the whole batch with one store; each caller then reads its own 24-byte decision
-// out of the record array and delegates to the inner service for the response body — so the
-// gRPC surface and mock.go stay unchanged.  (Round 1 packed on the flusher thread: one memcpy
-// per request on one core capped the seam at 3e6 requests/s.)
+// and without a limit (main.go:74-77).  Every caller packs ITS OWN request: it takes the next
+// record index of the open batch with one fetch_add, copies its payload into that index's slot of
+// the page-locked arena and its tool name into the index's record, and commits by storing its
+// length.  The ONE flusher thread per GPU never touches payload bytes: it seals the open batch
+// (size-, deadline- or work-conserving trigger), opens the next arena so producers carry on, waits
+// for the last commits while it spreads the records into the arrays of include/pk_route.h, crosses
+// the C ABI once (pk_submit / pk_wait, `pipeline_depth` batches in flight) and publishes the whole
+// batch with one store; each caller then reads its own 24-byte decision out of the record array
+// and delegates to the inner service for the response body — so the gRPC surface and mock.go stay
+// unchanged.  (Round 1 packed on the flusher thread: one memcpy per request on one core capped the
+// seam at 3e6 requests/s.)
 //
 // Requests shard across GPUs by request id (id % n_gpus); there is no exchange between GPUs.
 // A device error is returned to every request of the failed batch as a plain error (surfaced
@@ -93,7 +93,8 @@ struct BatchingConfig {
     uint32_t caller_spin_us = 150;         // a caller polls for its decision this long before it sleeps ...
     uint32_t caller_spin_max_waiters = 8;  // ... unless more callers than this are already waiting (they would
                                            // only steal cores from each other and from the flusher)
-    uint64_t max_payload_bytes = 32u << 20;   // payload arena per batch (<= 1 GiB)
+    uint64_t max_payload_bytes = 32u << 20;   // payload arena per batch; a request's slot is max_payload_bytes / max_batch
+                                              // (rounded down to 16) — a larger payload takes several slots
     // A request's tool name may be at most this long to be ROUTED.  A longer name cannot equal any
     // table entry (PK_MAX_TOOL_NAME is 64), so it is the switch's default branch whatever its
     // bytes (mock.go:60-64): ExecuteTool answers it through the inner service without a routing
@@ -115,25 +116,41 @@ class BatchingService;
 
 namespace detail {
 // One batch under construction / in flight: the flat arrays of include/pk_route.h in memory the
-// backend allocated, plus the words producers and the flusher meet on.  One per backend slot.
+// backend allocated, plus the words producers and the flusher meet on.
+//
+// Layout.  Request i of a batch owns a fixed SLOT of the payload arena, payload[i * slot_bytes ..)
+// (the C ABI allows gaps between requests; the device reads only the bytes a request has), and ONE
+// 64-byte record of its own — length, name length and the tool name itself when it has at most 56
+// bytes (longer ones go to a side array).  So a reservation is nothing but taking the next index:
+// ONE fetch_add on the batch's counter, which cannot fail and retry under contention the way a
+// compare-and-swap on packed byte counts did (that word was the front-end's ceiling, and a
+// metastable one: 4e6 or 9e6 requests/s from run to run), and everything a producer writes
+// afterwards lies in cache lines no other producer of the batch touches.  A payload larger than
+// one slot takes the k slots it covers; the k - 1 indices after it become empty placeholder requests.
 struct Arena {
+    struct alignas(64) Rec {
+        uint32_t len;                      // payload bytes; kUncommitted until the producer has copied them, and again
+                                           // once the caller has picked its record up (each caller marks its own)
+        uint32_t name_len;                 // kPlaceholder: an index covered by the big payload before it
+        uint8_t  name[56];                 // the tool name, if it fits
+    };
+    static constexpr uint32_t kInlineName = 56;
     // ---- written by producers ----
-    uint8_t* payload = nullptr;            // page-locked; request i at payload[16 * rec[i].off16 ..)
-    uint8_t* names = nullptr;
+    uint8_t* payload = nullptr;            // page-locked
+    uint8_t* long_names = nullptr;         // name i at long_names[i * name_stride ..) when longer than kInlineName
     pk_decision* out = nullptr;            // page-locked; the device's records
-    // What a producer says about its request, in ONE 16-byte record (four to a cache line) rather
-    // than in the three arrays the C ABI takes: a request then dirties one shared line, not three.
-    // len == kUncommitted until the producer has copied its bytes, and again once the caller has
-    // picked its record up (each caller marks its own word: no counter every caller of a batch
-    // would fight over).  The flusher spreads the records into pay_off / pay_len / name_off.
-    struct Rec { uint32_t off16, len, noff, reserved; };
     std::vector<Rec> rec;
     // ---- written by the flusher (the arrays of include/pk_route.h) ----
     std::vector<uint64_t> pay_off;
     std::vector<uint32_t> pay_len;
     std::vector<uint32_t> name_off;
-    // ---- reservation: [sealed:1][count:17][payload bytes / 16 : 26][name bytes : 20] ----
+    std::vector<uint8_t>  names;           // packed
+    // ---- reservation: [sealed:1][slots taken:63] ----
     alignas(64) std::atomic<uint64_t> state{kSealed};
+    // How many slots were taken successfully, published by whoever closed the batch: the first to
+    // set the sealed bit if the batch had not overflowed by then, else the one producer whose
+    // request was the first not to fit (requests after it add to the counter but never fit).
+    std::atomic<uint32_t> final_n{kUnset};
     // ---- completion ----
     alignas(64) std::atomic<uint32_t> gen_done{0};   // generation whose records are in `out`
     int rc = 0;                            // status of generation gen_done (written before gen_done)
@@ -146,12 +163,8 @@ struct Arena {
     int64_t t_submit_ns = 0;
 
     static constexpr uint64_t kSealed = 1ull << 63;
-    static constexpr uint32_t kUncommitted = 0xFFFFFFFFu;
-    static constexpr unsigned kCountShift = 46, kPayShift = 20;
-    static constexpr uint64_t kCountMask = (1ull << 17) - 1, kPayMask = (1ull << 26) - 1, kNameMask = (1ull << 20) - 1;
-    static uint32_t count_of(uint64_t st) { return (uint32_t)((st >> kCountShift) & kCountMask); }
-    static uint64_t pay16_of(uint64_t st) { return (st >> kPayShift) & kPayMask; }
-    static uint32_t names_of(uint64_t st) { return (uint32_t)(st & kNameMask); }
+    static constexpr uint32_t kUncommitted = 0xFFFFFFFFu, kPlaceholder = 0xFFFFFFFFu, kUnset = 0xFFFFFFFFu;
+    static uint64_t count_of(uint64_t st) { return st & ~kSealed; }
 };
 }  // namespace detail
 
@@ -173,7 +186,7 @@ public:
 private:
     friend class BatchingService;
     detail::Arena* arena_ = nullptr;                        // set while in flight
-    uint32_t idx_ = 0, gen_ = 0;
+    uint32_t idx_ = 0, gen_ = 0, slots_ = 1;
     pk_decision decision_{};
     int rc_ = 0;
 };
@@ -203,7 +216,7 @@ public:
 
 private:
     using Arena = detail::Arena;
-    struct Ticket { Arena* a = nullptr; uint32_t idx = 0, gen = 0; };
+    struct Ticket { Arena* a = nullptr; uint32_t idx = 0, gen = 0, slots = 1; };
     static constexpr uint32_t kNone = 0xFFFFFFFFu;
     struct Shard {
         RouteBackend* be = nullptr;
@@ -228,7 +241,8 @@ private:
 
     Service* inner_;
     BatchingConfig cfg_;
-    uint32_t name_cap_ = 0;                 // name arena bytes per batch
+    uint64_t slot_bytes_ = 0;               // payload slot of one request (a multiple of 16)
+    uint32_t name_stride_ = 0;              // bytes per request in Arena::long_names
     std::vector<std::unique_ptr<Shard>> shards_;
     std::atomic<uint64_t> next_id_{0};
     std::atomic<bool> stopping_{false}, healthy_{true};

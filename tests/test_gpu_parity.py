@@ -214,8 +214,8 @@ def test_async_slots_and_resident_form(pk, router, oracle):
 
 def test_small_batches_skip_the_copies(pk, oracle):
     """A small batch in page-locked buffers is routed by ONE launch on the caller's memory (no
-    H2D / D2H copies): same records; pageable buffers, long requests, big batches and a zero
-    threshold all take the copying path."""
+    H2D / D2H copies): same records; pageable buffers, big batches and a zero threshold take the
+    copying path."""
     t = oracle.default_table()
     r = pk.Router(device=0, max_requests=4096, max_payload_bytes=16 << 20, n_slots=2)
     try:
@@ -244,8 +244,11 @@ def test_small_batches_skip_the_copies(pk, oracle):
                 r.launch(1)                                   # nothing was staged on the device
         b = oracle.gen_batch(7100, 64, 0, 3000, mode=0)                                  # pageable payload
         assert_records_equal(r.route_batch(b), oracle.route_batch(t, b, threads=4)[1], "pageable")
-        b = oracle.gen_batch(7101, 8, 16385, 30000, mode=0, payload_out=buf)             # long requests
+        b = oracle.gen_batch(7101, 8, 16385, 30000, mode=0, payload_out=buf)             # long requests: in place too
         assert_records_equal(r.route_batch(b, out=out[:8]), oracle.route_batch(t, b, threads=4)[1], "long")
+        assert_records_equal(r.route_batch(b, out=out[:8]), oracle.route_batch(t, b, threads=4)[1], "long, again")
+        seen += 2
+        assert r.direct_count == seen
         b = oracle.gen_batch(7102, 1024, 2048, 2048, mode=0, payload_out=buf)            # 2 MiB > threshold
         assert_records_equal(r.route_batch(b, out=out[:1024]), oracle.route_batch(t, b, threads=4)[1], "big")
         assert r.direct_count == seen

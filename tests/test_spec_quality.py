@@ -32,6 +32,27 @@ def test_route_hash_avalanche(oracle):
         assert min(flips) >= 12 and 24 <= np.mean(flips) <= 40, (length, flips)
 
 
+def test_same_flip_in_different_blocks_gives_different_hashes(oracle):
+    """Stripe digests are ADDED, so a stripe's digest must not be an affine function of its block:
+    otherwise the same bit flipped at the same offset of two different blocks moves the sum by the
+    same amount and the two payloads collide.  (A digest without the per-stripe finaliser does
+    exactly that — tried in round 2 to save its 64-bit multiplications on tiny payloads, and
+    caught by this test: every single-bit variant of a payload must hash differently.)"""
+    rng = np.random.default_rng(5)
+    for length in (16, 48, 256, 2048):
+        base = bytearray(rng.bytes(length))
+        variants = [bytes(base)]
+        for pos in range(min(length, 64)):
+            for bit in range(8):
+                v = bytearray(base)
+                v[pos] ^= 1 << bit
+                variants.append(bytes(v))
+        h = hashes(oracle, variants)["route_hash"]
+        assert len(set(h.tolist())) == len(variants), length
+        flips = [popcount64(h[0] ^ x) for x in h[1:]]
+        assert min(flips) >= 12, (length, min(flips))
+
+
 def test_route_hash_depends_on_name_length_and_order(oracle):
     rng = np.random.default_rng(2)
     p = rng.bytes(500)
