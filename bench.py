@@ -680,7 +680,7 @@ def frontend_leg(ctx: Ctx, seconds: float = 1.5):
             return {"unavailable": f"host/latency_bench could not be built: {e!r}"}
     G = ctx.world
     env = dict(os.environ, PK_BACKENDS=str(G))
-    gens = max(2, min(ctx.cores - 2 * G - 2, 12))          # leave cores for the flushers and this process
+    gens = max(2, min(ctx.cores - G - 3, 24))              # leave a core per flusher, and some for this process
     out = {"gpus": G, "generators": gens, "payload_bytes": 2048, "max_batch": 4096, "max_wait_us": 200,
            "api": "BatchingService::EnqueueAsync -> decision (C++ mirror of the Go batcher), open loop, Poisson arrivals",
            "rates": []}

@@ -12,55 +12,40 @@ import subprocess
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpkroute.so")
-SOURCES = ["pk_kernels.cu", "pk_abi.cu", "pk_noalloc.cu", "pk_gcm.cu"]
-HEADERS = ["pk_kernels.cuh", "pk_spec.cuh", "pk_gcm.cuh", os.path.join("..", "..", "include", "pk_route.h"),
-           os.path.join("..", "..", "include", "pk_gcm.h")]
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-shared"]
+# The nvcc command line lives in ONE place, deploy/Makefile.pkroute — the target a maintainer adds
+# to the reference's Makefile (north_star: "the Makefile/Dockerfile (nvcc sm_100a build)").  This
+# module only drives it, so what __graft_entry__.build() compiles is what a deployment compiles.
+MAKEFILE = os.path.join(ROOT, "deploy", "Makefile.pkroute")
 
 
-def nvcc() -> str:
-    for cand in (shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
-        if cand and os.path.exists(cand):
-            return cand
-    raise RuntimeError("nvcc not found: libpkroute.so cannot be built (there is no CPU fallback)")
-
-
-def stale() -> bool:
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS] + [os.path.abspath(__file__)]
-    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+def _make(*args: str) -> None:
+    if not shutil.which("make"):
+        raise RuntimeError("make not found: libpkroute.so cannot be built (there is no CPU fallback)")
+    subprocess.check_call(["make", "--no-print-directory", "-f", MAKEFILE, *args], cwd=ROOT)
 
 
 def build(force: bool = False, verbose: bool = False, defines=(), out: str | None = None) -> str:
-    """defines/out: build a tuning variant (e.g. defines=["PK_PIPE=0"]) to another path."""
-    if out is None and not force and not stale():
-        return LIB
-    out = out or LIB
-    cmd = [nvcc(), *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-o", out] + [os.path.join(CSRC, f) for f in SOURCES]
+    """defines/out: build a tuning variant (e.g. defines=["PK_MIN_CTAS=4"]) to another path."""
+    target = os.path.abspath(out) if out else LIB
+    args = ["libpkroute-force" if (force or out) else "libpkroute", f"OUT={target}"]
+    if defines:
+        args.append("DEFINES=" + " ".join(defines))
     if verbose:
-        cmd.insert(1, "-Xptxas=-v")
-    subprocess.check_call(cmd)
-    return out
+        args.append("PK_VERBOSE=1")
+    _make(*args)
+    return target
 
 
 def build_latency_bench(force: bool = False) -> str:
     """g++ build of host/latency_bench.cpp (the load generator that drives the C++ batching
     front-end; bench.py's `latency` / `e2e.with_pack` legs run it) into build/latency_bench."""
-    root = os.path.dirname(HERE)
-    host = os.path.join(HERE, "host")
-    exe = os.path.join(root, "build", "latency_bench")
-    srcs = [os.path.join(host, f) for f in ("latency_bench.cpp", "batching_service.cpp", "service.cpp")]
-    deps = srcs + [os.path.join(host, f) for f in ("batching_service.hpp", "service.hpp")] + [LIB]
-    if not force and os.path.exists(exe) and all(os.path.getmtime(d) <= os.path.getmtime(exe) for d in deps if os.path.exists(d)):
-        return exe
-    os.makedirs(os.path.dirname(exe), exist_ok=True)
-    subprocess.check_call(["g++", "-std=c++20", "-O2", "-pthread", "-o", exe, *srcs, "-L" + HERE, "-lpkroute",
-                           "-Wl,-rpath," + HERE])
+    exe = os.path.join(ROOT, "build", "latency_bench")
+    if force and os.path.exists(exe):
+        os.remove(exe)
+    _make("latency-bench")
     return exe
 
 
