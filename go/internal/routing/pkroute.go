@@ -16,6 +16,7 @@ package routing
 import "C"
 
 import (
+	"errors"
 	"fmt"
 	"unsafe"
 )
@@ -52,7 +53,7 @@ func NewRouter(device int, maxRequests uint32, maxPayloadBytes uint64, slots uin
 		max_requests:      C.uint32_t(maxRequests),
 		n_slots:           C.uint32_t(slots),
 		max_payload_bytes: C.uint64_t(maxPayloadBytes),
-		max_name_bytes:    C.uint64_t(256 * uint64(maxRequests)),
+		max_name_bytes:    C.uint64_t(256 * uint64(maxRequests)), // >= the front-end's MaxNameBytes per request
 	}
 	var h *C.pk_handle
 	if rc := C.pk_init(C.int(device), &tbl, &cfg, &h); rc != 0 {
@@ -82,9 +83,37 @@ func (r *Router) HostAlloc(n int) []byte {
 	return unsafe.Slice((*byte)(p), n)
 }
 
+// HostAllocDecisions: a pinned record array (the device writes the batch's decisions into it).
+func (r *Router) HostAllocDecisions(n int) []Decision {
+	p := C.pk_host_alloc(r.h, C.size_t(n)*C.size_t(unsafe.Sizeof(Decision{})))
+	if p == nil {
+		return nil
+	}
+	return unsafe.Slice((*Decision)(p), n)
+}
+
+// RouteError carries the pk_status of a failed call.
+type RouteError struct {
+	Status int // PK_ERR_*
+	Cuda   int // cudaError_t when Status is PK_ERR_CUDA
+	Where  string
+}
+
+func (e *RouteError) Error() string {
+	return fmt.Sprintf("routing failed: %s: %s (cuda %d)", e.Where, C.GoString(C.pk_strerror(C.int(e.Status))), e.Cuda)
+}
+
+// IsDeviceFailure: a failure of the device (health goes NOT_SERVING), as opposed to a batch the
+// device refused (argument / capacity: only its requests fail).
+func IsDeviceFailure(err error) bool {
+	var re *RouteError
+	return errors.As(err, &re) && (re.Status == int(C.PK_ERR_CUDA) || re.Status == int(C.PK_ERR_NO_DEVICE))
+}
+
 // Submit enqueues H2D copies, the fused kernel and the D2H copy of one batch on `slot` and
-// returns at once; Wait blocks until `out` holds the records.  Every slice must come from
-// HostAlloc and stay untouched until Wait returns.
+// returns at once; Wait blocks until `out` holds the records.  payload and out must come from
+// HostAlloc / HostAllocDecisions and stay untouched until Wait returns; the offset, length and name
+// arrays are consumed before Submit returns and may be ordinary Go slices (no Go pointers in them).
 func (r *Router) Submit(slot uint32, payload []byte, payOff []uint64, payLen []uint32,
 	names []byte, nameOff []uint32, out []Decision) error {
 	n := len(payLen)
@@ -100,14 +129,14 @@ func (r *Router) Submit(slot uint32, payload []byte, payOff []uint64, payLen []u
 		C.uint32_t(n),
 		(*C.pk_decision)(unsafe.Pointer(unsafe.SliceData(out))))
 	if rc != 0 {
-		return fmt.Errorf("pk_submit: %s (cuda %d)", C.GoString(C.pk_strerror(rc)), int(C.pk_last_cuda_error(r.h)))
+		return &RouteError{int(rc), int(C.pk_last_cuda_error(r.h)), "pk_submit"}
 	}
 	return nil
 }
 
 func (r *Router) Wait(slot uint32) error {
 	if rc := C.pk_wait(r.h, C.uint32_t(slot)); rc != 0 {
-		return fmt.Errorf("pk_wait: %s (cuda %d)", C.GoString(C.pk_strerror(rc)), int(C.pk_last_cuda_error(r.h)))
+		return &RouteError{int(rc), int(C.pk_last_cuda_error(r.h)), "pk_wait"}
 	}
 	return nil
 }
