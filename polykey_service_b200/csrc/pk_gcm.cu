@@ -121,6 +121,95 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
     }
 }
 
+// kGroupLanes lanes per SHORT message (the messages gcm_long_kernel does not take) — the default
+// for them since round 2; gcm_kernel above (one thread per message) stays for comparison
+// (PK_GCM_GROUP=0).  65,536 secrets are 65,536 threads there: 14 warps per SM, each on one serial
+// chain of 17 dependent AES blocks and table walks; here they are four times as many threads on
+// chains a quarter as long.  Dynamic shared memory, 81 KB -> 2 CTAs of 512 threads per SM (which is
+// also what its 53 registers allow):
+//   [0, 64 KB)   Te0 | Te2 replicated per bank, pkgcm::TeDual's layout (half the ALU instructions
+//                per AES round of the single replicated table — the pipe this kernel is bound by)
+//   then         pkgcm::GroupTables (round keys, tables of H^1..H^4: 16.6 KB)
+//   then         the round keys rotated left by 8 (TeDual::rkr)
+constexpr int kGroupThreads = 512;
+constexpr uint32_t kGroupSmemBytes = kTabBytes + (uint32_t)sizeof(pkgcm::GroupTables) + 256u;
+
+__global__ void __launch_bounds__(kGroupThreads) gcm_group_kernel(const KeyContext* __restrict__ kc_g,
+                                                                  const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
+                                                                  const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
+                                                                  uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
+                                                                  uint32_t* __restrict__ status, uint32_t first, uint32_t n, int mode,
+                                                                  uint32_t long_bytes)
+{
+    constexpr uint32_t G = pkgcm::kGroupLanes;
+    extern __shared__ __align__(16) uint8_t smem[];
+    pkgcm::GroupTables* gt = reinterpret_cast<pkgcm::GroupTables*>(smem + kTabBytes);
+    uint32_t* rkr = reinterpret_cast<uint32_t*>(smem + kTabBytes + sizeof(pkgcm::GroupTables));
+    for (uint32_t i = threadIdx.x; i < sizeof(pkgcm::GroupTables) / 16; i += blockDim.x)
+        reinterpret_cast<uint4*>(gt)[i] = __ldg(reinterpret_cast<const uint4*>(&kc_g->gg) + i);
+    for (uint32_t i = threadIdx.x; i < 60; i += blockDim.x) {
+        const uint32_t k = __ldg(&kc_g->gg.rk[i]);
+        rkr[i] = (k << 8) | (k >> 24);
+    }
+    for (uint32_t x = threadIdx.x; x < 512; x += blockDim.x) {       // x = 2·entry + table
+        const uint32_t t = __ldg(&kc_g->te[(x & 1u) * 2u][x >> 1]);
+        const uint4 t4 = make_uint4(t, t, t, t);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + x * 128u)[q] = t4;
+    }
+    __syncthreads();
+    const pkgcm::TeDual te{smem, rkr, (threadIdx.x & 31u) * 4u};
+
+    // every thread stays to the end: the group's lanes meet in shuffles
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t i = first + t / G, lig = t % G, lane = threadIdx.x & 31u, lead = lane & ~(G - 1u);
+    uint32_t len = i < n ? in_len[i] : 0u;
+    bool active = i < n && len < long_bytes;                 // (the long ones are gcm_long_kernel's)
+    const uint8_t* src = active ? in + in_off[i] : nullptr;
+    uint8_t* dst = active ? out + out_off[i] : nullptr;
+    if (active && mode != 0 && len < pkgcm::kOverhead) {     // shorter than nonce + tag: cipher.go:69-71 / Open fails
+        if (lig == 0) status[i] = len < pkgcm::kNonceBytes ? 2u : 1u;
+        active = false;
+    }
+    const uint32_t clen = mode == 0 ? len : len - pkgcm::kOverhead;   // (meaningful when active)
+    const uint8_t* nonce = mode == 0 ? nonces + (size_t)i * pkgcm::kNonceBytes : src;
+    uint64_t yh = 0, yl = 0;
+    uint32_t j0[4] = {0u, 0u, 0u, 0u};
+    if (active) {
+        if (mode == 0 && lig == 0)
+            for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];        // cipher.go:51-52
+        pkgcm::gcm_group_pass<(int)G>(gt, te, nonce, mode == 0 ? src : src + pkgcm::kNonceBytes,
+                                      mode == 0 ? dst + pkgcm::kNonceBytes : dst, clen, mode != 0, lig, yh, yl, j0);
+    }
+#pragma unroll
+    for (uint32_t d = G / 2u; d > 0; d >>= 1) {
+        yh ^= __shfl_xor_sync(0xFFFFFFFFu, yh, d);
+        yl ^= __shfl_xor_sync(0xFFFFFFFFu, yl, d);
+    }
+    // the lane that owned the lengths block holds E_K(J0): it makes the tag
+    const uint32_t owner = active ? ((clen + 15u) >> 4) % G : 0u;
+    uint32_t ok = 1u;
+    if (active && lig == owner) {
+        const uint32_t tw[4] = {(uint32_t)(yh >> 32) ^ j0[0], (uint32_t)yh ^ j0[1], (uint32_t)(yl >> 32) ^ j0[2], (uint32_t)yl ^ j0[3]};
+        if (mode == 0) {
+            uint8_t* tp = dst + pkgcm::kNonceBytes + len;
+            for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) tp[b] = (uint8_t)(tw[b >> 2] >> (24u - 8u * (b & 3u)));
+        } else {
+            const uint8_t* tp = src + pkgcm::kNonceBytes + clen;
+            uint32_t diff = 0;
+            for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) diff |= (uint32_t)tp[b] ^ ((tw[b >> 2] >> (24u - 8u * (b & 3u))) & 0xFFu);
+            ok = diff == 0u;
+            status[i] = ok ? 0u : 1u;
+        }
+    }
+    if (mode != 0) {
+        ok = __shfl_sync(0xFFFFFFFFu, ok, lead + owner);
+        if (active && !ok)                                   // authentication failed: release no plaintext
+            for (uint32_t b = lig * 16u; b < clen; b += G * 16u)
+                for (uint32_t k = b; k < b + 16u && k < clen; ++k) dst[k] = 0;
+    }
+}
+
 // One WARP per long message (those gcm_kernel skipped; long_idx lists them).  Lane l takes the
 // 16-byte blocks l, l+32, ... — a warp reads and writes 512 consecutive bytes per step — and the
 // lanes' GHASH terms (pkgcm::gcm_lane_pass) XOR together through shuffles.
@@ -351,10 +440,19 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
         if (lo == 0) PKG_CUDA(h, cudaEventRecord(h->ev0, s_run));
         const uint32_t cnt = hi - lo, cnt_long = l_hi - l_lo;
         if (cnt_long < cnt) {
-            // one thread per message: spread a small batch over more SMs with narrower blocks
-            const uint32_t threads = cnt >= 148u * 2u * kThreads ? kThreads : cnt >= 148u * 64u ? 64u : 32u;
-            gcm_kernel<<<(cnt + threads - 1) / threads, threads, 0, s_run>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
-                                                                             h->d_out, h->d_out_off, h->d_status, lo, hi, mode, long_bytes);
+            static const char* const g_env = std::getenv("PK_GCM_GROUP");     // "0": one thread per message (comparison)
+            if (!(g_env && g_env[0] == '0')) {
+                // kGroupLanes lanes per message; narrower blocks spread a small batch over more SMs
+                const uint64_t lanes = (uint64_t)cnt * pkgcm::kGroupLanes;
+                const uint32_t threads = lanes >= 148u * (uint64_t)kGroupThreads ? (uint32_t)kGroupThreads : lanes >= 148u * 128u ? 128u : 64u;
+                gcm_group_kernel<<<(uint32_t)((lanes + threads - 1) / threads), threads, kGroupSmemBytes, s_run>>>(
+                    h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce, h->d_out, h->d_out_off, h->d_status, lo, hi, mode, long_bytes);
+            } else {
+                // one thread per message: spread a small batch over more SMs with narrower blocks
+                const uint32_t threads = cnt >= 148u * 2u * kThreads ? kThreads : cnt >= 148u * 64u ? 64u : 32u;
+                gcm_kernel<<<(cnt + threads - 1) / threads, threads, 0, s_run>>>(h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce,
+                                                                                 h->d_out, h->d_out_off, h->d_status, lo, hi, mode, long_bytes);
+            }
             PKG_CUDA(h, cudaGetLastError());
             ++h->launches;
         }
@@ -426,6 +524,7 @@ int pk_gcm_init(int device, const uint8_t* key, uint32_t key_len, uint32_t max_m
     const size_t n = max_messages;
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gcm_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gcm_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGroupSmemBytes);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->s_run, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking);

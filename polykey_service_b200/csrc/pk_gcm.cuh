@@ -46,10 +46,21 @@ struct GcmTables {
     HEntry ht32[256];           // the same table for H^32 (the warp-per-message Horner step)
     HEntry pw[32];              // pw[e-1] = H^e, e = 1..32
 };
+// What the lane-group kernel (kGroupLanes lanes per short message) keeps in shared memory: the round
+// keys and the 8-bit Shoup tables of H^1 .. H^G — H^G is the lanes' Horner step, H^e (e = 1..G) a
+// lane's closing power, so every multiplication is a 16-step table walk (no bit-serial product).
+constexpr int kGroupLanes = 4;
+struct GroupTables {
+    uint32_t rk[60];
+    uint32_t pad[4];
+    HEntry hp[kGroupLanes][256];    // hp[e-1] = table of H^e
+};
 struct KeyContext {
     uint32_t te[4][256];        // T-tables: te[0][x] = (2·S[x], S[x], S[x], 3·S[x]) big-endian; te[k] = te[0] rotated right by 8k
     GcmTables g;
+    GroupTables gg;
 };
+static_assert(sizeof(GroupTables) % 16 == 0, "GroupTables is staged as uint4");
 static_assert(sizeof(GcmTables) % 16 == 0, "GcmTables is staged as uint4");
 static_assert(sizeof(KeyContext) % 16 == 0, "KeyContext is staged as uint4");
 
@@ -245,12 +256,12 @@ PKG_HD void ghash_mul_bitwise(uint64_t ph, uint64_t pl, uint64_t& xh, uint64_t& 
 // CTR-crypt one 16-byte (or final partial) block at offset `at` and return the CIPHERTEXT block
 // as big-endian words, zero padded.
 template <typename Te>
-PKG_HD void ctr_block(const GcmTables* __restrict__ kc, const Te& te, uint32_t n0, uint32_t n1, uint32_t n2,
+PKG_HD void ctr_block(const uint32_t* __restrict__ rk, const Te& te, uint32_t n0, uint32_t n1, uint32_t n2,
                       const uint8_t* __restrict__ in, uint8_t* __restrict__ out, uint32_t len, uint32_t at,
                       bool decrypt, uint32_t c[4])
 {
     uint32_t ks[4] = {n0, n1, n2, 2u + (at >> 4)};
-    aes256_encrypt_block(te, kc->rk, ks);
+    aes256_encrypt_block(te, rk, ks);
     const uint32_t nb = len - at < 16 ? len - at : 16;
     c[0] = c[1] = c[2] = c[3] = 0;
     if (nb == 16) {
@@ -289,7 +300,7 @@ PKG_HD void gcm_lane_pass(const GcmTables* __restrict__ kc, const Te& te, const 
         if (last != 0xFFFFFFFFu) ghash_mul_table(kc->ht32, yh, yl);
         if (b < nblk) {
             uint32_t c[4];
-            ctr_block(kc, te, n0, n1, n2, in, out, len, b << 4, decrypt, c);
+            ctr_block(kc->rk, te, n0, n1, n2, in, out, len, b << 4, decrypt, c);
             yh ^= ((uint64_t)c[0] << 32) | c[1];
             yl ^= ((uint64_t)c[2] << 32) | c[3];
         } else {
@@ -301,6 +312,40 @@ PKG_HD void gcm_lane_pass(const GcmTables* __restrict__ kc, const Te& te, const 
         const uint32_t e = m - last;               // 1..32
         ghash_mul_bitwise(kc->pw[e - 1].h, kc->pw[e - 1].l, yh, yl);
     }
+}
+
+// Lane-group form for SHORT messages (a secret of 32-256 bytes is 2-16 blocks: one thread walking
+// them serially leaves the SM's warp slots a fifth full and every thread on one dependent chain).
+// G lanes share a message: lane l takes blocks l, l+G, ... of the m = (ciphertext blocks) + 1 GHASH
+// blocks — Horner with H^G over its own blocks, closed with H^(m - its last block), every step a
+// table walk — and the lanes' terms XOR to X.  The lane that owns the lengths block (it has no AES
+// block to encrypt for it) encrypts J0 = nonce || 1 instead and returns E_K(J0) in j0[]: the work
+// is even and the tag needs no serial tail.  (yh, yl) = this lane's term.
+template <int G, typename Te>
+PKG_HD void gcm_group_pass(const GroupTables* __restrict__ gt, const Te& te, const uint8_t* __restrict__ nonce,
+                           const uint8_t* __restrict__ in, uint8_t* __restrict__ out, uint32_t len,
+                           bool decrypt, uint32_t lig, uint64_t& yh, uint64_t& yl, uint32_t j0[4])
+{
+    const uint32_t n0 = load_be32(nonce), n1 = load_be32(nonce + 4), n2 = load_be32(nonce + 8);
+    const uint32_t nblk = (len + 15u) >> 4;
+    const uint32_t m = nblk + 1u;
+    yh = 0; yl = 0;
+    uint32_t last = 0xFFFFFFFFu;
+    for (uint32_t b = lig; b < m; b += (uint32_t)G) {
+        if (last != 0xFFFFFFFFu) ghash_mul_table(gt->hp[G - 1], yh, yl);
+        if (b < nblk) {
+            uint32_t c[4];
+            ctr_block(gt->rk, te, n0, n1, n2, in, out, len, b << 4, decrypt, c);
+            yh ^= ((uint64_t)c[0] << 32) | c[1];
+            yl ^= ((uint64_t)c[2] << 32) | c[3];
+        } else {
+            yl ^= (uint64_t)len * 8u;              // the lengths block: len(A) = 0 || len(C) in bits
+            j0[0] = n0; j0[1] = n1; j0[2] = n2; j0[3] = 1u;
+            aes256_encrypt_block(te, gt->rk, j0);
+        }
+        last = b;
+    }
+    if (last != 0xFFFFFFFFu) ghash_mul_table(gt->hp[m - last - 1u], yh, yl);     // H^(m - last), 1..G
 }
 
 // tag = X ^ E_K(nonce || 1), as 16 bytes
@@ -449,6 +494,10 @@ static inline void make_key_context(const uint8_t key[32], KeyContext& kc)
         ghash_mul_bitwise(Hh, Hl, ph, pl);
     }
     make_shoup_table(kc.g.pw[31].h, kc.g.pw[31].l, kc.g.ht32);
+    // the lane-group kernel's copy: round keys, tables of H^1 .. H^G
+    for (int i = 0; i < 60; ++i) kc.gg.rk[i] = kc.g.rk[i];
+    for (int k = 0; k < 4; ++k) kc.gg.pad[k] = 0;
+    for (int e = 1; e <= kGroupLanes; ++e) make_shoup_table(kc.g.pw[e - 1].h, kc.g.pw[e - 1].l, kc.gg.hp[e - 1]);
 }
 
 }  // namespace pkgcm

@@ -89,3 +89,25 @@ extern "C" int gcmh_open_lanes(const uint8_t* key, const uint8_t* sealed, uint32
     gcm_tag(&kc.g, TeTables{kc.te}, sealed, xh, xl, tag);
     return std::memcmp(tag, sealed + len - 16, 16) == 0 ? 0 : 1;
 }
+
+// The lane-group form for short messages (kGroupLanes lanes, Horner with H^G, table multiplications,
+// E_K(J0) computed by the lane that owns the lengths block) run as a loop over the lanes on the host.
+extern "C" int gcmh_group(const uint8_t* key, const uint8_t* nonce, const uint8_t* in, uint32_t len, int decrypt,
+                          uint8_t* out, uint8_t* tag)
+{
+    KeyContext kc;
+    make_key_context(key, kc);
+    uint64_t xh = 0, xl = 0;
+    uint32_t j0[4] = {0, 0, 0, 0};
+    int owners = 0;
+    for (uint32_t lig = 0; lig < (uint32_t)kGroupLanes; ++lig) {
+        uint64_t yh, yl;
+        uint32_t mine[4] = {0, 0, 0, 0};
+        gcm_group_pass<kGroupLanes>(&kc.gg, TeTables{kc.te}, nonce, in, out, len, decrypt != 0, lig, yh, yl, mine);
+        xh ^= yh; xl ^= yl;
+        if (lig == ((len + 15u) >> 4) % (uint32_t)kGroupLanes) { std::memcpy(j0, mine, 16); ++owners; }
+    }
+    const uint32_t t[4] = {(uint32_t)(xh >> 32) ^ j0[0], (uint32_t)xh ^ j0[1], (uint32_t)(xl >> 32) ^ j0[2], (uint32_t)xl ^ j0[3]};
+    for (int b = 0; b < 16; ++b) tag[b] = (uint8_t)(t[b >> 2] >> (24 - 8 * (b & 3)));
+    return owners;
+}
