@@ -705,6 +705,69 @@ def frontend_leg(ctx: Ctx, seconds: float = 1.5):
     return out
 
 
+def gcm_leg(ctx: Ctx):
+    """SURVEY §8(f) rank 1 — batched AES-256-GCM (internal/adapters/security/cipher.go:110-141): two
+    batches sealed on the GPU through its C ABI (include/pk_gcm.h) from page-locked arenas, checked
+    byte for byte against OpenSSL, timed beside OpenSSL on the host cores with the key set once per
+    thread (the reference's own loop rebuilds the cipher per message: cpu_reference_shape_ms)."""
+    import ctypes as C
+    from polykey_service_b200 import gcm
+    ref = C.CDLL(os.path.join(ROOT, "oracle", "libpkaesref.so"))
+    ref.pk_aes_ref_seal_batch.argtypes = [C.c_char_p] + [C.c_void_p] * 4 + [C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int]
+    rng = np.random.default_rng(7)
+    key = rng.bytes(32)
+    rows = {}
+
+    def med(f, reps):
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            f()
+            ts.append(time.perf_counter() - t0)
+        return sorted(ts)[len(ts) // 2] * 1e3
+
+    for name, n, length in (("65536x256B", 65536, 256), ("32768x4KiB", 32768, 4096)):
+        plen = np.full(n, length, dtype=np.uint32)
+        poff, ptotal = gcm.slots(plen)
+        soff, stotal = gcm.slots(plen.astype(np.uint64) + gcm.OVERHEAD)
+        with gcm.Gcm(key, device=ctx.local, max_messages=n, max_bytes=stotal + 64) as g:
+            arrs = {"plain": rng.integers(0, 256, ptotal, dtype=np.uint8), "poff": poff, "plen": plen,
+                    "nonces": rng.integers(0, 256, 12 * n, dtype=np.uint8), "sealed": np.zeros(stotal, dtype=np.uint8), "soff": soff}
+            pin = {}
+            for k, a in arrs.items():                          # page-locked, as the host mirror packs them
+                pin[k] = g.pinned(a.nbytes, a.dtype)[:a.size]
+                pin[k][:] = a
+            call = lambda: g.seal_arena(pin["plain"], pin["poff"], pin["plen"], pin["nonces"], pin["sealed"], pin["soff"])  # noqa: E731
+            call()
+            want = np.zeros(stotal, dtype=np.uint8)
+            cpu = lambda threads, per_item: ref.pk_aes_ref_seal_batch(  # noqa: E731
+                key, arrs["plain"].ctypes.data, poff.ctypes.data, plen.ctypes.data, arrs["nonces"].ctypes.data, n,
+                want.ctypes.data, soff.ctypes.data, threads, per_item)
+            cpu(ctx.cores, 0)
+            sealed = np.asarray(pin["sealed"])
+            ok = all((sealed[int(o):int(o) + length + gcm.OVERHEAD] == want[int(o):int(o) + length + gcm.OVERHEAD]).all()
+                     for o in soff[:: max(1, n // 512)]) and (sealed[int(soff[-1]):] == want[int(soff[-1]):]).all()
+            assert ok, f"AES-GCM: GPU and OpenSSL differ ({name})"
+            for _ in range(5):
+                call()
+            t0 = time.perf_counter()
+            call_ms = med(call, 15)
+            ctx.windows.append((t0, time.perf_counter()))
+            g.set_chunks(1)                                    # kernels alone: no copy overlapping them
+            ks = []
+            for _ in range(7):
+                call()
+                ks.append(g.last_kernel_ms)
+            rows[name] = {"messages": n, "bytes": length, "kernel_ms": sorted(ks)[len(ks) // 2], "call_ms": call_ms,
+                          "openssl_key_once_ms": med(lambda: cpu(ctx.cores, 0), 5),
+                          "cpu_reference_shape_ms": med(lambda: cpu(ctx.cores, 1), 3), "cores": ctx.cores,
+                          "kernel_gbs": n * length / (sorted(ks)[len(ks) // 2] / 1e3) / 1e9,
+                          "parity_gate": "sealed bytes equal OpenSSL's (every 128th message and the last, all bytes)"}
+    rows["what"] = ("pk_gcm_seal_batch, page-locked arenas; kernel_ms = the kernels alone (CUDA events); call_ms = one call, "
+                    "copies included; OpenSSL EVP on all host cores, key set once per thread / fresh cipher per message")
+    return rows
+
+
 def run_gpu(args):
     ctx = Ctx(args)
     O, pk = ctx.O, ctx.pk
@@ -751,6 +814,12 @@ def run_gpu(args):
                                                               "d2h_bytes_per_step", "pipeline_depth", "copies")},
                                 "parity_gate": "slot 0 and the last e2e batch bit-exact vs the oracle"}
         c4 = c4_record(ctx, c4_leg(ctx, args.c4_batch, 245 * 4, 5))
+    gcm_rec = None
+    if not args.lean and ctx.world == 1 and workload == "c1":
+        try:
+            gcm_rec = gcm_leg(ctx)
+        except (OSError, ImportError) as e:                  # no libcrypto / cryptography on this box: say so
+            gcm_rec = {"unavailable": repr(e)[:200]}
     latency = None
     if not (args.lean or args.no_frontend):
         # rank 0 drives every GPU from one server-shaped process; the other ranks wait on the
@@ -833,6 +902,8 @@ def run_gpu(args):
         line["workloads"] = workloads
     if c4:
         line["c4"] = c4
+    if gcm_rec:
+        line["gcm"] = gcm_rec
     if latency:
         line["latency"] = latency
         if "sustained_per_s" in latency:

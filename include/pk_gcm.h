@@ -65,7 +65,14 @@ PK_GCM_API int  pk_gcm_seal_batch(pk_gcm* h, const uint8_t* plain, const uint64_
 
 /* BatchDecrypt (cipher.go:126-141).  status[i]: 0 opened, 1 authentication failed ("failed to
  * decrypt"), 2 shorter than a nonce ("ciphertext too short", cipher.go:69-71).  Returns
- * PK_GCM_ERR_AUTH if any status is non-zero; plaintext of a failed message is zeroed.           */
+ * PK_GCM_ERR_AUTH if any status is non-zero; plaintext of a failed message is zeroed.
+ * The kernels decrypt while they authenticate (one pass over the ciphertext) and wipe the output
+ * of a message whose tag does not match before the call returns — so `plain` must not be read by
+ * anyone until the call has returned.  That matters for the in-place path (every array page-locked,
+ * small batch: the kernel writes straight into the caller's `plain`), where for the duration of the
+ * call unauthenticated plaintext sits in host memory another thread could see; with the copying
+ * path it only ever exists in the library's device buffer.  A caller that cannot guarantee that
+ * turns the in-place path off (pk_gcm_set_direct_bytes(h, 0)).                                  */
 PK_GCM_API int  pk_gcm_open_batch(pk_gcm* h, const uint8_t* sealed, const uint64_t* sealed_off,
                                   const uint32_t* sealed_len, uint32_t n, uint8_t* plain,
                                   const uint64_t* plain_off, uint32_t* status);

@@ -91,3 +91,22 @@ def test_product_never_touches_the_oracle():
                 assert "pk_oracle" not in src and "libpkoracle" not in src and "pk_ref_" not in src, f
     out = subprocess.check_output(["ldd", os.path.join(pkg, "libpkroute.so")], text=True)
     assert "oracle" not in out
+
+
+def test_the_deploy_makefile_is_the_build(pk):
+    """The nvcc command of deploy/Makefile.pkroute — the target a maintainer adds to the reference's
+    Makefile (north_star: "the Makefile/Dockerfile (nvcc sm_100a build)") — is what builds
+    libpkroute.so here: sm_100a only, every CUDA source, and the library is up to date with it."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    dry = subprocess.run(["make", "-n", "-B", "-f", os.path.join(root, "deploy", "Makefile.pkroute"), "libpkroute"],
+                         capture_output=True, text=True, cwd=root)
+    assert dry.returncode == 0, dry.stderr
+    cmd = dry.stdout
+    assert "arch=compute_100a,code=sm_100a" in cmd and cmd.count("-gencode") == 1 and "-lineinfo" in cmd
+    for src in ("pk_kernels.cu", "pk_abi.cu", "pk_noalloc.cu", "pk_gcm.cu"):
+        assert src in cmd
+    up_to_date = subprocess.run(["make", "-q", "-f", os.path.join(root, "deploy", "Makefile.pkroute"), "libpkroute"], cwd=root)
+    assert up_to_date.returncode == 0                                 # build.py went through this very target
+    from polykey_service_b200 import build
+    assert build.MAKEFILE.endswith("deploy/Makefile.pkroute")

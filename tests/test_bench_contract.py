@@ -74,6 +74,9 @@ def test_product_arm_line(oracle, pk):
     c4 = d["c4"]                                                      # BASELINE configs[4]
     assert c4["scaling"] == "strong" and c4["batches_per_shard"] == 245 and c4["e2e"]["value"] > 0
     assert abs(c4["value"] - 1e6 / (c4["pass_ms"] / 1e3)) / c4["value"] < 1e-9
+    g = d["gcm"]                                                      # SURVEY §8(f) rank 1, cipher.go:110-141
+    for k in ("65536x256B", "32768x4KiB"):
+        assert g[k]["kernel_ms"] > 0 and g[k]["call_ms"] >= g[k]["kernel_ms"] and g[k]["openssl_key_once_ms"] > 0 and g[k]["parity_gate"]
     lat = d["latency"]                                                # the front-end at the service.Service seam
     assert lat["gpus"] == 1 and lat["p50_us"] > 0 and lat["p99_us"] >= lat["p50_us"] and len(lat["rates"]) >= 3
     assert e["with_pack"]["value"] == lat["sustained_per_s"] > 0
