@@ -8,8 +8,33 @@
 
 namespace polykey {
 
+#if defined(__x86_64__)
+#include <emmintrin.h>
+#endif
+
 namespace {
 inline uint64_t round16(uint64_t x) { return (x + 15u) & ~uint64_t(15); }
+
+// A request's payload into its slot of the page-locked arena.  Nobody on the CPU reads these bytes
+// again (the GPU pulls them over PCIe), so whole 16-byte pieces go out with non-temporal stores:
+// no read-for-ownership of the destination lines, no cache pollution — at 1e7 requests/s of 2 KB
+// the ordinary copy's extra read of the arena is 20 GB/s of memory traffic.  dst is 16-byte aligned
+// (slots are).  The caller's release store of the length is preceded by the sfence below.
+inline void copy_to_arena(uint8_t* dst, const void* src, size_t len)
+{
+#if defined(__x86_64__)
+    if (len >= 256) {
+        const uint8_t* s = static_cast<const uint8_t*>(src);
+        const size_t whole = len & ~size_t(15);
+        for (size_t i = 0; i < whole; i += 16)
+            _mm_stream_si128(reinterpret_cast<__m128i*>(dst + i), _mm_loadu_si128(reinterpret_cast<const __m128i*>(s + i)));
+        if (len > whole) std::memcpy(dst + whole, s + whole, len - whole);
+        _mm_sfence();                                        // the streamed bytes are visible before the commit
+        return;
+    }
+#endif
+    std::memcpy(dst, src, len);
+}
 using Clock = std::chrono::steady_clock;
 inline void cpu_relax()
 {
@@ -158,7 +183,7 @@ BatchingService::Reserve BatchingService::reserve(Shard* s, const std::string& n
                         // slots [old, old + k) are ours; the arena cannot be recycled before we commit
                         const uint32_t i = (uint32_t)old;
                         t.a = &a; t.idx = i; t.gen = a.gen; t.slots = (uint32_t)k;
-                        if (len) std::memcpy(a.payload + (uint64_t)i * slot_bytes_, payload, len);
+                        if (len) copy_to_arena(a.payload + (uint64_t)i * slot_bytes_, payload, len);
                         Arena::Rec& r = a.rec[i];
                         r.name_len = (uint32_t)name.size();
                         if (!name.empty())
