@@ -112,9 +112,10 @@ def main():
                "gpu_sync_vs_cpu_b_best": first(lambda x: x["gpu_sync_us"] < x["cpu_b_best_us"]),
                "gpu_pipe_vs_cpu_b_best": first(lambda x: x["gpu_pipe_us"] < x["cpu_b_best_us"]),
                "gpu_pipe_vs_cpu_a_1core": first(lambda x: x["gpu_pipe_us"] < x["cpu_a_1core_us"])},
-           "note": "ctypes call overhead (~2-4 us) is inside every number; cpu_b_all spawns its threads per call "
-                   "(no pool), so cpu_b_best = min(all cores, 1 core) is the fair CPU-B figure; cpu_a is the tool "
-                   "switch only (what the Go reference does); None = the GPU never wins in this sweep"}
+           "note": "ctypes call overhead (~2-4 us) is inside every number; cpu_b is the AVX-512 port with its persistent "
+                   "thread pool (round 2), re-reading ONE batch — cache-resident up to the last-level cache, which is the "
+                   "CPU's best case and, for a batch that has just arrived, the realistic one; cpu_b_best = min(all cores, "
+                   "1 core); cpu_a is the tool switch only (what the Go reference does); None = the GPU never wins in this sweep"}
     print(json.dumps(out))
 
 
