@@ -340,6 +340,7 @@ int main(int argc, char** argv)
         test_batching(1, 16, 120, 64, true);
         test_batching(2, 32, 60, 8, true);
         test_batching(1, 16, 60, 64, true, true);
+        test_batching(1, 16, 60, 4096, true);        // 256-byte slots: payloads span several, placeholder requests reach the kernel
         std::printf(g_fail ? "HOST TESTS FAILED (%d)\n" : "HOST CUDA TESTS OK\n", g_fail);
         return g_fail ? 1 : 0;
     }
