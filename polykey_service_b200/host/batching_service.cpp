@@ -148,6 +148,18 @@ BatchingStats BatchingService::stats() const
     return t;
 }
 
+// Request ids are per calling thread — thread k's are k, k + 2^40, ... in the id space, i.e. its own
+// round robin over the shards starting at shard k — so that taking one is not a read-modify-write on
+// a line every caller of the service shares (with one batch counter per shard already being the
+// front-end's ceiling, a second global counter per request was measurable).
+uint64_t& BatchingService::thread_request_id()
+{
+    static std::atomic<uint64_t> next_thread{0};
+    thread_local uint64_t id = next_thread.fetch_add(1, std::memory_order_relaxed);
+    return id;
+}
+uint64_t BatchingService::next_request_id() { return thread_request_id()++; }
+
 void BatchingService::wake_flusher(Shard* s)
 {
     if (!s->sleeping.load()) return;                        // seq_cst: pairs with the flusher's sleeping / state check
@@ -237,7 +249,7 @@ Result BatchingService::ExecuteTool(Context& ctx, const std::string& toolName, c
     if (round16(payload.size()) > cfg_.max_payload_bytes || payload.size() >= Arena::kUncommitted)
         return Result{nullptr, std::string("request payload exceeds the routing stage's arena")};
 
-    const uint64_t id = next_id_.fetch_add(1, std::memory_order_relaxed);
+    const uint64_t id = next_request_id();
     Shard* s = shards_[id % shards_.size()].get();          // shard by request id, no exchange
     Ticket t;
     if (reserve(s, toolName, payload.data(), payload.size(), t, true) != Reserve::kOk)
@@ -310,16 +322,16 @@ BatchingService::Enqueue BatchingService::EnqueueAsync(AsyncRequest& r, const st
     if (stopping_.load() || shards_.empty() || !healthy_.load()) return Enqueue::kRefused;
     if (round16(payload.size()) > cfg_.max_payload_bytes || payload.size() >= Arena::kUncommitted) return Enqueue::kRefused;
     if (toolName.size() > cfg_.max_name_bytes_per_request) return Enqueue::kRefused;
-    // the id (hence the shard) is taken only once the request is in: a busy shard must not skew the others
-    const uint64_t id = next_id_.load(std::memory_order_relaxed);
-    Shard* s = shards_[id % shards_.size()].get();
+    // the id (hence the shard) is consumed only once the request is in: a busy shard must not skew the others
+    uint64_t& local = thread_request_id();
+    Shard* s = shards_[local % shards_.size()].get();
     Ticket t;
     switch (reserve(s, toolName, payload.data(), payload.size(), t, false)) {
     case Reserve::kBusy:   return Enqueue::kBusy;
     case Reserve::kClosed: return Enqueue::kRefused;
     case Reserve::kOk:     break;
     }
-    next_id_.fetch_add(1, std::memory_order_relaxed);
+    ++local;
     r.rc_ = 0;
     r.idx_ = t.idx;
     r.slots_ = t.slots;

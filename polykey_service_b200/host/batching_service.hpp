@@ -234,6 +234,8 @@ private:
     enum class Reserve { kOk, kBusy, kClosed };
     Reserve reserve(Shard* s, const std::string& name, const void* payload, size_t len, Ticket& t, bool block);
     void wake_flusher(Shard* s);
+    static uint64_t& thread_request_id();
+    static uint64_t next_request_id();
     void flusher(Shard* s);
     void open_arena(Shard* s, uint32_t slot);
     void complete(Shard* s, Arena& a, int rc);
@@ -244,7 +246,6 @@ private:
     uint64_t slot_bytes_ = 0;               // payload slot of one request (a multiple of 16)
     uint32_t name_stride_ = 0;              // bytes per request in Arena::long_names
     std::vector<std::unique_ptr<Shard>> shards_;
-    std::atomic<uint64_t> next_id_{0};
     std::atomic<bool> stopping_{false}, healthy_{true};
     std::mutex log_mu_;                     // flushers of different GPUs share the sink
 };
