@@ -684,8 +684,9 @@ def frontend_leg(ctx: Ctx, seconds: float = 1.5):
     out = {"gpus": G, "generators": gens, "payload_bytes": 2048, "max_batch": 4096, "max_wait_us": 200,
            "api": "BatchingService::EnqueueAsync -> decision (C++ mirror of the Go batcher), open loop, Poisson arrivals",
            "rates": []}
-    # offered rates per GPU: light load (latency = service time), moderate, heavy, and flat out
-    for per_gpu in (1e5, 1e6, 5e6, 1e7):
+    # offered rates per GPU: light load (latency = service time), moderate, heavy, very heavy, and flat out
+    # (more than one process of producers can deliver: its completed rate is the front-end's ceiling)
+    for per_gpu in (1e5, 1e6, 5e6, 1e7, 2e7):
         rate = per_gpu * G
         try:
             p = subprocess.run([exe, "open", str(int(rate)), str(seconds), "4096", "200", "2048", str(gens)],
