@@ -150,6 +150,7 @@ func NewBatchingService(inner service.Service, cfg Config) (*BatchingService, er
 				names:     make([]byte, cfg.MaxBatch*cfg.MaxNameBytes),
 			}
 			if a.payload == nil || a.out == nil {
+				r.Close() // not yet in b.shards: Shutdown below would not reach it
 				b.Shutdown()
 				return nil, errors.New("routing: pinned allocation failed")
 			}
