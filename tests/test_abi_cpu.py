@@ -110,3 +110,23 @@ def test_the_deploy_makefile_is_the_build(pk):
     assert up_to_date.returncode == 0                                 # build.py went through this very target
     from polykey_service_b200 import build
     assert build.MAKEFILE.endswith("deploy/Makefile.pkroute")
+
+
+def test_deploy_files_are_well_formed():
+    """deploy/compose.gpu.yml parses and asks for what the reference's compose.yml (compose.yml:24-31:
+    0.5 CPU, 512 MiB, no device) does not: a GPU reservation; deploy/Dockerfile.gpu keeps the
+    reference's stage names and builds with cgo on through the same Makefile target."""
+    import yaml
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    comp = yaml.safe_load(open(os.path.join(root, "deploy", "compose.gpu.yml")))
+    svc = comp["services"]["polykey-server"]
+    dev = svc["deploy"]["resources"]["reservations"]["devices"][0]
+    assert dev["driver"] == "nvidia" and "gpu" in dev["capabilities"]
+    assert float(svc["deploy"]["resources"]["limits"]["cpus"]) >= 2
+    assert svc["build"]["dockerfile"] == "deploy/Dockerfile.gpu"
+    df = open(os.path.join(root, "deploy", "Dockerfile.gpu")).read()
+    for stage in ("AS builder", "AS tester", "AS production", "AS server"):
+        assert stage in df
+    assert "make -f deploy/Makefile.pkroute libpkroute" in df and "make -f deploy/Makefile.pkroute build-gpu" in df
+    mk = open(os.path.join(root, "deploy", "Makefile.pkroute")).read()
+    assert "CGO_ENABLED=1" in mk and "CGO_ENABLED=0" not in mk.split("build-gpu:")[1]
