@@ -8,7 +8,8 @@ workload is BASELINE.json configs[1] (C1): 4,096 tool-execution requests x 2 KB 
 8 providers.  One JSON line is printed by rank 0:
 
   value         whole-job requests/s with the batches already resident in HBM: K launches of the
-                fused kernel issued back to back (one CUDA graph of K kernel nodes) over a ring of
+                fused kernel issued back to back (one CUDA graph of K kernel nodes in four parallel
+                chains, programmatic dependent launch inside each) over a ring of
                 resident batches larger than L2, timed with CUDA events on the launching stream
   steady_state  the same issue mode over >= 2,000 launches (fill and drain of the overlapped
                 pipeline amortised) — `value` at the driver's K, this one K-independent
@@ -58,7 +59,10 @@ L2_BYTES = 126 << 20
 METRIC, UNIT = "routed_requests_per_sec", "requests/s"
 DTYPE = "u8/u32/u64 integer"
 PDL = 0x100                                                        # PK_LAUNCH_PDL, include/pk_route.h
-ISSUE = {"pdl": (1 | PDL, "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch "
+ISSUE = {"pdl4": (4 | PDL, "one CUDA graph of K kernel nodes in four parallel chains (a batch's chain = its ring position mod 4), "
+                            "programmatic dependent launch inside each chain (a kernel may start while its predecessor "
+                            "drains; batches are independent)"),
+         "pdl": (1 | PDL, "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch "
                           "(a kernel may start while its predecessor drains; batches are independent)"),
          "serial": (1, "one CUDA graph of K kernel nodes in a chain, each starting after its predecessor completed"),
          "plain": (0, "K plain launches")}
@@ -427,7 +431,8 @@ def resident_leg(ctx: Ctx, workload: str, steps: int, warmup: int, issue: str, a
         ctx.windows.append((t0, time.perf_counter()))
         res["steady"] = (steady_steps, ms_ss)
     other = {}
-    modes = (("pdl", 1 | PDL), ("serial", 1), ("plain", 0), ("plain_pdl", PDL), ("four_chains", 4)) if all_modes \
+    modes = (("pdl4", 4 | PDL), ("pdl", 1 | PDL), ("serial", 1), ("plain", 0), ("plain_pdl", PDL), ("four_chains", 4),
+             ("two_chains_pdl", 2 | PDL)) if all_modes \
         else (("serial", 1),)
     for name, mode in modes:
         if mode != use_graph:
@@ -599,11 +604,11 @@ def c4_leg(ctx: Ctx, batch: int, steps: int, warmup: int, e2e_reps: int = 3, pre
     t_end = time.perf_counter() + (0.4 if prewarm else 0.0)
     while time.perf_counter() < t_end:
         router.launch_many(slots, nb, use_graph=False)
-    router.launch_many(slots, nb * max(1, warmup // nb + 1), use_graph=1 | PDL)
+    router.launch_many(slots, nb * max(1, warmup // nb + 1), use_graph=4 | PDL)
     launches_before = router.launch_count
     ctx.barrier()
     w0 = time.perf_counter()
-    ms = router.launch_many(slots, nb * reps, use_graph=1 | PDL)
+    ms = router.launch_many(slots, nb * reps, use_graph=4 | PDL)
     ctx.torch.cuda.synchronize(ctx.local)
     w1 = time.perf_counter()
     ctx.barrier()
@@ -803,7 +808,7 @@ def run_gpu(args):
     if not args.lean:
         if ctx.world == 1 and workload == "c1":
             for w, k, k_e in (("c2", 2000, 60), ("c3", 60, 8)):
-                r2, s2 = resident_leg(ctx, w, k, 10, "pdl", all_modes=False, steady_steps=0, depth=2)
+                r2, s2 = resident_leg(ctx, w, k, 10, issue, all_modes=False, steady_steps=0, depth=2)
                 e2 = e2e_leg(ctx, r2, s2, 2, k_e, n_arenas=2, both_paths=False, sync_latency=False)
                 r2.close()
                 workloads[w] = {"workload": s2["desc"], "steps": k, "ms_per_step": s2["ms"] / k,
@@ -878,7 +883,7 @@ def run_gpu(args):
         "l2": f"ring of {res['ring']} resident batches = {res['ring'] * res['batch_bytes'] / 2**20:.0f} MiB > 126 MiB L2; launch k "
               "reads the batch after the one launch k-1 read, and the walk carries on across calls (warm-up launches "
               "never pre-load the timed ones)",
-        "issue": res["issue_desc"] + "; one stream, CUDA events on that stream",
+        "issue": res["issue_desc"] + "; CUDA events on the stream the graph is launched on",
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": ctx.peak, "unit": "GB/s",
                      "frac": achieved / ctx.peak, "traffic": traffic, "traffic_source": traffic_src,
                      "peak_source": ctx.peak_src, "kernel": "route_kernel (fused scan+hash+select)",
@@ -950,8 +955,7 @@ def run_gpu_c4(args):
                    "providers": 8},
         "parallelism": f"dp{ctx.world}: requests sharded by id, no collective",
         "l2": f"the shard is resident ({nb * c['batch_bytes'] / 2**20:.0f} MiB on rank 0) and each pass walks all of it",
-        "issue": "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch; one stream, "
-                 "CUDA events on that stream",
+        "issue": ISSUE["pdl4"][1] + "; CUDA events on the stream the graph is launched on",
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": ctx.peak, "unit": "GB/s", "frac": achieved / ctx.peak,
                      "traffic": None, "peak_source": ctx.peak_src, "kernel": "route_kernel (fused scan+hash+select)",
                      "algorithmic_bytes_per_launch": algorithmic_bytes(first), "avg_launch_us": pass_s * 1e6 / nb},
@@ -972,8 +976,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS) + ["c4"])
     ap.add_argument("--c4-batch", type=int, default=4096, help="requests per batch of the C4 stream (4096 / 16384 / 65536)")
-    ap.add_argument("--issue", default="pdl", choices=["pdl", "serial", "plain"],
-                    help="how the K timed launches are issued on their one stream (default: graph chain + programmatic dependent launch)")
+    ap.add_argument("--issue", default="pdl4", choices=["pdl4", "pdl", "serial", "plain"],
+                    help="how the K timed launches are issued (default: a graph of four parallel chains with programmatic "
+                         "dependent launch inside each; pdl = one such chain)")
     ap.add_argument("--depth", type=int, default=3, help="e2e pipeline depth: batches in flight through pk_submit/pk_wait")
     ap.add_argument("--no-graph", action="store_true", help="same as --issue plain")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -190,8 +190,9 @@ PK_API int  pk_wait(pk_handle* h, uint32_t slot);
  * the handle's previous pk_launch_many call stopped, so that a short call does not start on
  * the batches the call before it left in L2 — all on ONE stream (slot slots[0]'s), either
  * as `count` plain launches or (use_graph == 1) as one CUDA graph of `count` kernel
- * nodes in a chain, or (use_graph = k >= 2) as a graph of k parallel chains, launch j in
- * chain j % k, so that independent batches may overlap on the GPU; it brackets them with
+ * nodes in a chain, or (use_graph = k >= 2) as a graph of k parallel chains — a launch runs in
+ * chain (its position in the slot list) % k, so a slot is always in the same chain — so that
+ * independent batches may overlap on the GPU; it brackets them with
  * CUDA events on that stream, waits, and reports the device time in *elapsed_ms;
  * use_graph | PK_LAUNCH_PDL issues the same launches with programmatic stream serialization
  * (programmatic dependent launch): still one stream / one chain, but a kernel may start while

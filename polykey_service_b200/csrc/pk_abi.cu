@@ -512,7 +512,9 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
                 fe = cudaStreamWaitEvent(h->slots[slots[b]].stream, h->ev0, 0);
             if (fe != cudaSuccess) rc = PK_ERR_CUDA;
             for (uint32_t k = 0; k < count && rc == PK_OK; ++k) {
-                const uint32_t b = k % width;
+                // a slot always runs in the same chain, so two launches of one slot (which share its
+                // long-request scratch and its record array) are never concurrent
+                const uint32_t b = (uint32_t)((pos + k) % n_list) % width;
                 rc = launch_slot(h, nth(k), b == 0 ? st : h->slots[slots[b]].stream, pdl);
             }
             // join

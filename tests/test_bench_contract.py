@@ -63,7 +63,7 @@ def test_product_arm_line(oracle, pk):
     assert d["config"] == C1_CONFIG
     assert "L2" in d["l2"] and "programmatic dependent launch" in d["issue"]
     modes = d["issue_modes_ms_per_step"]
-    assert {"pdl", "serial", "plain", "plain_pdl", "four_chains"} <= set(modes) and modes["pdl"] == d["ms_per_step"]
+    assert {"pdl4", "pdl", "serial", "plain", "plain_pdl", "four_chains"} <= set(modes) and modes["pdl4"] == d["ms_per_step"]
     assert d["serial"]["ms_per_step"] == modes["serial"] and 0 < d["serial"]["frac"] <= r["frac"] * 1.25
     ss = d["steady_state"]
     assert ss["steps"] >= 2000 and 0 < ss["frac"] < 1.2 and ss["ms_per_step"] > 0
