@@ -40,6 +40,9 @@
 #ifndef PK_MIN_CTAS_TINY
 #define PK_MIN_CTAS_TINY 8   // ... lane-group kernels (G < 32): latency-bound, more resident warps win
 #endif
+#ifndef PK_MIN_CTAS_TINY4
+#define PK_MIN_CTAS_TINY4 6  // ... the 4-lane x 4-block variant: four 128-bit loads in flight per lane need the registers
+#endif
 #ifndef PK_UNROLL
 #define PK_UNROLL 4      // 128-bit loads in flight per lane
 #endif
@@ -525,7 +528,7 @@ __device__ __forceinline__ void route_body(const RouteParams& P, const DevTable&
 // slot's long-request scratch, so launch_route never sets pdl for a batch with long requests —
 // those are bandwidth-bound launches of hundreds of µs that have nothing to gain from overlap.
 template <int G, bool kWarpFinal, int B>
-__global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : PK_MIN_CTAS_TINY)
+__global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : B >= 4 ? PK_MIN_CTAS_TINY4 : PK_MIN_CTAS_TINY)
 route_kernel(const RouteParams P, const __grid_constant__ DevTable T)
 {
     if (P.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -595,13 +598,21 @@ cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len,
     if (p.n == 0) return cudaSuccess;
     pdl = pdl && p.n_extra == 0u;       // long requests share their slot's scratch between launches: no overlap
     // lanes per request: a full warp, or a half / quarter warp when every payload fits one step
-    // Up to 128 bytes: 8 lanes, a block each.  Up to 256 bytes: 8 lanes, TWO blocks each — against 16
-    // lanes with one block each, a warp pass then covers four requests instead of two for the same
-    // loop overhead, both loads of a lane are in flight together, and phase 2 adds 8 partials per
-    // request instead of 16 (PK_TINY_SHAPE=16 selects the old shape, for comparison).
+    // Payloads of at most 256 bytes (16 blocks): FOUR lanes per request, each taking 1, 2 or 4 blocks
+    // (all loaded before any is used), so a warp pass covers eight requests.  Against 16 lanes x 1
+    // block (round 1) and 8 x 2 the loop overhead per request and the partial sums phase 2 adds up
+    // halve each time; the four loads in flight per lane cost registers (40: six CTAs per SM instead
+    // of eight), which the measurement pays for: 65,536 x 256 B under the bench's issue 5.01 µs per
+    // batch at 4 x 4 against 5.15 at 8 x 2 (PK_TINY_SHAPE=8 / 16 select the older shapes).
     static const char* const t_env = std::getenv("PK_TINY_SHAPE");
-    int G = max_len <= 16u * kBlockBytes ? 8 : 32, B = max_len <= 8u * kBlockBytes ? 1 : 2;
-    if (G == 8 && B == 2 && t_env && std::atoi(t_env) == 16) { G = 16; B = 1; }
+    const int t_shape = t_env ? std::atoi(t_env) : 4;
+    int G = 32, B = 1;
+    if (max_len <= 16u * kBlockBytes) {
+        const uint32_t nblk_max = (max_len + kBlockBytes - 1u) / kBlockBytes;
+        G = 4; B = nblk_max <= 4u ? 1 : nblk_max <= 8u ? 2 : 4;
+        if (t_shape == 8 || (t_shape == 16 && nblk_max <= 8u)) { G = 8; B = nblk_max <= 8u ? 1 : 2; }
+        else if (t_shape == 16) { G = 16; B = 1; }
+    }
     // Few tiny requests: a warp each (latency mode below) beats packing them 2 or 4 to a warp —
     // the packed path pays a CTA barrier and a second phase that only pay off when warps are scarce.
     static const char* const g_env = std::getenv("PK_TINY_WARP_MAX");      // tuning aid: largest such batch
@@ -618,10 +629,6 @@ cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len,
     // R = 8; alone, the R = 64 batch takes 15 µs).
     // No more than 256 KiB of payload per CTA, so long payloads keep the thin shape.
     if (pdl) R = std::min(pow2_floor(p.n / 16u + 1u), pow2_floor((256u << 10) / (max_len ? max_len : 1u) + 1u));
-    // ... and no more than 128 requests per CTA for the lane-group kernels: with 256 the grid of a
-    // 65,536-request batch is 256 CTAs whose second phase runs one request per thread with nothing
-    // left to overlap it (65,536 x 256 B: 5.25 µs per batch at 128, 5.65 at 256, 5.89 at 64).
-    if (pdl && G < 32) R = std::min(R, 128u);
     static const char* const r_env = std::getenv("PK_REQS_PER_CTA");     // tuning aid (power of two)
     if (r_env && std::atoi(r_env) > 0) R = pow2_floor((uint32_t)std::atoi(r_env));
     R = R < r_min ? r_min : R > r_max ? r_max : R;
@@ -640,6 +647,8 @@ cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len,
     cudaError_t le;
     switch (G) {
     case 8:  le = B == 2 ? launch_one<8, false, 2>(p, table, ctas, stream) : launch_one<8, false, 1>(p, table, ctas, stream); break;
+    case 4:  le = B == 4 ? launch_one<4, false, 4>(p, table, ctas, stream)
+                : B == 2 ? launch_one<4, false, 2>(p, table, ctas, stream) : launch_one<4, false, 1>(p, table, ctas, stream); break;
     case 16: le = launch_one<16, false>(p, table, ctas, stream); break;
     default: le = warp_final ? launch_one<32, true>(p, table, ctas, stream) : launch_one<32, false>(p, table, ctas, stream); break;
     }
