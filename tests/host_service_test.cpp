@@ -274,6 +274,15 @@ static void test_oversized_name()
     const std::string edge(cfg.max_name_bytes_per_request, 'y');                        // the longest routed name
     r = svc.ExecuteTool(ctx, edge, nullptr, nullptr, nullptr);
     CHECK(!r.error && r.resp && r.resp->decision.has_value() && (r.resp->decision->flags & PK_FLAG_UNKNOWN_TOOL));
+    // names of 57..256 bytes travel in the arena's side array, not in the request's record: same decision as the oracle's
+    for (size_t len : {size_t(56), size_t(57), size_t(64), size_t(100), size_t(256)}) {
+        std::string nm(len, 'a');
+        for (size_t i = 0; i < len; ++i) nm[i] = (char)('a' + (i * 7 + len) % 26);
+        Struct params{{"prompt", Value(std::string("route me ") + std::to_string(len))}};
+        r = svc.ExecuteTool(ctx, nm, &params, nullptr, nullptr);
+        const pk_decision want = oracle_one(be.table_, nm, to_json(params));
+        CHECK(!r.error && r.resp && r.resp->decision.has_value() && std::memcmp(&want, &*r.resp->decision, sizeof want) == 0);
+    }
     r = svc.ExecuteTool(ctx, "example_tool", nullptr, nullptr, nullptr);
     CHECK(!r.error && r.resp && r.resp->decision.has_value() && r.resp->decision->tool_class == 0);
     CHECK(svc.healthy() && svc.stats().errors == 0);
