@@ -703,6 +703,15 @@ def frontend_leg(ctx: Ctx, seconds: float = 1.5):
         out["rates"].append({"offered_per_s": rate, "completed_per_s": r["completed_per_s"], "dropped": r["dropped"],
                              "errors": r["errors"], "p50_us": r["latency_us"]["p50"], "p99_us": r["latency_us"]["p99"],
                              "mean_batch": r["mean_batch"]})
+    # the same flat out with TWO shards (handle, flusher, open batch) per GPU: one open batch means one
+    # reservation counter every producer of the GPU meets on, and that counter is the single-shard ceiling
+    try:
+        p = subprocess.run([exe, "open", str(int(2e7 * G)), str(seconds), "4096", "200", "2048", str(gens)],
+                           capture_output=True, text=True, timeout=120, env=dict(env, PK_SHARDS_PER_GPU="2"))
+        r = json.loads(p.stdout.strip().splitlines()[-1])
+        out["two_shards_per_gpu"] = {"offered_per_s": 2e7 * G, "completed_per_s": r["completed_per_s"], "mean_batch": r["mean_batch"]}
+    except Exception as e:
+        out["two_shards_per_gpu"] = {"error": repr(e)[:200]}
     ok = [r for r in out["rates"] if "error" not in r]
     if ok:
         light = ok[0]

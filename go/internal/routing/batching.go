@@ -42,7 +42,9 @@ type Config struct {
 	MaxNameBytes int           // longest tool name that is routed (default 256)
 	MaxWait      time.Duration // hold-the-batch policy: deadline from the first request of a batch
 	HoldBatches  bool          // false (default): work-conserving — a free slot takes what is there now
-	Devices      []int         // one flusher, one Router, one table replica per GPU
+	Devices      []int         // one flusher, one Router, one table replica per entry; listing a GPU twice gives it two
+	                           // shards — two open batches, hence two reservation counters: measured with the C++
+	                           // mirror, one GPU takes 1.5e7 requests/s of 2 KB with one shard and 2.05e7 with two
 	Slots        int           // batches in flight on a GPU
 }
 

@@ -193,7 +193,10 @@ private:
 
 class BatchingService final : public Service {
 public:
-    // backends: one per GPU; not owned.
+    // backends: one per shard; not owned.  Usually one per GPU; two backends on the same GPU give it two
+    // open batches, i.e. two reservation counters for its producers to meet on — one GPU then takes
+    // 2.05e7 requests/s of 2 KB instead of 1.5e7 (the C ABI underneath: 2.4e7), at the price of a
+    // second polling flusher thread.
     BatchingService(Service* inner, std::vector<RouteBackend*> backends, BatchingConfig cfg);
     ~BatchingService() override;
 
