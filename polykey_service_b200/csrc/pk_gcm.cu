@@ -125,14 +125,37 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
 // for them since round 2; gcm_kernel above (one thread per message) stays for comparison
 // (PK_GCM_GROUP=0).  65,536 secrets are 65,536 threads there: 14 warps per SM, each on one serial
 // chain of 17 dependent AES blocks and table walks; here they are four times as many threads on
-// chains a quarter as long.  Dynamic shared memory, 81 KB -> 2 CTAs of 512 threads per SM (which is
-// also what its 53 registers allow):
-//   [0, 64 KB)   Te0 | Te2 replicated per bank, pkgcm::TeDual's layout (half the ALU instructions
-//                per AES round of the single replicated table — the pipe this kernel is bound by)
-//   then         pkgcm::GroupTables (round keys, tables of H^1..H^4: 16.6 KB)
+// chains a quarter as long.  Its time goes to shared-memory wavefronts first (the AES and GHASH
+// table lookups) and instruction issue second, so the layout is chosen for the lookups.  Dynamic
+// shared memory, 108.5 KB -> 2 CTAs of 512 threads per SM (which is also what its registers allow):
+//   [0, 64 KB)   Te0 | Te2 replicated per bank, pkgcm::TeDual's layout (conflict-free, and half the
+//                ALU instructions per AES round of the single replicated table)
+//   then         the head of pkgcm::GroupTables: round keys and the tables of H^1..H^(G-1), the
+//                lanes' closing powers (12.2 KB; one multiplication in five for a 256-byte secret)
 //   then         the round keys rotated left by 8 (TeDual::rkr)
+//   then         the table of H^G — the Horner step, four multiplications in five — replicated once
+//                per 16-byte bank group (32 KB: entry e of copy r at (8·e + r)·16, lane l reads copy
+//                l mod 8): the eight lanes a 128-bit shared load serves per wavefront never collide.
+//                Unreplicated, a lookup costs 10 wavefronts instead of 4 (r02 ncu: 7.0M of 19.8M
+//                load wavefronts were bank conflicts, all of them here).
 constexpr int kGroupThreads = 512;
-constexpr uint32_t kGroupSmemBytes = kTabBytes + (uint32_t)sizeof(pkgcm::GroupTables) + 256u;
+constexpr uint32_t kGroupHeadBytes = (uint32_t)(sizeof(pkgcm::GroupTables) - sizeof(pkgcm::HEntry) * 256u);
+constexpr uint32_t kGroupRkrAt = kTabBytes + kGroupHeadBytes;
+constexpr uint32_t kGroupHrepAt = kGroupRkrAt + 256u;
+constexpr uint32_t kGroupSmemBytes = kGroupHrepAt + 8u * 256u * (uint32_t)sizeof(pkgcm::HEntry);
+static_assert(kGroupHeadBytes % 16 == 0 && kGroupHrepAt % 128 == 0, "group-kernel shared layout");
+
+// The GHASH tables of gcm_group_pass in the layout above.
+struct GroupTablesSmem {
+    const uint8_t* hp;          // tables of H^1..H^(G-1), 4 KB each, plain
+    const uint8_t* hrep_lane;   // replicated table of H^G + this lane's copy offset
+    __device__ __forceinline__ void horner(uint64_t& yh, uint64_t& yl) const { pkgcm::ghash_mul_smem(hrep_lane, 7u, yh, yl); }
+    __device__ __forceinline__ void close(uint32_t e, uint64_t& yh, uint64_t& yl) const
+    {
+        const bool top = e == (uint32_t)pkgcm::kGroupLanes;      // (one lane of every group: no divergence)
+        pkgcm::ghash_mul_smem(top ? hrep_lane : hp + (e - 1u) * 4096u, top ? 7u : 4u, yh, yl);
+    }
+};
 
 __global__ void __launch_bounds__(kGroupThreads) gcm_group_kernel(const KeyContext* __restrict__ kc_g,
                                                                   const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
@@ -143,21 +166,32 @@ __global__ void __launch_bounds__(kGroupThreads) gcm_group_kernel(const KeyConte
 {
     constexpr uint32_t G = pkgcm::kGroupLanes;
     extern __shared__ __align__(16) uint8_t smem[];
-    pkgcm::GroupTables* gt = reinterpret_cast<pkgcm::GroupTables*>(smem + kTabBytes);
-    uint32_t* rkr = reinterpret_cast<uint32_t*>(smem + kTabBytes + sizeof(pkgcm::GroupTables));
-    for (uint32_t i = threadIdx.x; i < sizeof(pkgcm::GroupTables) / 16; i += blockDim.x)
-        reinterpret_cast<uint4*>(gt)[i] = __ldg(reinterpret_cast<const uint4*>(&kc_g->gg) + i);
+    const uint32_t* rk = reinterpret_cast<const uint32_t*>(smem + kTabBytes);       // GroupTables::rk
+    uint32_t* rkr = reinterpret_cast<uint32_t*>(smem + kGroupRkrAt);
+    for (uint32_t i = threadIdx.x; i < kGroupHeadBytes / 16; i += blockDim.x)
+        reinterpret_cast<uint4*>(smem + kTabBytes)[i] = __ldg(reinterpret_cast<const uint4*>(&kc_g->gg) + i);
     for (uint32_t i = threadIdx.x; i < 60; i += blockDim.x) {
         const uint32_t k = __ldg(&kc_g->gg.rk[i]);
         rkr[i] = (k << 8) | (k >> 24);
     }
+    // a thread fills a 128-byte row with eight copies of one value; it starts at chunk (row mod 8), so
+    // the eight lanes a 128-bit store serves per wavefront are on eight different bank groups (all
+    // starting at chunk 0 put every lane on the same banks: 1.8M of the kernel's 2.2M store
+    // wavefronts).  (Keep this loop shape: with one store per thread and iteration the compiler
+    // holds the shared base in a vector register and pays an extra add for every AES lookup.)
     for (uint32_t x = threadIdx.x; x < 512; x += blockDim.x) {       // x = 2·entry + table
         const uint32_t t = __ldg(&kc_g->te[(x & 1u) * 2u][x >> 1]);
         const uint4 t4 = make_uint4(t, t, t, t);
 #pragma unroll
-        for (int q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + x * 128u)[q] = t4;
+        for (uint32_t q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + x * 128u)[(q + x) & 7u] = t4;
+    }
+    for (uint32_t e = threadIdx.x; e < 256; e += blockDim.x) {       // H^G: copy r of entry e at (8·e + r)·16
+        const uint4 h4 = __ldg(reinterpret_cast<const uint4*>(&kc_g->gg.hp[G - 1][e]));
+#pragma unroll
+        for (uint32_t q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + kGroupHrepAt + e * 128u)[(q + e) & 7u] = h4;
     }
     __syncthreads();
+    const GroupTablesSmem gt{smem + kTabBytes + 256u, smem + kGroupHrepAt + (threadIdx.x & 7u) * 16u};
     const pkgcm::TeDual te{smem, rkr, (threadIdx.x & 31u) * 4u};
 
     // every thread stays to the end: the group's lanes meet in shuffles
@@ -178,7 +212,8 @@ __global__ void __launch_bounds__(kGroupThreads) gcm_group_kernel(const KeyConte
     if (active) {
         if (mode == 0 && lig == 0)
             for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];        // cipher.go:51-52
-        pkgcm::gcm_group_pass<(int)G>(gt, te, nonce, mode == 0 ? src : src + pkgcm::kNonceBytes,
+        pkgcm::gcm_group_pass<(int)G>(rk, gt, te, nonce,
+                                      mode == 0 ? src : src + pkgcm::kNonceBytes,
                                       mode == 0 ? dst + pkgcm::kNonceBytes : dst, clen, mode != 0, lig, yh, yl, j0);
     }
 #pragma unroll

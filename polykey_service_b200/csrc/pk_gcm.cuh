@@ -215,8 +215,38 @@ PKG_HD HEntry load_entry(const HEntry* __restrict__ t, uint32_t b)
 // byte r off the low end: its bit j (0 = least significant) is the coefficient of x^(135-j) =
 // x^(7-j) · x^128, and x^128 = 1 + x + x^2 + x^7 — 0xE1 at the top — so the byte folds back as the
 // carry-less product r ⊗ 0x1C2 placed at bits 48..63: four shifts, no table.
+#if defined(__CUDACC__)
+// Device form of the walk below for a table in SHARED memory, on 32-bit words and fully unrolled:
+// one 128-bit shared load per step (on 64-bit halves the compiler splits it in two, twice the
+// shared-memory wavefronts), constant byte positions, the fold as four shifts of one word.
+//   tbl     entry 0, in shared memory (plus the caller's lane offset in a replicated table)
+//   stride  log2 of the distance between entries in bytes: 4 plain, 7 replicated per bank group
+__device__ __forceinline__ void ghash_mul_smem(const uint8_t* __restrict__ tbl, uint32_t stride, uint64_t& xh, uint64_t& xl)
+{
+    const uint32_t x[4] = {(uint32_t)xl, (uint32_t)(xl >> 32), (uint32_t)xh, (uint32_t)(xh >> 32)};
+    uint4 e = *reinterpret_cast<const uint4*>(tbl + ((x[0] & 0xFFu) << stride));
+    uint32_t z0 = e.z, z1 = e.w, z2 = e.x, z3 = e.y;           // HEntry {h, l}: x, y = h low, high; z, w = l low, high
+#pragma unroll
+    for (int i = 1; i < 16; ++i) {
+        e = *reinterpret_cast<const uint4*>(tbl + (((x[i >> 2] >> (8 * (i & 3))) & 0xFFu) << stride));
+        const uint32_t r = z0 << 24;                           // the byte that falls off, at the top of a word
+        const uint32_t f = r ^ (r >> 1) ^ (r >> 2) ^ (r >> 7); // (rem<<8 ^ rem<<7 ^ rem<<6 ^ rem<<1) << 16
+        z0 = __funnelshift_r(z0, z1, 8) ^ e.z;
+        z1 = __funnelshift_r(z1, z2, 8) ^ e.w;
+        z2 = __funnelshift_r(z2, z3, 8) ^ e.x;
+        z3 = (z3 >> 8) ^ f ^ e.y;
+    }
+    xh = ((uint64_t)z3 << 32) | z2;
+    xl = ((uint64_t)z1 << 32) | z0;
+}
+#endif
+
+// On the device `t` must point into shared memory (every kernel stages its tables there).
 PKG_HD void ghash_mul_table(const HEntry* __restrict__ t, uint64_t& xh, uint64_t& xl)
 {
+#if defined(__CUDA_ARCH__)
+    ghash_mul_smem(reinterpret_cast<const uint8_t*>(t), 4u, xh, xl);
+#else
     HEntry e = load_entry(t, (uint32_t)xl & 0xFFu);
     uint64_t zh = e.h, zl = e.l;
 #pragma unroll 1
@@ -231,6 +261,7 @@ PKG_HD void ghash_mul_table(const HEntry* __restrict__ t, uint64_t& xh, uint64_t
     }
     xh = zh;
     xl = zl;
+#endif
 }
 PKG_HD void ghash_mul(const GcmTables* __restrict__ kc, uint64_t& xh, uint64_t& xl)
 {
@@ -321,8 +352,15 @@ PKG_HD void gcm_lane_pass(const GcmTables* __restrict__ kc, const Te& te, const 
 // table walk — and the lanes' terms XOR to X.  The lane that owns the lengths block (it has no AES
 // block to encrypt for it) encrypts J0 = nonce || 1 instead and returns E_K(J0) in j0[]: the work
 // is even and the tag needs no serial tail.  (yh, yl) = this lane's term.
-template <int G, typename Te>
-PKG_HD void gcm_group_pass(const GroupTables* __restrict__ gt, const Te& te, const uint8_t* __restrict__ nonce,
+// The GHASH tables arrive as a policy H: H.horner(yh, yl) multiplies by H^G, H.close(e, yh, yl) by H^e
+// (e = 1..G) — GroupTablesPlain below (host, unit test) or the kernel's shared-memory form.
+struct GroupTablesPlain {
+    const GroupTables* gt;
+    PKG_HDM void horner(uint64_t& yh, uint64_t& yl) const { ghash_mul_table(gt->hp[kGroupLanes - 1], yh, yl); }
+    PKG_HDM void close(uint32_t e, uint64_t& yh, uint64_t& yl) const { ghash_mul_table(gt->hp[e - 1u], yh, yl); }
+};
+template <int G, typename Te, typename H>
+PKG_HD void gcm_group_pass(const uint32_t* __restrict__ rk, const H& ht, const Te& te, const uint8_t* __restrict__ nonce,
                            const uint8_t* __restrict__ in, uint8_t* __restrict__ out, uint32_t len,
                            bool decrypt, uint32_t lig, uint64_t& yh, uint64_t& yl, uint32_t j0[4])
 {
@@ -332,20 +370,20 @@ PKG_HD void gcm_group_pass(const GroupTables* __restrict__ gt, const Te& te, con
     yh = 0; yl = 0;
     uint32_t last = 0xFFFFFFFFu;
     for (uint32_t b = lig; b < m; b += (uint32_t)G) {
-        if (last != 0xFFFFFFFFu) ghash_mul_table(gt->hp[G - 1], yh, yl);
+        if (last != 0xFFFFFFFFu) ht.horner(yh, yl);
         if (b < nblk) {
             uint32_t c[4];
-            ctr_block(gt->rk, te, n0, n1, n2, in, out, len, b << 4, decrypt, c);
+            ctr_block(rk, te, n0, n1, n2, in, out, len, b << 4, decrypt, c);
             yh ^= ((uint64_t)c[0] << 32) | c[1];
             yl ^= ((uint64_t)c[2] << 32) | c[3];
         } else {
             yl ^= (uint64_t)len * 8u;              // the lengths block: len(A) = 0 || len(C) in bits
             j0[0] = n0; j0[1] = n1; j0[2] = n2; j0[3] = 1u;
-            aes256_encrypt_block(te, gt->rk, j0);
+            aes256_encrypt_block(te, rk, j0);
         }
         last = b;
     }
-    if (last != 0xFFFFFFFFu) ghash_mul_table(gt->hp[m - last - 1u], yh, yl);     // H^(m - last), 1..G
+    if (last != 0xFFFFFFFFu) ht.close(m - last, yh, yl);       // H^(m - last), 1..G
 }
 
 // tag = X ^ E_K(nonce || 1), as 16 bytes

@@ -103,7 +103,7 @@ extern "C" int gcmh_group(const uint8_t* key, const uint8_t* nonce, const uint8_
     for (uint32_t lig = 0; lig < (uint32_t)kGroupLanes; ++lig) {
         uint64_t yh, yl;
         uint32_t mine[4] = {0, 0, 0, 0};
-        gcm_group_pass<kGroupLanes>(&kc.gg, TeTables{kc.te}, nonce, in, out, len, decrypt != 0, lig, yh, yl, mine);
+        gcm_group_pass<kGroupLanes>(kc.gg.rk, GroupTablesPlain{&kc.gg}, TeTables{kc.te}, nonce, in, out, len, decrypt != 0, lig, yh, yl, mine);
         xh ^= yh; xl ^= yl;
         if (lig == ((len + 15u) >> 4) % (uint32_t)kGroupLanes) { std::memcpy(j0, mine, 16); ++owners; }
     }
