@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(kThreads) gcm_kernel(const KeyContext* __restr
 //                Unreplicated, a lookup costs 10 wavefronts instead of 4 (r02 ncu: 7.0M of 19.8M
 //                load wavefronts were bank conflicts, all of them here).
 constexpr int kGroupThreads = 512;
+constexpr uint32_t kGroupCtasPerSm = 2;
 constexpr uint32_t kGroupHeadBytes = (uint32_t)(sizeof(pkgcm::GroupTables) - sizeof(pkgcm::HEntry) * 256u);
 constexpr uint32_t kGroupRkrAt = kTabBytes + kGroupHeadBytes;
 constexpr uint32_t kGroupHrepAt = kGroupRkrAt + 256u;
@@ -174,74 +175,97 @@ __global__ void __launch_bounds__(kGroupThreads) gcm_group_kernel(const KeyConte
         const uint32_t k = __ldg(&kc_g->gg.rk[i]);
         rkr[i] = (k << 8) | (k >> 24);
     }
-    // a thread fills a 128-byte row with eight copies of one value; it starts at chunk (row mod 8), so
-    // the eight lanes a 128-bit store serves per wavefront are on eight different bank groups (all
-    // starting at chunk 0 put every lane on the same banks: 1.8M of the kernel's 2.2M store
-    // wavefronts).  (Keep this loop shape: with one store per thread and iteration the compiler
-    // holds the shared base in a vector register and pays an extra add for every AES lookup.)
-    for (uint32_t x = threadIdx.x; x < 512; x += blockDim.x) {       // x = 2·entry + table
-        const uint32_t t = __ldg(&kc_g->te[(x & 1u) * 2u][x >> 1]);
-        const uint4 t4 = make_uint4(t, t, t, t);
+    // a thread fills a 128-byte row with eight copies of one value — a T-table word, or an entry of
+    // the H^G table (row 8·e .. 8·e+7 of 16 bytes).  It starts at chunk (row mod 8), so the eight lanes
+    // a 128-bit store serves per wavefront are on eight different bank groups (all starting at chunk 0
+    // put every lane on the same banks: 1.8M of the kernel's 2.2M store wavefronts).
+    // (One loop of this shape on purpose: with a second staging loop, or one store per thread and
+    // iteration, ptxas keeps the shared base in a vector register instead of a uniform one and every
+    // AES lookup below pays an extra add — 66 instead of 50 instructions per round.)
+    for (uint32_t x = threadIdx.x; x < 768; x += blockDim.x) {       // x = 2·entry + table; from 512: entry of H^G
+        uint4 t4;
+        uint32_t at = x * 128u;
+        if (x < 512) {
+            const uint32_t t = __ldg(&kc_g->te[(x & 1u) * 2u][x >> 1]);
+            t4 = make_uint4(t, t, t, t);
+        } else {
+            t4 = __ldg(reinterpret_cast<const uint4*>(&kc_g->gg.hp[G - 1][x - 512u]));
+            at += kGroupHrepAt - 512u * 128u;
+        }
 #pragma unroll
-        for (uint32_t q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + x * 128u)[(q + x) & 7u] = t4;
-    }
-    for (uint32_t e = threadIdx.x; e < 256; e += blockDim.x) {       // H^G: copy r of entry e at (8·e + r)·16
-        const uint4 h4 = __ldg(reinterpret_cast<const uint4*>(&kc_g->gg.hp[G - 1][e]));
-#pragma unroll
-        for (uint32_t q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + kGroupHrepAt + e * 128u)[(q + e) & 7u] = h4;
+        for (uint32_t q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + at)[(q + x) & 7u] = t4;
     }
     __syncthreads();
     const GroupTablesSmem gt{smem + kTabBytes + 256u, smem + kGroupHrepAt + (threadIdx.x & 7u) * 16u};
     const pkgcm::TeDual te{smem, rkr, (threadIdx.x & 31u) * 4u};
 
-    // every thread stays to the end: the group's lanes meet in shuffles
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t i = first + t / G, lig = t % G, lane = threadIdx.x & 31u, lead = lane & ~(G - 1u);
-    uint32_t len = i < n ? in_len[i] : 0u;
-    bool active = i < n && len < long_bytes;                 // (the long ones are gcm_long_kernel's)
-    const uint8_t* src = active ? in + in_off[i] : nullptr;
-    uint8_t* dst = active ? out + out_off[i] : nullptr;
-    if (active && mode != 0 && len < pkgcm::kOverhead) {     // shorter than nonce + tag: cipher.go:69-71 / Open fails
-        if (lig == 0) status[i] = len < pkgcm::kNonceBytes ? 2u : 1u;
-        active = false;
-    }
-    const uint32_t clen = mode == 0 ? len : len - pkgcm::kOverhead;   // (meaningful when active)
-    const uint8_t* nonce = mode == 0 ? nonces + (size_t)i * pkgcm::kNonceBytes : src;
-    uint64_t yh = 0, yl = 0;
-    uint32_t j0[4] = {0u, 0u, 0u, 0u};
-    if (active) {
-        if (mode == 0 && lig == 0)
-            for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];        // cipher.go:51-52
-        pkgcm::gcm_group_pass<(int)G>(rk, gt, te, nonce,
-                                      mode == 0 ? src : src + pkgcm::kNonceBytes,
-                                      mode == 0 ? dst + pkgcm::kNonceBytes : dst, clen, mode != 0, lig, yh, yl, j0);
-    }
-#pragma unroll
-    for (uint32_t d = G / 2u; d > 0; d >>= 1) {
-        yh ^= __shfl_xor_sync(0xFFFFFFFFu, yh, d);
-        yl ^= __shfl_xor_sync(0xFFFFFFFFu, yl, d);
-    }
-    // the lane that owned the lengths block holds E_K(J0): it makes the tag
-    const uint32_t owner = active ? ((clen + 15u) >> 4) % G : 0u;
-    uint32_t ok = 1u;
-    if (active && lig == owner) {
-        const uint32_t tw[4] = {(uint32_t)(yh >> 32) ^ j0[0], (uint32_t)yh ^ j0[1], (uint32_t)(yl >> 32) ^ j0[2], (uint32_t)yl ^ j0[3]};
-        if (mode == 0) {
-            uint8_t* tp = dst + pkgcm::kNonceBytes + len;
-            for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) tp[b] = (uint8_t)(tw[b >> 2] >> (24u - 8u * (b & 3u)));
-        } else {
-            const uint8_t* tp = src + pkgcm::kNonceBytes + clen;
-            uint32_t diff = 0;
-            for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) diff |= (uint32_t)tp[b] ^ ((tw[b >> 2] >> (24u - 8u * (b & 3u))) & 0xFFu);
-            ok = diff == 0u;
-            status[i] = ok ? 0u : 1u;
+    // The grid is resident (the host launches at most what fits on the SMs at once) and a warp walks
+    // UNITS of 32 / G consecutive messages, unit u = k · (warps in the grid) + warp · gridDim + CTA:
+    // warp-major, so when the units do not divide evenly every CTA — every SM — gets the same number
+    // of second helpings.  (With one CTA per 128 messages, 65,536 secrets were 1.73 waves of CTAs:
+    // the SMs sat idle for 18% of the kernel waiting for the last wave, r02 ncu sm__cycles_active.)
+    // Every lane of a warp stays to the end of a unit: the group's lanes meet in shuffles.
+    const uint32_t lane = threadIdx.x & 31u, lig = lane % G, lead = lane & ~(G - 1u);
+    const uint32_t n_units = (n - first + 32u / G - 1u) / (32u / G);
+    for (uint32_t u = (threadIdx.x >> 5) * gridDim.x + blockIdx.x; u < n_units; u += (blockDim.x >> 5) * gridDim.x) {
+        const uint32_t i = first + u * (32u / G) + lane / G;
+        uint32_t len = i < n ? in_len[i] : 0u;
+        bool active = i < n && len < long_bytes;                 // (the long ones are gcm_long_kernel's)
+        const uint8_t* src = active ? in + in_off[i] : nullptr;
+        uint8_t* dst = active ? out + out_off[i] : nullptr;
+        if (active && mode != 0 && len < pkgcm::kOverhead) {     // shorter than nonce + tag: cipher.go:69-71 / Open fails
+            if (lig == 0) status[i] = len < pkgcm::kNonceBytes ? 2u : 1u;
+            active = false;
         }
-    }
-    if (mode != 0) {
-        ok = __shfl_sync(0xFFFFFFFFu, ok, lead + owner);
-        if (active && !ok)                                   // authentication failed: release no plaintext
-            for (uint32_t b = lig * 16u; b < clen; b += G * 16u)
-                for (uint32_t k = b; k < b + 16u && k < clen; ++k) dst[k] = 0;
+        const uint32_t clen = mode == 0 ? len : len - pkgcm::kOverhead;   // (meaningful when active)
+        const uint8_t* nonce = mode == 0 ? nonces + (size_t)i * pkgcm::kNonceBytes : src;
+        uint64_t yh = 0, yl = 0;
+        uint32_t j0[4] = {0u, 0u, 0u, 0u};
+        if (active) {
+            if (mode == 0 && lig == 0) {                                                    // cipher.go:51-52
+                if (((uintptr_t)nonce & 3u) == 0)      // (dst is 4-byte aligned by contract)
+                    for (uint32_t b = 0; b < pkgcm::kNonceBytes; b += 4) pkgcm::store32(dst + b, pkgcm::load32(nonce + b));
+                else
+                    for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];
+            }
+            pkgcm::gcm_group_pass<(int)G>(rk, gt, te, nonce,
+                                          mode == 0 ? src : src + pkgcm::kNonceBytes,
+                                          mode == 0 ? dst + pkgcm::kNonceBytes : dst, clen, mode != 0, lig, yh, yl, j0);
+        }
+#pragma unroll
+        for (uint32_t d = G / 2u; d > 0; d >>= 1) {
+            yh ^= __shfl_xor_sync(0xFFFFFFFFu, yh, d);
+            yl ^= __shfl_xor_sync(0xFFFFFFFFu, yl, d);
+        }
+        // the lane that owned the lengths block holds E_K(J0): it makes the tag
+        const uint32_t owner = active ? ((clen + 15u) >> 4) % G : 0u;
+        uint32_t ok = 1u;
+        if (active && lig == owner) {
+            const uint32_t tw[4] = {(uint32_t)(yh >> 32) ^ j0[0], (uint32_t)yh ^ j0[1], (uint32_t)(yl >> 32) ^ j0[2], (uint32_t)yl ^ j0[3]};
+            // (the tag follows the ciphertext: word accesses when the message length is a multiple of 4)
+            if (mode == 0) {
+                uint8_t* tp = dst + pkgcm::kNonceBytes + len;
+                if ((len & 3u) == 0)
+                    for (uint32_t j = 0; j < 4; ++j) pkgcm::store32(tp + 4 * j, pkgcm::bswap32(tw[j]));
+                else
+                    for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) tp[b] = (uint8_t)(tw[b >> 2] >> (24u - 8u * (b & 3u)));
+            } else {
+                const uint8_t* tp = src + pkgcm::kNonceBytes + clen;
+                uint32_t diff = 0;
+                if ((clen & 3u) == 0)
+                    for (uint32_t j = 0; j < 4; ++j) diff |= pkgcm::load32(tp + 4 * j) ^ pkgcm::bswap32(tw[j]);
+                else
+                    for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) diff |= (uint32_t)tp[b] ^ ((tw[b >> 2] >> (24u - 8u * (b & 3u))) & 0xFFu);
+                ok = diff == 0u;
+                status[i] = ok ? 0u : 1u;
+            }
+        }
+        if (mode != 0) {
+            ok = __shfl_sync(0xFFFFFFFFu, ok, lead + owner);
+            if (active && !ok)                                   // authentication failed: release no plaintext
+                for (uint32_t b = lig * 16u; b < clen; b += G * 16u)
+                    for (uint32_t k = b; k < b + 16u && k < clen; ++k) dst[k] = 0;
+        }
     }
 }
 
@@ -304,6 +328,7 @@ __global__ void __launch_bounds__(kThreads) gcm_long_kernel(const KeyContext* __
 
 struct pk_gcm {
     int device = 0;
+    int num_sms = 148;
     uint32_t max_messages = 0;
     uint64_t max_bytes = 0;
     KeyContext* d_kc = nullptr;
@@ -480,7 +505,9 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
                 // kGroupLanes lanes per message; narrower blocks spread a small batch over more SMs
                 const uint64_t lanes = (uint64_t)cnt * pkgcm::kGroupLanes;
                 const uint32_t threads = lanes >= 148u * (uint64_t)kGroupThreads ? (uint32_t)kGroupThreads : lanes >= 148u * 128u ? 128u : 64u;
-                gcm_group_kernel<<<(uint32_t)((lanes + threads - 1) / threads), threads, kGroupSmemBytes, s_run>>>(
+                const uint64_t resident = (uint64_t)h->num_sms * kGroupCtasPerSm;      // (shared memory allows two per SM)
+                const uint64_t ctas = (lanes + threads - 1) / threads;
+                gcm_group_kernel<<<(uint32_t)(ctas < resident ? ctas : resident), threads, kGroupSmemBytes, s_run>>>(
                     h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce, h->d_out, h->d_out_off, h->d_status, lo, hi, mode, long_bytes);
             } else {
                 // one thread per message: spread a small batch over more SMs with narrower blocks
@@ -558,6 +585,7 @@ int pk_gcm_init(int device, const uint8_t* key, uint32_t key_len, uint32_t max_m
     pkgcm::make_key_context(key, kc);
     const size_t n = max_messages;
     cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gcm_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(gcm_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGroupSmemBytes);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);

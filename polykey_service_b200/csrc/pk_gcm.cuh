@@ -139,6 +139,10 @@ PKG_HD void aes256_encrypt_block(const Te& te, const uint32_t* __restrict__ rk, 
 }
 
 #if defined(__CUDACC__)
+#ifndef PK_GCM_AES_UNROLL
+#define PK_GCM_AES_UNROLL 1      // rounds per loop iteration of the device AES (tools/gpu_gcm_ab.sh tries 2)
+#endif
+constexpr int kAesUnroll = PK_GCM_AES_UNROLL;
 // Device form used by the kernels: Te0 and Te2 (= Te0 rotated by 16) side by side, each replicated
 // per bank — entry x is 256 bytes: 32 lanes × Te0[x], then 32 lanes × Te2[x] (64 KB in all).
 //   * the address of a lookup is ONE byte-permute: (byte k of the state word) << 8 | lane·4,
@@ -168,7 +172,7 @@ struct TeDual {
 __device__ __forceinline__ void aes256_encrypt_block(const TeDual& te, const uint32_t* __restrict__ rk, uint32_t s[4])
 {
     uint32_t s0 = s[0] ^ rk[0], s1 = s[1] ^ rk[1], s2 = s[2] ^ rk[2], s3 = s[3] ^ rk[3];
-#pragma unroll 1
+#pragma unroll kAesUnroll
     for (int r = 1; r < 14; ++r) {
         const uint4 kr = *reinterpret_cast<const uint4*>(te.rkr + 4 * r);
         const uint32_t u0 = te.at(s1, 2, 0) ^ te.at(s3, 0, 1) ^ kr.x;
@@ -296,12 +300,32 @@ PKG_HD void ctr_block(const uint32_t* __restrict__ rk, const Te& te, uint32_t n0
     const uint32_t nb = len - at < 16 ? len - at : 16;
     c[0] = c[1] = c[2] = c[3] = 0;
     if (nb == 16) {
+        uint32_t w[4], o[4];
+#if defined(__CUDA_ARCH__)
+        // one 128-bit access where the side is 16-byte aligned (the contract only promises 4; in a
+        // sealed slot the ciphertext sits 12 bytes in, so one side of every call is the narrow one)
+        if (((uintptr_t)(in + at) & 15u) == 0) {
+            const uint4 v = *reinterpret_cast<const uint4*>(in + at);
+            w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+        } else
+#endif
+        {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) w[j] = load32(in + at + 4 * j);
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const uint32_t w = load32(in + at + 4 * j);
-            const uint32_t o = w ^ bswap32(ks[j]);
-            store32(out + at + 4 * j, o);
-            c[j] = bswap32(decrypt ? w : o);
+            o[j] = w[j] ^ bswap32(ks[j]);
+            c[j] = bswap32(decrypt ? w[j] : o[j]);
+        }
+#if defined(__CUDA_ARCH__)
+        if (((uintptr_t)(out + at) & 15u) == 0) {
+            *reinterpret_cast<uint4*>(out + at) = make_uint4(o[0], o[1], o[2], o[3]);
+        } else
+#endif
+        {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) store32(out + at + 4 * j, o[j]);
         }
     } else {
         for (uint32_t b = 0; b < nb; ++b) {
@@ -311,6 +335,19 @@ PKG_HD void ctr_block(const uint32_t* __restrict__ rk, const Te& te, uint32_t n0
             c[b >> 2] |= (uint32_t)(decrypt ? ib : ob) << (24 - 8 * (b & 3));
         }
     }
+}
+
+// The 12 nonce bytes as three big-endian words: word loads when the nonce is 4-byte aligned (a
+// sealed slot's always is; a caller's nonce array need not be), byte loads otherwise.
+PKG_HD void load_nonce(const uint8_t* __restrict__ nonce, uint32_t& n0, uint32_t& n1, uint32_t& n2)
+{
+#if defined(__CUDA_ARCH__)
+    if (((uintptr_t)nonce & 3u) == 0) {
+        n0 = bswap32(load32(nonce)); n1 = bswap32(load32(nonce + 4)); n2 = bswap32(load32(nonce + 8));
+        return;
+    }
+#endif
+    n0 = load_be32(nonce); n1 = load_be32(nonce + 4); n2 = load_be32(nonce + 8);
 }
 
 // Warp-per-message form, one lane's share.  GHASH is X = sum over blocks B_b · H^(m-b), b = 0..m-1,
@@ -364,7 +401,8 @@ PKG_HD void gcm_group_pass(const uint32_t* __restrict__ rk, const H& ht, const T
                            const uint8_t* __restrict__ in, uint8_t* __restrict__ out, uint32_t len,
                            bool decrypt, uint32_t lig, uint64_t& yh, uint64_t& yl, uint32_t j0[4])
 {
-    const uint32_t n0 = load_be32(nonce), n1 = load_be32(nonce + 4), n2 = load_be32(nonce + 8);
+    uint32_t n0, n1, n2;
+    load_nonce(nonce, n0, n1, n2);
     const uint32_t nblk = (len + 15u) >> 4;
     const uint32_t m = nblk + 1u;
     yh = 0; yl = 0;
