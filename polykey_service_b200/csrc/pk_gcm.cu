@@ -26,13 +26,22 @@ constexpr int kThreads = 256;          // largest block; small batches use narro
 // 41 KB -> 5 CTAs of 256 threads per SM
 //   the key's round keys and GHASH tables (pkgcm::GcmTables, 8.8 KB) and Te0 replicated once per
 //   bank (32 KB: entry x of lane l at word 32·x + l), so the AES lookups of a warp never collide.
-// gcm_long_kernel (one warp per message; ALU-pipe-bound, wants fewer instructions): dynamic,
-// 72.5 KB -> 3 CTAs per SM
+// gcm_long_kernel (one warp per message): dynamic, 104.5 KB -> 2 CTAs per SM (of up to 16 warps)
 //   [0, 64 KB)   Te0 | Te2 replicated per bank, pkgcm::TeDual's layout
-//   then         pkgcm::GcmTables
-//   then         the round keys rotated left by 8 (TeDual::rkr)
+//   then         the round keys (GcmTables::rk), the round keys rotated left by 8 (TeDual::rkr),
+//                the 4-bit tables of H^1..H^32 (KeyContext::pw4, 8 KB: a lane closes with its own
+//                power, once per message — bit-serial, that product was a quarter of the kernel's
+//                instructions on 4 KiB messages, r02 ncu)
+//   then         the table of H^32 — the lanes' Horner step — replicated once per 16-byte bank
+//                group, as in the lane-group kernel below (32 KB; unreplicated, 39M of the
+//                kernel's 133M shared wavefronts were bank conflicts on it, r02 ncu)
 constexpr uint32_t kTabBytes = 256u * 256u;
-constexpr uint32_t kSmemBytes = kTabBytes + (uint32_t)sizeof(pkgcm::GcmTables) + 256u;
+constexpr uint32_t kLongRkAt = kTabBytes, kLongRkrAt = kLongRkAt + 256u, kLongPwAt = kLongRkrAt + 256u;
+constexpr uint32_t kLongHrepAt = kLongPwAt + 32u * 16u * (uint32_t)sizeof(pkgcm::HEntry);
+constexpr uint32_t kSmemBytes = kLongHrepAt + 8u * 256u * (uint32_t)sizeof(pkgcm::HEntry);
+constexpr uint32_t kLongCtasPerSm = 2;
+constexpr int kLongThreads = 512;      // largest block of gcm_long_kernel
+static_assert(kLongHrepAt % 128 == 0, "long-kernel shared layout");
 
 __device__ __forceinline__ void stage_key(pkgcm::GcmTables* kc, const KeyContext* __restrict__ kc_g)
 {
@@ -50,30 +59,6 @@ __device__ __forceinline__ void stage_single(pkgcm::GcmTables& kc, uint32_t* te_
         for (int q = 0; q < 8; ++q) reinterpret_cast<uint4*>(te_rep + x * 32)[q] = t4;
     }
     __syncthreads();
-}
-
-struct Staged {
-    const pkgcm::GcmTables* kc;
-    pkgcm::TeDual te;
-};
-
-__device__ __forceinline__ Staged stage_dual(uint8_t* smem, const KeyContext* __restrict__ kc_g)
-{
-    pkgcm::GcmTables* kc = reinterpret_cast<pkgcm::GcmTables*>(smem + kTabBytes);
-    uint32_t* rkr = reinterpret_cast<uint32_t*>(smem + kTabBytes + sizeof(pkgcm::GcmTables));
-    stage_key(kc, kc_g);
-    for (uint32_t i = threadIdx.x; i < 60; i += blockDim.x) {
-        const uint32_t k = __ldg(&kc_g->g.rk[i]);
-        rkr[i] = (k << 8) | (k >> 24);
-    }
-    for (uint32_t x = threadIdx.x; x < 512; x += blockDim.x) {       // x = 2·entry + table
-        const uint32_t t = __ldg(&kc_g->te[(x & 1u) * 2u][x >> 1]);
-        const uint4 t4 = make_uint4(t, t, t, t);
-#pragma unroll
-        for (int q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + x * 128u)[q] = t4;
-    }
-    __syncthreads();
-    return Staged{kc, pkgcm::TeDual{smem, rkr, (threadIdx.x & 31u) * 4u}};
 }
 
 // mode 0: seal   in = plaintext arena,  out = sealed arena (nonce || ct || tag per message)
@@ -207,7 +192,8 @@ __global__ void __launch_bounds__(kGroupThreads) gcm_group_kernel(const KeyConte
     // Every lane of a warp stays to the end of a unit: the group's lanes meet in shuffles.
     const uint32_t lane = threadIdx.x & 31u, lig = lane % G, lead = lane & ~(G - 1u);
     const uint32_t n_units = (n - first + 32u / G - 1u) / (32u / G);
-    for (uint32_t u = (threadIdx.x >> 5) * gridDim.x + blockIdx.x; u < n_units; u += (blockDim.x >> 5) * gridDim.x) {
+    const uint32_t warp = __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0);     // (uniform by construction: see gcm_long_kernel)
+    for (uint32_t u = warp * gridDim.x + blockIdx.x; u < n_units; u += (blockDim.x >> 5) * gridDim.x) {
         const uint32_t i = first + u * (32u / G) + lane / G;
         uint32_t len = i < n ? in_len[i] : 0u;
         bool active = i < n && len < long_bytes;                 // (the long ones are gcm_long_kernel's)
@@ -269,57 +255,98 @@ __global__ void __launch_bounds__(kGroupThreads) gcm_group_kernel(const KeyConte
     }
 }
 
-// One WARP per long message (those gcm_kernel skipped; long_idx lists them).  Lane l takes the
+// The GHASH tables of gcm_lane_pass in gcm_long_kernel's shared layout.
+struct LaneTablesSmem {
+    const uint8_t* hrep_lane;        // replicated table of H^32 + this lane's copy offset
+    const pkgcm::HEntry* pw4;        // 4-bit tables of H^1..H^32, 16 entries each
+    __device__ __forceinline__ void horner(uint64_t& yh, uint64_t& yl) const { pkgcm::ghash_mul_smem(hrep_lane, 7u, yh, yl); }
+    __device__ __forceinline__ void close(uint32_t e, uint64_t& yh, uint64_t& yl) const { pkgcm::ghash_mul_table4(pw4 + (e - 1u) * 16u, yh, yl); }
+};
+
+// One WARP per long message (those the short-message kernels skip; long_idx lists them).  Lane l takes the
 // 16-byte blocks l, l+32, ... — a warp reads and writes 512 consecutive bytes per step — and the
-// lanes' GHASH terms (pkgcm::gcm_lane_pass) XOR together through shuffles.
-__global__ void __launch_bounds__(kThreads) gcm_long_kernel(const KeyContext* __restrict__ kc_g,
-                                                            const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
-                                                            const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
-                                                            uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
-                                                            uint32_t* __restrict__ status, const uint32_t* __restrict__ long_idx,
-                                                            uint32_t first, uint32_t n_long, int mode)
+// lanes' GHASH terms (pkgcm::gcm_lane_pass) XOR together through shuffles.  The grid is resident and
+// a warp walks the list warp-major (entry k · (warps in the grid) + warp · gridDim + CTA), like
+// gcm_group_kernel: the tables are staged once per CTA, not once per eight messages.
+__global__ void __launch_bounds__(kLongThreads) gcm_long_kernel(const KeyContext* __restrict__ kc_g,
+                                                                const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
+                                                                const uint32_t* __restrict__ in_len, const uint8_t* __restrict__ nonces,
+                                                                uint8_t* __restrict__ out, const uint64_t* __restrict__ out_off,
+                                                                uint32_t* __restrict__ status, const uint32_t* __restrict__ long_idx,
+                                                                uint32_t first, uint32_t n_long, int mode)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    const Staged st = stage_dual(smem, kc_g);
-    const pkgcm::GcmTables* kc = st.kc;
-    const pkgcm::TeDual& te = st.te;
+    uint32_t* rk_s = reinterpret_cast<uint32_t*>(smem + kLongRkAt);
+    uint32_t* rkr = reinterpret_cast<uint32_t*>(smem + kLongRkrAt);
+    for (uint32_t i = threadIdx.x; i < 60; i += blockDim.x) {
+        const uint32_t k = __ldg(&kc_g->g.rk[i]);
+        rk_s[i] = k;
+        rkr[i] = (k << 8) | (k >> 24);
+    }
+    for (uint32_t i = threadIdx.x; i < 32 * 16; i += blockDim.x)
+        reinterpret_cast<uint4*>(smem + kLongPwAt)[i] = __ldg(reinterpret_cast<const uint4*>(&kc_g->pw4[0][0]) + i);
+    // (the staging loop of gcm_group_kernel, with its reasons: rotated chunks, one loop)
+    for (uint32_t x = threadIdx.x; x < 768; x += blockDim.x) {       // x = 2·entry + table; from 512: entry of H^32
+        uint4 t4;
+        uint32_t at = x * 128u;
+        if (x < 512) {
+            const uint32_t t = __ldg(&kc_g->te[(x & 1u) * 2u][x >> 1]);
+            t4 = make_uint4(t, t, t, t);
+        } else {
+            t4 = __ldg(reinterpret_cast<const uint4*>(&kc_g->g.ht32[x - 512u]));
+            at += kLongHrepAt - 512u * 128u;
+        }
+#pragma unroll
+        for (uint32_t q = 0; q < 8; ++q) reinterpret_cast<uint4*>(smem + at)[(q + x) & 7u] = t4;
+    }
+    __syncthreads();
+    const uint32_t* rk = rk_s;
+    const LaneTablesSmem ht{smem + kLongHrepAt + (threadIdx.x & 7u) * 16u, reinterpret_cast<const pkgcm::HEntry*>(smem + kLongPwAt)};
+    const pkgcm::TeDual te{smem, rkr, (threadIdx.x & 31u) * 4u};
     const uint32_t lane = threadIdx.x & 31u;
 
-    const uint32_t w = first + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);   // list entries [first, n_long)
-    if (w >= n_long) return;                              // whole warps leave together
-    const uint32_t i = long_idx[w];
-    const uint8_t* src = in + in_off[i];
-    uint8_t* dst = out + out_off[i];
-    const uint32_t len = in_len[i];                       // >= long_bytes > kOverhead
-    const uint8_t* nonce = mode == 0 ? nonces + (size_t)i * pkgcm::kNonceBytes : src;
-    const uint32_t clen = mode == 0 ? len : len - pkgcm::kOverhead;
-    uint64_t yh, yl;
-    pkgcm::gcm_lane_pass(kc, te, nonce, mode == 0 ? src : src + pkgcm::kNonceBytes,
-                         mode == 0 ? dst + pkgcm::kNonceBytes : dst, clen, mode != 0, lane, yh, yl);
+    // (the warp's rank comes out of a shuffle so that the compiler KNOWS it is the same in every lane:
+    // the loop, the message's pointers and the shared-memory base of every table lookup then live in
+    // uniform registers — 40 registers instead of 63, and no extra add per AES lookup)
+    const uint32_t warp = __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0);
+    for (uint32_t w = first + warp * gridDim.x + blockIdx.x; w < n_long; w += (blockDim.x >> 5) * gridDim.x) {   // list entries [first, n_long)
+        const uint32_t i = long_idx[w];
+        const uint8_t* src = in + in_off[i];
+        uint8_t* dst = out + out_off[i];
+        const uint32_t len = in_len[i];                       // >= long_bytes > kOverhead
+        const uint8_t* nonce = mode == 0 ? nonces + (size_t)i * pkgcm::kNonceBytes : src;
+        const uint32_t clen = mode == 0 ? len : len - pkgcm::kOverhead;
+        uint64_t yh, yl;
+        uint32_t j0[4] = {0u, 0u, 0u, 0u};
+        pkgcm::gcm_lane_pass(rk, ht, te, nonce, mode == 0 ? src : src + pkgcm::kNonceBytes,
+                             mode == 0 ? dst + pkgcm::kNonceBytes : dst, clen, mode != 0, lane, yh, yl, j0);
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-        yh ^= __shfl_xor_sync(0xFFFFFFFFu, yh, d);
-        yl ^= __shfl_xor_sync(0xFFFFFFFFu, yl, d);
-    }
-    uint32_t ok = 1;
-    if (lane == 0) {
-        uint8_t tag[16];
-        pkgcm::gcm_tag(kc, te, nonce, yh, yl, tag);
-        if (mode == 0) {
-            for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];
-            for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) dst[pkgcm::kNonceBytes + len + b] = tag[b];
-        } else {
-            uint32_t diff = 0;
-            for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) diff |= (uint32_t)(tag[b] ^ src[pkgcm::kNonceBytes + clen + b]);
-            ok = diff == 0;
-            status[i] = ok ? 0u : 1u;
+        for (int d = 16; d > 0; d >>= 1) {
+            yh ^= __shfl_xor_sync(0xFFFFFFFFu, yh, d);
+            yl ^= __shfl_xor_sync(0xFFFFFFFFu, yl, d);
         }
-    }
-    if (mode != 0) {
-        ok = __shfl_sync(0xFFFFFFFFu, ok, 0);
-        if (!ok) {                                        // authentication failed: release no plaintext
-            __syncwarp();
-            for (uint32_t b = lane; b < clen; b += 32u) dst[b] = 0;
+        // the lane that owned the lengths block holds E_K(J0): it makes the tag
+        const uint32_t owner = ((clen + 15u) >> 4) & 31u;
+        uint32_t ok = 1;
+        if (lane == owner) {
+            const uint32_t tw[4] = {(uint32_t)(yh >> 32) ^ j0[0], (uint32_t)yh ^ j0[1], (uint32_t)(yl >> 32) ^ j0[2], (uint32_t)yl ^ j0[3]};
+            if (mode == 0) {
+                for (uint32_t b = 0; b < pkgcm::kNonceBytes; ++b) dst[b] = nonce[b];
+                for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b) dst[pkgcm::kNonceBytes + len + b] = (uint8_t)(tw[b >> 2] >> (24u - 8u * (b & 3u)));
+            } else {
+                uint32_t diff = 0;
+                for (uint32_t b = 0; b < pkgcm::kTagBytes; ++b)
+                    diff |= (uint32_t)src[pkgcm::kNonceBytes + clen + b] ^ ((tw[b >> 2] >> (24u - 8u * (b & 3u))) & 0xFFu);
+                ok = diff == 0;
+                status[i] = ok ? 0u : 1u;
+            }
+        }
+        if (mode != 0) {
+            ok = __shfl_sync(0xFFFFFFFFu, ok, owner);
+            if (!ok) {                                        // authentication failed: release no plaintext
+                __syncwarp();
+                for (uint32_t b = lane; b < clen; b += 32u) dst[b] = 0;
+            }
         }
     }
 }
@@ -387,6 +414,20 @@ uint32_t long_threshold(uint32_t n)
     return n < 8192u ? 256u : n < 32768u ? 1024u : 2048u;
 }
 
+// Warps per CTA of gcm_long_kernel for a batch of n_long messages (narrow blocks spread a small
+// batch over more SMs; PK_GCM_LONG_WARPS overrides), and the resident grid for it.
+uint32_t long_warps(uint32_t n_long)
+{
+    static const char* const env = std::getenv("PK_GCM_LONG_WARPS");
+    if (env && *env) { const long w = std::atol(env); return w < 1 ? 1u : w > 16 ? 16u : (uint32_t)w; }
+    return n_long >= 148u * 2u * 16u ? 16u : n_long >= 148u * 2u * 8u ? 8u : n_long >= 148u * 2u ? 2u : 1u;
+}
+uint32_t long_grid(const pk_gcm* h, uint32_t n_long, uint32_t warps)
+{
+    const uint32_t ctas = (n_long + warps - 1) / warps, resident = (uint32_t)h->num_sms * kLongCtasPerSm;
+    return ctas < resident ? ctas : resident;
+}
+
 int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const uint32_t* in_len,
         const uint8_t* nonces, uint32_t n, uint8_t* out, const uint64_t* out_off, uint32_t* status)
 {
@@ -443,7 +484,7 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
             }
             if (n_long) {
                 const uint32_t warps = n_long >= 148u * 2u ? 2u : 1u;
-                gcm_long_kernel<<<(n_long + warps - 1) / warps, warps * 32u, kSmemBytes, st>>>(
+                gcm_long_kernel<<<long_grid(h, n_long, warps), warps * 32u, kSmemBytes, st>>>(
                     h->d_kc, v_in, v_in_off, v_len, v_nonce, v_out, v_out_off, v_status, h->h_long_dev, 0u, n_long, mode);
                 PKG_CUDA(h, cudaGetLastError());
                 ++h->launches;
@@ -519,8 +560,8 @@ int run(pk_gcm* h, int mode, const uint8_t* in, const uint64_t* in_off, const ui
             ++h->launches;
         }
         if (cnt_long) {
-            const uint32_t warps = cnt_long >= 148u * 2u * 8u ? 8u : cnt_long >= 148u * 2u ? 2u : 1u;   // 16-warp CTAs measured slower
-            gcm_long_kernel<<<(cnt_long + warps - 1) / warps, warps * 32u, kSmemBytes, s_run>>>(
+            const uint32_t warps = long_warps(cnt_long);
+            gcm_long_kernel<<<long_grid(h, cnt_long, warps), warps * 32u, kSmemBytes, s_run>>>(
                 h->d_kc, h->d_in, h->d_in_off, h->d_len, h->d_nonce, h->d_out, h->d_out_off, h->d_status, h->d_long, l_lo, l_hi, mode);
             PKG_CUDA(h, cudaGetLastError());
             ++h->launches;

@@ -59,6 +59,8 @@ struct KeyContext {
     uint32_t te[4][256];        // T-tables: te[0][x] = (2·S[x], S[x], S[x], 3·S[x]) big-endian; te[k] = te[0] rotated right by 8k
     GcmTables g;
     GroupTables gg;
+    HEntry pw4[32][16];         // 4-bit Shoup tables of H^1..H^32: pw4[e-1][v] = H^e · (v << 4)(x) — the warp-per-message
+                                // kernel's closing powers, a different one per lane (8 KB for all 32; ghash_mul_table4)
 };
 static_assert(sizeof(GroupTables) % 16 == 0, "GroupTables is staged as uint4");
 static_assert(sizeof(GcmTables) % 16 == 0, "GcmTables is staged as uint4");
@@ -267,6 +269,45 @@ PKG_HD void ghash_mul_table(const HEntry* __restrict__ t, uint64_t& xh, uint64_t
     xl = zl;
 #endif
 }
+// The same product with a 4-BIT table t16[v] = V · (v << 4)(x) — sixteen entries of V's 8-bit table,
+// 256 bytes per element instead of 4 KB — walking the 32 nibbles of X from the last to the first:
+// a byte step of the walk above is two of these (low nibble, then high), because shifting right by
+// 8 with its fold is shifting right by 4 with its fold, twice, and the table is linear in the byte.
+// Twice the steps, so only where 4 KB per multiplier is too much: gcm_long_kernel's 32 closing powers.
+PKG_HD void ghash_mul_table4(const HEntry* __restrict__ t16, uint64_t& xh, uint64_t& xl)
+{
+#if defined(__CUDA_ARCH__)
+    const uint8_t* tbl = reinterpret_cast<const uint8_t*>(t16);             // shared memory, as for ghash_mul_table
+    const uint32_t x[4] = {(uint32_t)xl, (uint32_t)(xl >> 32), (uint32_t)xh, (uint32_t)(xh >> 32)};
+    uint4 e = *reinterpret_cast<const uint4*>(tbl + ((x[0] & 0xFu) << 4));
+    uint32_t z0 = e.z, z1 = e.w, z2 = e.x, z3 = e.y;
+#pragma unroll
+    for (int i = 1; i < 32; ++i) {
+        e = *reinterpret_cast<const uint4*>(tbl + (((x[i >> 3] >> (4 * (i & 7))) & 0xFu) << 4));
+        const uint32_t r = z0 << 28;                           // the four bits that fall off, at the top of a word
+        const uint32_t f = r ^ (r >> 1) ^ (r >> 2) ^ (r >> 7); // (rem<<8 ^ rem<<7 ^ rem<<6 ^ rem<<1) << 20
+        z0 = __funnelshift_r(z0, z1, 4) ^ e.z;
+        z1 = __funnelshift_r(z1, z2, 4) ^ e.w;
+        z2 = __funnelshift_r(z2, z3, 4) ^ e.x;
+        z3 = (z3 >> 4) ^ f ^ e.y;
+    }
+    xh = ((uint64_t)z3 << 32) | z2;
+    xl = ((uint64_t)z1 << 32) | z0;
+#else
+    uint64_t zh = t16[xl & 0xFu].h, zl = t16[xl & 0xFu].l;
+    for (int i = 1; i < 32; ++i) {
+        const uint64_t word = i < 16 ? xl : xh;
+        const HEntry e = t16[(word >> (4 * (i & 15))) & 0xFu];
+        const uint64_t rem = zl & 0xFu;
+        const uint64_t fold = (rem << 1) ^ (rem << 6) ^ (rem << 7) ^ (rem << 8);
+        zl = (zh << 60) | (zl >> 4);
+        zh = (zh >> 4) ^ (fold << 52) ^ e.h;
+        zl ^= e.l;
+    }
+    xh = zh;
+    xl = zl;
+#endif
+}
 PKG_HD void ghash_mul(const GcmTables* __restrict__ kc, uint64_t& xh, uint64_t& xl)
 {
     ghash_mul_table(kc->ht, xh, xl);
@@ -354,32 +395,41 @@ PKG_HD void load_nonce(const uint8_t* __restrict__ nonce, uint32_t& n0, uint32_t
 // where m = (ciphertext blocks) + 1 and the last block is the lengths block.  Lane l takes blocks
 // l, l+32, ...: Horner with H^32 over its own blocks, then one multiplication by H^(m - last block)
 // — the lanes' results XOR to X.  Returns this lane's term in (yh, yl); (0, 0) if it had no block.
-template <typename Te>
-PKG_HD void gcm_lane_pass(const GcmTables* __restrict__ kc, const Te& te, const uint8_t* __restrict__ nonce,
+// The GHASH tables arrive as a policy H (as for gcm_group_pass below): H.horner multiplies by H^32,
+// H.close(e, ..) by H^e, e = 1..32.  The lane that owns the lengths block has no AES block to
+// encrypt for it: it encrypts J0 = nonce || 1 instead and returns E_K(J0) in j0[], so the tag
+// needs no serial AES block after the lanes have met.
+struct LaneTablesPlain {
+    const KeyContext* kc;
+    PKG_HDM void horner(uint64_t& yh, uint64_t& yl) const { ghash_mul_table(kc->g.ht32, yh, yl); }
+    PKG_HDM void close(uint32_t e, uint64_t& yh, uint64_t& yl) const { ghash_mul_table4(kc->pw4[e - 1u], yh, yl); }
+};
+template <typename Te, typename H>
+PKG_HD void gcm_lane_pass(const uint32_t* __restrict__ rk, const H& ht, const Te& te, const uint8_t* __restrict__ nonce,
                           const uint8_t* __restrict__ in, uint8_t* __restrict__ out, uint32_t len,
-                          bool decrypt, uint32_t lane, uint64_t& yh, uint64_t& yl)
+                          bool decrypt, uint32_t lane, uint64_t& yh, uint64_t& yl, uint32_t j0[4])
 {
-    const uint32_t n0 = load_be32(nonce), n1 = load_be32(nonce + 4), n2 = load_be32(nonce + 8);
+    uint32_t n0, n1, n2;
+    load_nonce(nonce, n0, n1, n2);
     const uint32_t nblk = (len + 15u) >> 4;
     const uint32_t m = nblk + 1u;
     yh = 0; yl = 0;
     uint32_t last = 0xFFFFFFFFu;
     for (uint32_t b = lane; b < m; b += 32u) {
-        if (last != 0xFFFFFFFFu) ghash_mul_table(kc->ht32, yh, yl);
+        if (last != 0xFFFFFFFFu) ht.horner(yh, yl);
         if (b < nblk) {
             uint32_t c[4];
-            ctr_block(kc->rk, te, n0, n1, n2, in, out, len, b << 4, decrypt, c);
+            ctr_block(rk, te, n0, n1, n2, in, out, len, b << 4, decrypt, c);
             yh ^= ((uint64_t)c[0] << 32) | c[1];
             yl ^= ((uint64_t)c[2] << 32) | c[3];
         } else {
             yl ^= (uint64_t)len * 8u;              // the lengths block: len(A) = 0 || len(C) in bits
+            j0[0] = n0; j0[1] = n1; j0[2] = n2; j0[3] = 1u;
+            aes256_encrypt_block(te, rk, j0);
         }
         last = b;
     }
-    if (last != 0xFFFFFFFFu) {
-        const uint32_t e = m - last;               // 1..32
-        ghash_mul_bitwise(kc->pw[e - 1].h, kc->pw[e - 1].l, yh, yl);
-    }
+    if (last != 0xFFFFFFFFu) ht.close(m - last, yh, yl);       // H^(m - last), 1..32
 }
 
 // Lane-group form for SHORT messages (a secret of 32-256 bytes is 2-16 blocks: one thread walking
@@ -570,6 +620,11 @@ static inline void make_key_context(const uint8_t key[32], KeyContext& kc)
         ghash_mul_bitwise(Hh, Hl, ph, pl);
     }
     make_shoup_table(kc.g.pw[31].h, kc.g.pw[31].l, kc.g.ht32);
+    for (int e = 1; e <= 32; ++e) {                                  // 4-bit tables of the closing powers
+        HEntry t[256];
+        make_shoup_table(kc.g.pw[e - 1].h, kc.g.pw[e - 1].l, t);
+        for (int v = 0; v < 16; ++v) kc.pw4[e - 1][v] = t[v << 4];
+    }
     // the lane-group kernel's copy: round keys, tables of H^1 .. H^G
     for (int i = 0; i < 60; ++i) kc.gg.rk[i] = kc.g.rk[i];
     for (int k = 0; k < 4; ++k) kc.gg.pad[k] = 0;

@@ -56,6 +56,31 @@ extern "C" int gcmh_check_ghash(const uint8_t* key, uint64_t seed, int trials)
     return bad;
 }
 
+// ghash_mul_table4 with the 4-bit table of H^e against the bit-serial product by H^e, e = 1..32
+extern "C" int gcmh_check_table4(const uint8_t* key, uint64_t seed, int rounds)
+{
+    KeyContext kc;
+    make_key_context(key, kc);
+    int bad = 0;
+    for (int r = 0; r < rounds; ++r)
+        for (int e = 1; e <= 32; ++e) {
+            seed = seed * 6364136223846793005ull + 1442695040888963407ull; const uint64_t a = seed;
+            seed = seed * 6364136223846793005ull + 1442695040888963407ull; const uint64_t b = seed;
+            uint64_t xh = a, xl = b, yh = a, yl = b;
+            ghash_mul_table4(kc.pw4[e - 1], xh, xl);
+            ghash_mul_bitwise(kc.g.pw[e - 1].h, kc.g.pw[e - 1].l, yh, yl);
+            if (xh != yh || xl != yl) ++bad;
+        }
+    return bad;
+}
+
+// tag = X ^ E_K(J0), big-endian words to bytes
+static void lanes_tag(uint64_t xh, uint64_t xl, const uint32_t j0[4], uint8_t tag[16])
+{
+    const uint32_t t[4] = {(uint32_t)(xh >> 32) ^ j0[0], (uint32_t)xh ^ j0[1], (uint32_t)(xl >> 32) ^ j0[2], (uint32_t)xl ^ j0[3]};
+    for (int b = 0; b < 16; ++b) tag[b] = (uint8_t)(t[b >> 2] >> (24 - 8 * (b & 3)));
+}
+
 // The warp-per-message form run as a loop over 32 lanes on the host: must equal gcm_crypt_message.
 extern "C" void gcmh_seal_lanes(const uint8_t* key, const uint8_t* nonce, const uint8_t* pt, uint32_t len, uint8_t* out)
 {
@@ -63,13 +88,16 @@ extern "C" void gcmh_seal_lanes(const uint8_t* key, const uint8_t* nonce, const 
     make_key_context(key, kc);
     std::memcpy(out, nonce, 12);
     uint64_t xh = 0, xl = 0;
+    uint32_t j0[4] = {0, 0, 0, 0};
     for (uint32_t lane = 0; lane < 32; ++lane) {
         uint64_t yh, yl;
-        gcm_lane_pass(&kc.g, TeTables{kc.te}, nonce, pt, out + 12, len, false, lane, yh, yl);
+        uint32_t mine[4] = {0, 0, 0, 0};
+        gcm_lane_pass(kc.g.rk, LaneTablesPlain{&kc}, TeTables{kc.te}, nonce, pt, out + 12, len, false, lane, yh, yl, mine);
         xh ^= yh; xl ^= yl;
+        if (lane == ((len + 15u) >> 4) % 32u) std::memcpy(j0, mine, 16);      // the owner of the lengths block
     }
     uint8_t tag[16];
-    gcm_tag(&kc.g, TeTables{kc.te}, nonce, xh, xl, tag);
+    lanes_tag(xh, xl, j0, tag);
     std::memcpy(out + 12 + len, tag, 16);
 }
 
@@ -80,13 +108,16 @@ extern "C" int gcmh_open_lanes(const uint8_t* key, const uint8_t* sealed, uint32
     KeyContext kc;
     make_key_context(key, kc);
     uint64_t xh = 0, xl = 0;
+    uint32_t j0[4] = {0, 0, 0, 0};
     for (uint32_t lane = 0; lane < 32; ++lane) {
         uint64_t yh, yl;
-        gcm_lane_pass(&kc.g, TeTables{kc.te}, sealed, sealed + 12, pt, len - 28, true, lane, yh, yl);
+        uint32_t mine[4] = {0, 0, 0, 0};
+        gcm_lane_pass(kc.g.rk, LaneTablesPlain{&kc}, TeTables{kc.te}, sealed, sealed + 12, pt, len - 28, true, lane, yh, yl, mine);
         xh ^= yh; xl ^= yl;
+        if (lane == ((len - 28u + 15u) >> 4) % 32u) std::memcpy(j0, mine, 16);
     }
     uint8_t tag[16];
-    gcm_tag(&kc.g, TeTables{kc.te}, sealed, xh, xl, tag);
+    lanes_tag(xh, xl, j0, tag);
     return std::memcmp(tag, sealed + len - 16, 16) == 0 ? 0 : 1;
 }
 

@@ -43,6 +43,7 @@ def gcmh(tmp_path_factory):
     L.gcmh_group.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint32, C.c_int, C.c_char_p, C.c_char_p]
     L.gcmh_encrypt_block.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
     L.gcmh_check_ghash.argtypes = [C.c_char_p, C.c_uint64, C.c_int]
+    L.gcmh_check_table4.argtypes = [C.c_char_p, C.c_uint64, C.c_int]
     return L
 
 
@@ -75,6 +76,13 @@ def test_ghash_table_method_equals_bitwise(gcmh):
     rng = np.random.default_rng(2)
     for _ in range(20):
         assert gcmh.gcmh_check_ghash(rng.bytes(32), int(rng.integers(1, 2**62)), 200) == 0
+
+
+def test_ghash_4bit_tables_of_the_closing_powers_equal_bitwise(gcmh):
+    """pw4[e-1] (16 entries of H^e's Shoup table) walked nibble by nibble = X · H^e, e = 1..32."""
+    rng = np.random.default_rng(12)
+    for _ in range(3):
+        assert gcmh.gcmh_check_table4(rng.bytes(32), int(rng.integers(1, 2**62)), 20) == 0
 
 
 def test_seal_matches_openssl_all_lengths(gcmh):
