@@ -411,7 +411,9 @@ uint32_t long_threshold(uint32_t n)
 {
     const char* e = std::getenv("PK_GCM_LONG_BYTES");
     if (e && *e) { const long forced = std::atol(e); return forced < 64 ? 64u : (uint32_t)forced; }
-    return n < 8192u ? 256u : n < 32768u ? 1024u : 2048u;
+    // crossovers measured on B200 with both kernels as they are since round 2 (tools/bench_gcm.py "sweep",
+    // profiles/README.md): the more messages there are, the longer the lane-group kernel keeps winning
+    return n < 512u ? 256u : n < 2048u ? 512u : n < 8192u ? 1024u : n < 32768u ? 2048u : 8192u;
 }
 
 // Warps per CTA of gcm_long_kernel for a batch of n_long messages (narrow blocks spread a small
