@@ -59,11 +59,20 @@ L2_BYTES = 126 << 20
 METRIC, UNIT = "routed_requests_per_sec", "requests/s"
 DTYPE = "u8/u32/u64 integer"
 PDL = 0x100                                                        # PK_LAUNCH_PDL, include/pk_route.h
+
+
+def FUSE(m):                                                       # PK_LAUNCH_FUSE(m): m staged batches per kernel launch
+    return m << 12
+
+
 ISSUE = {"pdl4": (4 | PDL, "one CUDA graph of K kernel nodes in four parallel chains (a batch's chain = its ring position mod 4), "
                             "programmatic dependent launch inside each chain (a kernel may start while its predecessor "
                             "drains; batches are independent)"),
          "pdl": (1 | PDL, "one CUDA graph of K kernel nodes in a chain, programmatic dependent launch "
                           "(a kernel may start while its predecessor drains; batches are independent)"),
+         "fused": (1 | PDL | FUSE(32), "up to 32 staged batches per kernel launch (grid.y = batch; PK_LAUNCH_FUSE), the launches "
+                                       "in one CUDA graph chain with programmatic dependent launch — K = 20 is ONE launch, "
+                                       "whose duration a profiler can check directly"),
          "serial": (1, "one CUDA graph of K kernel nodes in a chain, each starting after its predecessor completed"),
          "plain": (0, "K plain launches")}
 C4_TOTAL = 1_000_000
@@ -403,6 +412,8 @@ def resident_leg(ctx: Ctx, workload: str, steps: int, warmup: int, issue: str, a
 
     slots = list(range(ring))
     use_graph, issue_desc = ISSUE[issue]
+    if issue == "fused":                                  # (a batch may appear once per launch: no more than the ring holds)
+        use_graph = 1 | PDL | FUSE(min(32, ring))
     # bring clocks up, then the W warm-up steps
     t_end = time.perf_counter() + (0.4 if prewarm else 0.0)
     while time.perf_counter() < t_end:
@@ -432,10 +443,10 @@ def resident_leg(ctx: Ctx, workload: str, steps: int, warmup: int, issue: str, a
         res["steady"] = (steady_steps, ms_ss)
     other = {}
     modes = (("pdl4", 4 | PDL), ("pdl", 1 | PDL), ("serial", 1), ("plain", 0), ("plain_pdl", PDL), ("four_chains", 4),
-             ("two_chains_pdl", 2 | PDL)) if all_modes \
+             ("two_chains_pdl", 2 | PDL), ("fused", 1 | PDL | FUSE(min(32, ring)))) if all_modes \
         else (("serial", 1),)
     for name, mode in modes:
-        if mode != use_graph:
+        if name != issue:
             other[name] = ctx.max(router.launch_many(slots, steps, use_graph=mode)) / steps
     res["other"] = other
     return router, res
@@ -808,7 +819,8 @@ def run_gpu(args):
         e2e["frac_of_pcie"] = (e2e["h2d_bytes_per_step"] / (e2e["ms_per_step"] / 1e3) / 1e9) / probe["peak_gbs_per_gpu"]
     router.close()
 
-    per_launch_s = ms / 1e3 / args.steps
+    per_launch_s = ms / 1e3 / args.steps                 # per step; a launch covers batches_per_launch steps (1 unless fused)
+    batches_per_launch = args.steps / max(1, res["launches"])
     value = ctx.world * args.steps * n / (ms / 1e3)
     ms_serial = res["other"].get("serial", ms / args.steps)
 
@@ -882,7 +894,9 @@ def run_gpu(args):
                      "cpu_switch_only_1core": {"value": v_sw1, "unit": UNIT, "cores": 1}}
 
     achieved = alg_bytes / per_launch_s / 1e9
-    traffic, traffic_src = ncu_traffic(workload)
+    traffic, traffic_src = ncu_traffic(workload)       # per batch on file; a launch covers batches_per_launch of them
+    if traffic is not None:
+        traffic = int(round(traffic * batches_per_launch))
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": ctx.world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -895,8 +909,10 @@ def run_gpu(args):
         "issue": res["issue_desc"] + "; CUDA events on the stream the graph is launched on",
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": ctx.peak, "unit": "GB/s",
                      "frac": achieved / ctx.peak, "traffic": traffic, "traffic_source": traffic_src,
-                     "peak_source": ctx.peak_src, "kernel": "route_kernel (fused scan+hash+select)",
-                     "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_us": per_launch_s * 1e6},
+                     "peak_source": ctx.peak_src,
+                     "kernel": ("route_fused_kernel" if batches_per_launch > 1 else "route_kernel") + " (fused scan+hash+select)",
+                     "algorithmic_bytes_per_launch": alg_bytes * batches_per_launch,
+                     "avg_launch_us": per_launch_s * batches_per_launch * 1e6, "batches_per_launch": batches_per_launch},
         "cpu_baseline": cpu_baseline,
         "e2e": e2e,
         "gpu_launches": res["launches"],
@@ -911,8 +927,9 @@ def run_gpu(args):
         k_ss, ms_ss = res.get("steady", (args.steps, ms))
         line["steady_state"] = {"steps": k_ss, "ms_per_step": ms_ss / k_ss, "value": ctx.world * k_ss * n / (ms_ss / 1e3),
                                 "unit": UNIT, "frac": alg_bytes / (ms_ss / 1e3 / k_ss) / 1e9 / ctx.peak,
-                                "note": "same issue mode, enough launches that the fill and drain of the overlapped "
-                                        "pipeline (a third of a 20-launch graph) are amortised"}
+                                "note": "same issue mode over enough steps that the ramp and the tail of the first and "
+                                        "last launch are amortised (fused: 32 batches per launch, consecutive launches "
+                                        "overlapping through programmatic dependent launch)"}
     if workloads:
         line["workloads"] = workloads
     if c4:
@@ -985,9 +1002,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS) + ["c4"])
     ap.add_argument("--c4-batch", type=int, default=4096, help="requests per batch of the C4 stream (4096 / 16384 / 65536)")
-    ap.add_argument("--issue", default="pdl4", choices=["pdl4", "pdl", "serial", "plain"],
-                    help="how the K timed launches are issued (default: a graph of four parallel chains with programmatic "
-                         "dependent launch inside each; pdl = one such chain)")
+    ap.add_argument("--issue", default="fused", choices=["fused", "pdl4", "pdl", "serial", "plain"],
+                    help="how the K timed steps are issued (default fused: up to 32 staged batches per kernel launch, the "
+                         "launches in a graph chain with programmatic dependent launch; pdl4: one launch per batch, a graph of "
+                         "four parallel chains; pdl: one such chain)")
     ap.add_argument("--depth", type=int, default=3, help="e2e pipeline depth: batches in flight through pk_submit/pk_wait")
     ap.add_argument("--no-graph", action="store_true", help="same as --issue plain")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -199,8 +199,16 @@ PK_API int  pk_wait(pk_handle* h, uint32_t slot);
  * its predecessor drains — batches are independent; a batch with long requests, which owns
  * per-request scratch in its slot, is launched without the attribute (it starts after its
  * predecessor completed).  Stream order for what follows is kept.
+ * use_graph | PK_LAUNCH_FUSE(m), 2 <= m <= 32 and m <= n_slots_in_list: every m consecutive
+ * launches of the walk become ONE kernel launch over m staged batches (grid.y = batch) — what a
+ * router with a queue of ready batches does in throughput mode: one launch latency, one ramp and
+ * one tail for all of them; the records are the same as from m launches.  Batches whose longest
+ * payloads fall in different kernel classes (<= 256 bytes, or longer) are launched one by one
+ * instead.  Fused launches run in one chain (a graph width is ignored); PK_LAUNCH_PDL applies
+ * between them.  pk_launch_count counts kernel launches, so it shows which happened.
  * pk_fetch copies the slot's records out (synchronous).                               */
 #define PK_LAUNCH_PDL 0x100
+#define PK_LAUNCH_FUSE(m) (((m) & 0xFF) << 12)
 PK_API int  pk_stage(pk_handle* h, uint32_t slot,
               const uint8_t* payload, const uint64_t* pay_off, const uint32_t* pay_len,
               const uint8_t* names, const uint32_t* name_off, uint32_t n);

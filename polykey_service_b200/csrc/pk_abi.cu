@@ -195,6 +195,25 @@ int launch_slot(pk_handle* h, const Slot& s, cudaStream_t stream, bool pdl = fal
     return PK_OK;
 }
 
+// `g` staged batches (slots list[0..g)) in one kernel launch when they share a kernel shape
+// (pk::launch_route_fused), else one launch each.
+int launch_group(pk_handle* h, Slot* const* list, uint32_t g, cudaStream_t stream, bool pdl)
+{
+    if (g >= 2 && g <= pk::kMaxFused) {
+        pk::RouteParams params[pk::kMaxFused];
+        uint32_t max_len[pk::kMaxFused];
+        for (uint32_t k = 0; k < g; ++k) { params[k] = list[k]->params; max_len[k] = list[k]->max_len; }
+        bool launched = false;
+        PK_CUDA(h, pk::launch_route_fused(params, max_len, g, h->table, h->num_sms, stream, pdl, &launched));
+        if (launched) { ++h->launches; return PK_OK; }
+    }
+    for (uint32_t k = 0; k < g; ++k) {
+        const int rc = launch_slot(h, *list[k], stream, pdl);
+        if (rc) return rc;
+    }
+    return PK_OK;
+}
+
 void free_slot(Slot& s)
 {
     if (s.d_payload) cudaFree(s.d_payload);
@@ -482,18 +501,36 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
     for (uint32_t k = 1; k < n_list; ++k) PK_CUDA(h, cudaStreamSynchronize(h->slots[slots[k]].stream));
 
     const bool pdl = (use_graph & PK_LAUNCH_PDL) != 0;
-    use_graph &= ~PK_LAUNCH_PDL;
+    const uint32_t fuse = ((uint32_t)use_graph >> 12) & 0xFFu;          // PK_LAUNCH_FUSE(m)
+    use_graph &= ~(PK_LAUNCH_PDL | PK_LAUNCH_FUSE(0xFF));
+    if (fuse > pk::kMaxFused || fuse > n_list) return PK_ERR_ARG;      // (a batch may not appear twice in one launch)
     // The walk through the slot list continues where the previous call stopped: a call never
     // starts on the batches its predecessor (a warm-up, say) touched last, which would still be
     // in L2 when the list is larger than L2 but the call is short.
     const uint64_t pos = h->ring_pos;
     h->ring_pos = (pos + count) % n_list;
     auto nth = [&](uint32_t k) -> Slot& { return h->slots[slots[(pos + k) % n_list]]; };
+    // launches k .. k+g-1 as one kernel launch (fuse >= 2) — consecutive list positions, so distinct slots
+    auto fused_run = [&](cudaStream_t stream) -> int {
+        Slot* group[pk::kMaxFused];
+        for (uint32_t k = 0; k < count; k += fuse) {
+            const uint32_t g = std::min(fuse, count - k);
+            for (uint32_t j = 0; j < g; ++j) group[j] = &nth(k + j);
+            const int rc = launch_group(h, group, g, stream, pdl);
+            if (rc) return rc;
+        }
+        return PK_OK;
+    };
     if (!use_graph) {
         PK_CUDA(h, cudaEventRecord(h->ev0, st));
-        for (uint32_t k = 0; k < count; ++k) {
-            int rc = launch_slot(h, nth(k), st, pdl);
+        if (fuse >= 2) {
+            const int rc = fused_run(st);
             if (rc) return rc;
+        } else {
+            for (uint32_t k = 0; k < count; ++k) {
+                int rc = launch_slot(h, nth(k), st, pdl);
+                if (rc) return rc;
+            }
         }
         PK_CUDA(h, cudaEventRecord(h->ev1, st));
     } else {
@@ -501,8 +538,10 @@ int pk_launch_many(pk_handle* h, const uint32_t* slots, uint32_t n_list, uint32_
         cudaGraphExec_t exec = nullptr;
         PK_CUDA(h, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
         int rc = PK_OK;
-        const uint32_t width = use_graph >= 2 ? (uint32_t)use_graph : 1u;
-        if (width == 1 || n_list < width) {
+        const uint32_t width = use_graph >= 2 && fuse < 2 ? (uint32_t)use_graph : 1u;   // fused launches: one chain
+        if (fuse >= 2) {
+            rc = fused_run(st);
+        } else if (width == 1 || n_list < width) {
             for (uint32_t k = 0; k < count && rc == PK_OK; ++k)
                 rc = launch_slot(h, nth(k), st, pdl);
         } else {

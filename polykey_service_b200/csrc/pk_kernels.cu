@@ -536,6 +536,19 @@ route_kernel(const RouteParams P, const __grid_constant__ DevTable T)
     if (P.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
+// Several batches per launch: CTA (x, y) is CTA x of batch y (FusedParams; launch_route_fused).
+template <int G, bool kWarpFinal, int B>
+__global__ void __launch_bounds__(kThreads, G == 32 ? PK_MIN_CTAS : B >= 4 ? PK_MIN_CTAS_TINY4 : PK_MIN_CTAS_TINY)
+route_fused_kernel(const __grid_constant__ FusedParams M, const __grid_constant__ DevTable T)
+{
+    if (M.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const RouteParams& P = M.b[blockIdx.y];
+    // the grid is as wide as the widest batch needs
+    const uint32_t ctas = (P.n + P.reqs_per_cta - 1u) / P.reqs_per_cta + (P.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
+    if (blockIdx.x < ctas) route_body<G, kWarpFinal, B>(P, T);
+    if (M.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 #if PK_TMA
 // Segments >= 1 of long requests, one warp per (request, segment), the bytes staged through a
 // per-warp shared-memory ring by cp.async.bulk (SASS: UBLKCP) and consumed with LDS.128.
@@ -593,9 +606,18 @@ cudaError_t launch_one(const RouteParams& p, const DevTable& table, uint32_t cta
 }
 }  // namespace
 
-cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl)
+namespace {
+struct Shape {
+    int G, B;
+    bool warp_final;
+    uint32_t ctas;
+};
+
+// Kernel shape and requests per CTA for one batch (sets p.reqs_per_cta, p.one, p.pdl).  `n_total`:
+// the requests of the whole launch (the batch itself, or every batch of a fused launch) — what the
+// "enough CTAs to fill the machine" rule counts.
+Shape choose_shape(RouteParams& p, uint32_t max_len, int num_sms, bool& pdl, uint64_t n_total)
 {
-    if (p.n == 0) return cudaSuccess;
     pdl = pdl && p.n_extra == 0u;       // long requests share their slot's scratch between launches: no overlap
     // lanes per request: a full warp, or a half / quarter warp when every payload fits one step
     // Payloads of at most 256 bytes (16 blocks): FOUR lanes per request, each taking 1, 2 or 4 blocks
@@ -622,28 +644,42 @@ cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len,
     const uint32_t r_max = G == 32 ? 64u : G == 16 ? 128u : 256u;   // G * (R + 1) <= kPartialSlots
     // enough CTAs to fill the machine (4 per SM resident), then as many requests per CTA as
     // possible so that phase 2 runs with full warps
-    uint32_t R = pow2_floor(p.n / (uint32_t)(num_sms * 4) + 1u);
+    uint32_t R = pow2_floor((uint32_t)std::min<uint64_t>(n_total / (uint64_t)(num_sms * 4) + 1u, 1u << 20));
     // A stream of batches issued with programmatic dependent launch wants the opposite shape: few,
     // fat CTAs per batch, so that many batches are resident at once and one's latency chain hides
     // behind the others' streaming (measured, C1: 1.94 µs per batch at R = 64 against 2.86 at
     // R = 8; alone, the R = 64 batch takes 15 µs).
     // No more than 256 KiB of payload per CTA, so long payloads keep the thin shape.
-    if (pdl) R = std::min(pow2_floor(p.n / 16u + 1u), pow2_floor((256u << 10) / (max_len ? max_len : 1u) + 1u));
+    // (A fused launch already holds many batches: it keeps the fill-the-machine shape, the same R
+    // for every batch in it.)
+    if (pdl && n_total == p.n) R = std::min(pow2_floor(p.n / 16u + 1u), pow2_floor((256u << 10) / (max_len ? max_len : 1u) + 1u));
     static const char* const r_env = std::getenv("PK_REQS_PER_CTA");     // tuning aid (power of two)
     if (r_env && std::atoi(r_env) > 0) R = pow2_floor((uint32_t)std::atoi(r_env));
     R = R < r_min ? r_min : R > r_max ? r_max : R;
     p.reqs_per_cta = R;
     p.one = 1u;
     p.pdl = pdl ? 1u : 0u;
-#if PK_TMA
-    const uint32_t n_extra_tma = p.n_extra;
-    p.n_extra = 0;                                  // the main kernel scans first segments only
-#endif
     const uint32_t ctas = (p.n + R - 1u) / R + (p.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
     // latency mode while one request per warp already fills the machine's resident CTA slots
     static const char* const m_env = std::getenv("PK_LATENCY_MODE");     // tuning aid: 0 / 1 forces
     bool warp_final = G == 32 && R == r_min;
     if (m_env && G == 32) warp_final = std::atoi(m_env) != 0;
+    return Shape{G, B, warp_final, ctas};
+}
+}  // namespace
+
+cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl)
+{
+    if (p.n == 0) return cudaSuccess;
+#if PK_TMA
+    const uint32_t n_extra_tma = p.n_extra;
+    if (n_extra_tma) pdl = false;                   // (as choose_shape would have decided)
+    p.n_extra = 0;                                  // the main kernel scans first segments only
+#endif
+    const Shape sh = choose_shape(p, max_len, num_sms, pdl, p.n);
+    const int G = sh.G, B = sh.B;
+    const bool warp_final = sh.warp_final;
+    const uint32_t ctas = sh.ctas;
     cudaError_t le;
     switch (G) {
     case 8:  le = B == 2 ? launch_one<8, false, 2>(p, table, ctas, stream) : launch_one<8, false, 1>(p, table, ctas, stream); break;
@@ -661,6 +697,63 @@ cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len,
         segment_kernel_tma<<<(n_extra_tma + kWarpsPerCta - 1u) / kWarpsPerCta, kThreads, kTmaSmemBytes, stream>>>(p);
     }
 #endif
+    return cudaGetLastError();
+}
+
+namespace {
+template <int G, bool kWarpFinal, int B = 1>
+cudaError_t launch_fused(const FusedParams& f, const DevTable& table, uint32_t ctas, cudaStream_t stream)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(ctas, f.m);
+    cfg.blockDim = dim3(kThreads);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = f.pdl ? 1u : 0u;
+    return cudaLaunchKernelEx(&cfg, route_fused_kernel<G, kWarpFinal, B>, f, table);
+}
+}  // namespace
+
+cudaError_t launch_route_fused(const RouteParams* batches, const uint32_t* max_len, uint32_t m, const DevTable& table,
+                               int num_sms, cudaStream_t stream, bool pdl, bool* launched)
+{
+    *launched = false;
+#if PK_TMA
+    return cudaSuccess;                             // (the TMA variant keeps its two-kernel form)
+#endif
+    if (m == 0 || m > kMaxFused) return cudaSuccess;
+    FusedParams f{};
+    uint64_t n_total = 0;
+    for (uint32_t k = 0; k < m; ++k) {
+        if (batches[k].n == 0) return cudaSuccess;
+        n_total += batches[k].n;
+        if (batches[k].n_extra) pdl = false;        // one batch with long requests: the launch waits for its predecessor
+    }
+    Shape sh{};
+    uint32_t ctas = 0;
+    for (uint32_t k = 0; k < m; ++k) {
+        f.b[k] = batches[k];
+        bool pdl_k = pdl;
+        const Shape s = choose_shape(f.b[k], max_len[k], num_sms, pdl_k, n_total);
+        if (k == 0) sh = s;
+        else if (s.G != sh.G || s.B != sh.B || s.warp_final != sh.warp_final) return cudaSuccess;
+        ctas = std::max(ctas, s.ctas);
+    }
+    f.m = m;
+    f.pdl = pdl ? 1u : 0u;
+    cudaError_t le;
+    switch (sh.G) {
+    case 8:  le = sh.B == 2 ? launch_fused<8, false, 2>(f, table, ctas, stream) : launch_fused<8, false, 1>(f, table, ctas, stream); break;
+    case 4:  le = sh.B == 4 ? launch_fused<4, false, 4>(f, table, ctas, stream)
+                : sh.B == 2 ? launch_fused<4, false, 2>(f, table, ctas, stream) : launch_fused<4, false, 1>(f, table, ctas, stream); break;
+    case 16: le = launch_fused<16, false>(f, table, ctas, stream); break;
+    default: le = sh.warp_final ? launch_fused<32, true>(f, table, ctas, stream) : launch_fused<32, false>(f, table, ctas, stream); break;
+    }
+    if (le != cudaSuccess) return le;
+    *launched = true;
     return cudaGetLastError();
 }
 

@@ -43,4 +43,19 @@ struct RouteParams {
 // table: the host copy of *p.table — it also travels as a kernel parameter (constant bank).
 cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len, int num_sms, cudaStream_t stream, bool pdl = false);
 
+// Several staged batches in ONE launch (grid.y = batch): what a router with a queue of batches does
+// in throughput mode — one launch latency, one ramp and one tail for all of them.  The batches'
+// parameter blocks travel by value (constant bank), like the table.  All batches of a launch must
+// resolve to the same kernel shape (lane-group width, blocks per lane, latency mode), which they do
+// when their longest payloads fall in the same class; otherwise *launched = false, nothing was
+// issued and the caller launches them one by one.  No batch may appear twice.
+constexpr uint32_t kMaxFused = 32;
+struct FusedParams {
+    RouteParams b[kMaxFused];
+    uint32_t    m;              // batches in this launch
+    uint32_t    pdl;
+};
+cudaError_t launch_route_fused(const RouteParams* batches, const uint32_t* max_len, uint32_t m, const DevTable& table,
+                               int num_sms, cudaStream_t stream, bool pdl, bool* launched);
+
 }  // namespace pk

@@ -46,7 +46,10 @@ def test_product_arm_line(oracle, pk):
     d = run_bench("--steps", "200", "--warmup", "5", timeout=900)
     assert BASE_KEYS <= set(d) and "impl" not in d
     assert d["n_gpus"] == 1 and d["steps"] == 200 and d["warmup"] >= 3 and d["scaling"] == "weak"
-    assert d["gpu_launches"] == 200                                   # our kernel, once per step
+    r0 = d["roofline"]
+    assert d["gpu_launches"] == -(-200 // 32) and r0["batches_per_launch"] == 200 / d["gpu_launches"]   # 32 staged batches per launch
+    assert abs(r0["algorithmic_bytes_per_launch"] / r0["batches_per_launch"] - 8_584_333) < 200_000
+    assert abs(r0["avg_launch_us"] * d["gpu_launches"] - d["ms_per_step"] * 200 * 1e3) < 1e-6 * d["ms_per_step"] * 200 * 1e3 + 1e-9
     r = d["roofline"]
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and 0 < r["frac"] < 1.2 and r["peak"] > 1000
     assert abs(r["achieved"] / r["peak"] - r["frac"]) < 1e-9
@@ -63,7 +66,7 @@ def test_product_arm_line(oracle, pk):
     assert d["config"] == C1_CONFIG
     assert "L2" in d["l2"] and "programmatic dependent launch" in d["issue"]
     modes = d["issue_modes_ms_per_step"]
-    assert {"pdl4", "pdl", "serial", "plain", "plain_pdl", "four_chains"} <= set(modes) and modes["pdl4"] == d["ms_per_step"]
+    assert {"fused", "pdl4", "pdl", "serial", "plain", "plain_pdl", "four_chains"} <= set(modes) and modes["fused"] == d["ms_per_step"]
     assert d["serial"]["ms_per_step"] == modes["serial"] and 0 < d["serial"]["frac"] <= r["frac"] * 1.25
     ss = d["steady_state"]
     assert ss["steps"] >= 2000 and 0 < ss["frac"] < 1.2 and ss["ms_per_step"] > 0

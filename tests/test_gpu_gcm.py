@@ -254,3 +254,36 @@ def test_small_batches_in_place(G):
         g.set_direct_bytes(0)
         g.seal_arena(plain, p_poff, p_lens, nonces, sealed, p_soff)
         assert g.direct_count == before + 3
+
+
+def test_in_place_with_a_nonce_array_at_an_odd_address(G):
+    """The kernels read a nonce as three words only where it is 4-byte aligned (sealed slots always
+    are; a caller's nonce array need not be): the same batch sealed in place with the nonce array
+    at offsets 0..3 of a page-locked block gives OpenSSL's bytes every time."""
+    rng = np.random.default_rng(19)
+    key = rng.bytes(32)
+    ref = AESGCM(key)
+    lens = np.array([256, 300, 511, 512, 777, 1024, 2049] + rng.integers(256, 2000, 40).tolist(), dtype=np.uint32)
+    n = lens.size
+    with G.Gcm(key, max_messages=64, max_bytes=1 << 20) as g:
+        poff, ptotal = G.slots(lens)
+        soff, stotal = G.slots(lens.astype(np.uint64) + G.OVERHEAD)
+        pin = lambda a: (lambda d: (d.__setitem__(slice(0, a.size), a), d[:a.size])[1])(g.pinned(max(a.nbytes, 16), a.dtype))
+        plain = pin(rng.integers(0, 256, max(ptotal, 16), dtype=np.uint8))
+        p_lens, p_poff, p_soff = pin(lens), pin(poff), pin(soff)
+        sealed = pin(np.zeros(max(stotal, 16), dtype=np.uint8))
+        nonce_bytes = rng.integers(0, 256, 12 * n, dtype=np.uint8)
+        block = g.pinned(12 * n + 16, np.uint8)
+        for shift in range(4):
+            nonces = block[shift:shift + 12 * n]
+            nonces[:] = nonce_bytes
+            assert nonces.ctypes.data % 4 == (block.ctypes.data + shift) % 4
+            sealed[:] = 0
+            before = g.direct_count
+            g.seal_arena(plain, p_poff, p_lens, nonces, sealed, p_soff)
+            assert g.direct_count == before + 1
+            for i in range(n):
+                nce = bytes(nonce_bytes[12 * i:12 * i + 12])
+                pt = bytes(plain[int(poff[i]):int(poff[i]) + int(lens[i])])
+                got = bytes(sealed[int(soff[i]):int(soff[i]) + int(lens[i]) + G.OVERHEAD])
+                assert got == nce + ref.encrypt(nce, pt, None), (shift, int(lens[i]))

@@ -314,6 +314,81 @@ def test_programmatic_dependent_launch(pk, oracle):
         router.close()
 
 
+def test_fused_launches(pk, oracle):
+    """PK_LAUNCH_FUSE(m): m staged batches per kernel launch.  Same records as the oracle for every
+    batch — different sizes, ragged lengths, a batch with multi-segment requests, plain / graph /
+    PDL issue, groups that do not divide the count — and the launch counter shows what happened:
+    one launch per group while the batches share a kernel class, one per batch when a tiny-payload
+    batch sits in the group."""
+    t = oracle.default_table()
+    PDL, FUSE = 0x100, lambda m: m << 12
+    batches = [oracle.gen_batch(910, 3000, 300, 4000, mode=0), oracle.gen_batch(911, 2500, 257, 900, mode=2),
+               oracle.gen_batch(912, 48, 10000, 200000, mode=0), oracle.gen_batch(913, 4096, 2048, mode=0),
+               oracle.gen_batch(914, 1, 5000, mode=0), oracle.gen_batch(915, 777, 0, 3000, mode=1)]
+    tiny = oracle.gen_batch(916, 2000, 0, 256, mode=0)                  # <= 256 bytes: the lane-group kernels
+    want = [oracle.route_batch(t, b, threads=8)[1] for b in batches + [tiny]]
+    router = pk.Router(device=0, max_requests=4096, max_payload_bytes=16 << 20, n_slots=7)
+    try:
+        for s, b in enumerate(batches + [tiny]):
+            router.stage(s, b)
+        allb = batches + [tiny]
+
+        def verify(slots, what):
+            for s in slots:
+                assert_records_equal(router.fetch(s, int(allb[s]["pay_len"].size)), want[s], f"{what} slot {s}")
+
+        same = [0, 1, 2, 3, 4, 5]
+        for mode, what in ((0, "plain"), (1, "graph"), (1 | PDL, "graph+pdl"), (PDL, "plain+pdl"), (4 | PDL, "width ignored")):
+            for m, count in ((6, 6), (2, 6), (4, 6), (3, 7), (6, 13)):
+                before = router.launch_count
+                assert router.launch_many(same, count, use_graph=mode | FUSE(m)) > 0
+                assert router.launch_count == before + -(-count // m), (what, m, count)
+                verify(same, f"{what} fuse {m} x {count}")
+        # the ring position carries over between calls and groups wrap around the list
+        for count in (1, 5, 9):
+            router.launch_many(same, count, use_graph=1 | FUSE(4))
+            verify(same, f"wrap {count}")
+        # a tiny-payload batch in the group: another kernel class -> launched one by one, same records
+        mixed = [3, 6, 0]
+        before = router.launch_count
+        router.launch_many(mixed, 3, use_graph=FUSE(3))
+        assert router.launch_count == before + 3
+        verify(mixed, "mixed classes")
+        # tiny batches together fuse too
+        r2 = [6]
+        before = router.launch_count
+        router.launch_many(r2, 1, use_graph=0)
+        assert router.launch_count == before + 1
+        # arguments: m larger than the list, or larger than 32
+        with pytest.raises(pk.PkError):
+            router.launch_many([0, 1], 2, use_graph=FUSE(3))
+        with pytest.raises(pk.PkError):
+            router.launch_many(same, 6, use_graph=FUSE(33))
+    finally:
+        router.close()
+
+
+def test_fused_tiny_batches(pk, oracle):
+    """Fused launch of lane-group (<= 256-byte payload) batches of different sizes, C2-like."""
+    t = oracle.default_table()
+    FUSE = lambda m: m << 12
+    batches = [oracle.gen_batch(920 + k, n, 0, hi, mode=0) for k, (n, hi) in enumerate(((5000, 256), (1, 200), (4096, 256), (333, 64), (2048, 128)))]
+    want = [oracle.route_batch(t, b, threads=8)[1] for b in batches]
+    router = pk.Router(device=0, max_requests=8192, max_payload_bytes=4 << 20, n_slots=5)
+    try:
+        for s, b in enumerate(batches):
+            router.stage(s, b)
+        for mode in (0, 1, 1 | 0x100):
+            before = router.launch_count
+            router.launch_many(list(range(5)), 10, use_graph=mode | FUSE(5))
+            for s in range(5):
+                assert_records_equal(router.fetch(s, int(batches[s]["pay_len"].size)), want[s], f"tiny fused mode {mode:#x} slot {s}")
+            # (batches whose block counts differ resolve to different lane-group shapes: 2 <= launches <= 10)
+            assert before + 2 <= router.launch_count <= before + 10
+    finally:
+        router.close()
+
+
 def test_long_requests_twice_scratch_is_clean(router, oracle):
     """Multi-segment requests use the per-request scratch accumulators; a second pass over the
     same slot must see them zeroed by the first."""

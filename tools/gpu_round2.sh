@@ -13,10 +13,13 @@ timeout 900 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_
 timeout 600 python bench.py --steps 20 --warmup 3 --no-cpu --no-prewarm --lean > gpurun_out/plain_c1.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_c1.csv \
     python bench.py --steps 20 --warmup 3 --no-cpu --no-prewarm --lean > gpurun_out/ncu_launches_c1.log 2>&1; echo "ncu launches rc=$?"
-for w in c1 c2 c3; do
-  timeout 600 python bench.py --workload $w --steps 6 --warmup 3 --no-cpu --no-prewarm --lean > gpurun_out/plain_$w.log 2>&1 &&
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:route_kernel -s 8 -c 2 -f -o gpurun_out/prof_$w \
-      python bench.py --workload $w --steps 6 --warmup 3 --no-cpu --no-prewarm --lean > gpurun_out/ncu_full_$w.log 2>&1; echo "ncu full $w rc=$?"
+# (default issue = fused: the 2nd route_fused_kernel launch is the first timed one — all 20 batches of c1,
+#  all 17 of c2's ring, 2 of c3's; profiles/ncu_traffic.json divides its DRAM bytes by that count)
+for cfg in "c1 20" "c2 17" "c3 6"; do
+  set -- $cfg; w=$1; k=$2
+  timeout 600 python bench.py --workload $w --steps $k --warmup 3 --no-cpu --no-prewarm --lean > gpurun_out/plain_$w.log 2>&1 &&
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:route_fused -s 1 -c 1 -f -o gpurun_out/prof_$w \
+      python bench.py --workload $w --steps $k --warmup 3 --no-cpu --no-prewarm --lean > gpurun_out/ncu_full_$w.log 2>&1; echo "ncu full $w rc=$?"
 done
 # front-end: open loop, several rates
 : > gpurun_out/frontend.jsonl
