@@ -369,8 +369,8 @@ __device__ __forceinline__ void route_body(const RouteParams& P, const DevTable&
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t wid  = threadIdx.x >> 5;
-    const uint32_t R    = P.reqs_per_cta;
-    const uint32_t n_req_ctas = (P.n + R - 1u) / R;
+    const uint32_t R    = P.reqs_per_cta;                       // a power of two (choose_shape)
+    const uint32_t n_req_ctas = (P.n + R - 1u) >> (31u - (uint32_t)__clz((int)R));
 
     if (G == 32 && blockIdx.x >= n_req_ctas) {       // (a lane-group batch has no request longer than 256 bytes)
         // ---- extra segments (>= 1) of long requests: one warp per (request, segment) ----
@@ -544,7 +544,8 @@ route_fused_kernel(const __grid_constant__ FusedParams M, const __grid_constant_
     if (M.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const RouteParams& P = M.b[blockIdx.y];
     // the grid is as wide as the widest batch needs
-    const uint32_t ctas = (P.n + P.reqs_per_cta - 1u) / P.reqs_per_cta + (P.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
+    const uint32_t ctas = ((P.n + P.reqs_per_cta - 1u) >> (31u - (uint32_t)__clz((int)P.reqs_per_cta))) +
+                          (P.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
     if (blockIdx.x < ctas) route_body<G, kWarpFinal, B>(P, T);
     if (M.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
 }

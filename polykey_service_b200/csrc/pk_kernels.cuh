@@ -31,7 +31,7 @@ struct RouteParams {
     pk_decision*    out;         // n
     uint32_t        n;
     uint32_t        n_extra;
-    uint32_t        reqs_per_cta;   // R: set by launch_route
+    uint32_t        reqs_per_cta;   // R, a power of two: set by launch_route
     uint32_t        one;            // the integer 1 (see pk_spec.cuh: keeps adds on the FMA pipe)
     uint32_t        pdl;            // launched with programmatic stream serialization: set by launch_route
 };
