@@ -369,8 +369,8 @@ __device__ __forceinline__ void route_body(const RouteParams& P, const DevTable&
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t wid  = threadIdx.x >> 5;
-    const uint32_t R    = P.reqs_per_cta;                       // a power of two (choose_shape)
-    const uint32_t n_req_ctas = (P.n + R - 1u) >> (31u - (uint32_t)__clz((int)R));
+    const uint32_t R    = P.reqs_per_cta;
+    const uint32_t n_req_ctas = P.n_req_ctas;                   // ceil(n / R), computed on the host
 
     if (G == 32 && blockIdx.x >= n_req_ctas) {       // (a lane-group batch has no request longer than 256 bytes)
         // ---- extra segments (>= 1) of long requests: one warp per (request, segment) ----
@@ -544,8 +544,7 @@ route_fused_kernel(const __grid_constant__ FusedParams M, const __grid_constant_
     if (M.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const RouteParams& P = M.b[blockIdx.y];
     // the grid is as wide as the widest batch needs
-    const uint32_t ctas = ((P.n + P.reqs_per_cta - 1u) >> (31u - (uint32_t)__clz((int)P.reqs_per_cta))) +
-                          (P.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
+    const uint32_t ctas = P.n_req_ctas + (P.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
     if (blockIdx.x < ctas) route_body<G, kWarpFinal, B>(P, T);
     if (M.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
@@ -644,7 +643,10 @@ Shape choose_shape(RouteParams& p, uint32_t max_len, int num_sms, bool& pdl, uin
     const uint32_t r_min = kWarpsPerCta * (32u / G);          // one request per lane group per pass
     const uint32_t r_max = G == 32 ? 64u : G == 16 ? 128u : 256u;   // G * (R + 1) <= kPartialSlots
     // enough CTAs to fill the machine (4 per SM resident), then as many requests per CTA as
-    // possible so that phase 2 runs with full warps
+    // possible so that phase 2 runs with full warps.  (Sizing R so that the grid is a whole number
+    // of waves of resident CTAs — 20 fused batches of 4,096 are 1.73 waves at R = 64, two full ones
+    // at R = 56 — was measured and changes nothing at K = 20, and costs 3 % in the steady state and
+    // on 256-byte payloads: the kernel is issue-bound, a thinner last wave simply runs faster.)
     uint32_t R = pow2_floor((uint32_t)std::min<uint64_t>(n_total / (uint64_t)(num_sms * 4) + 1u, 1u << 20));
     // A stream of batches issued with programmatic dependent launch wants the opposite shape: few,
     // fat CTAs per batch, so that many batches are resident at once and one's latency chain hides
@@ -654,13 +656,14 @@ Shape choose_shape(RouteParams& p, uint32_t max_len, int num_sms, bool& pdl, uin
     // (A fused launch already holds many batches: it keeps the fill-the-machine shape, the same R
     // for every batch in it.)
     if (pdl && n_total == p.n) R = std::min(pow2_floor(p.n / 16u + 1u), pow2_floor((256u << 10) / (max_len ? max_len : 1u) + 1u));
-    static const char* const r_env = std::getenv("PK_REQS_PER_CTA");     // tuning aid (power of two)
-    if (r_env && std::atoi(r_env) > 0) R = pow2_floor((uint32_t)std::atoi(r_env));
+    static const char* const r_env = std::getenv("PK_REQS_PER_CTA");     // tuning aid
+    if (r_env && std::atoi(r_env) > 0) R = ((uint32_t)std::atoi(r_env) + 3u) & ~3u;
     R = R < r_min ? r_min : R > r_max ? r_max : R;
     p.reqs_per_cta = R;
+    p.n_req_ctas = (p.n + R - 1u) / R;
     p.one = 1u;
     p.pdl = pdl ? 1u : 0u;
-    const uint32_t ctas = (p.n + R - 1u) / R + (p.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
+    const uint32_t ctas = p.n_req_ctas + (p.n_extra + kWarpsPerCta - 1u) / kWarpsPerCta;
     // latency mode while one request per warp already fills the machine's resident CTA slots
     static const char* const m_env = std::getenv("PK_LATENCY_MODE");     // tuning aid: 0 / 1 forces
     bool warp_final = G == 32 && R == r_min;

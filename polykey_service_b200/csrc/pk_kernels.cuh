@@ -31,7 +31,8 @@ struct RouteParams {
     pk_decision*    out;         // n
     uint32_t        n;
     uint32_t        n_extra;
-    uint32_t        reqs_per_cta;   // R, a power of two: set by launch_route
+    uint32_t        reqs_per_cta;   // R, a multiple of (warps per CTA) x (requests per warp pass): set by launch_route
+    uint32_t        n_req_ctas;     // ceil(n / R): set by launch_route (CTAs past it take the long requests' extra segments)
     uint32_t        one;            // the integer 1 (see pk_spec.cuh: keeps adds on the FMA pipe)
     uint32_t        pdl;            // launched with programmatic stream serialization: set by launch_route
 };

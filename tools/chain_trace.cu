@@ -68,7 +68,7 @@ int main(int argc, char** argv)
         pk::RouteParams P{};
         P.payload = arena[pos % ring]; P.pay_off = d_off; P.pay_len = d_len; P.names = d_names; P.name_off = d_noff;
         P.extra = nullptr; P.table = d_table; P.scratch = d_scr; P.out = d_out + (size_t)(pos % ring) * n; P.n = n; P.n_extra = 0;
-        P.reqs_per_cta = R; P.one = 1u; P.pdl = 1u;
+        P.reqs_per_cta = R; P.n_req_ctas = (P.n + R - 1u) / R; P.one = 1u; P.pdl = 1u;
         cudaLaunchConfig_t cfg{}; cfg.gridDim = dim3((n + R - 1) / R); cfg.blockDim = dim3(pk::kThreads); cfg.stream = s;
         cudaLaunchAttribute attr{}; attr.id = cudaLaunchAttributeProgrammaticStreamSerialization; attr.val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = &attr; cfg.numAttrs = 1;

@@ -144,7 +144,7 @@ int main(int argc, char** argv)
     pk::RouteParams P{};
     P.payload = arena; P.pay_off = pay_off; P.pay_len = pay_len; P.names = names; P.name_off = name_off;
     P.extra = nullptr; P.table = d_table; P.scratch = d_scratch; P.out = out; P.n = 1; P.n_extra = 0;
-    P.reqs_per_cta = 8; P.one = 1u; P.pdl = 0;
+    P.reqs_per_cta = 8; P.n_req_ctas = 1; P.one = 1u; P.pdl = 0;
     cudaStream_t st;
     CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     resident_router<<<1, pk::kThreads, 0, st>>>(db, P, dt, 2000000000ull /* idle: 2 s */, 30000000000ull /* life: 30 s */);
