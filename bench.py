@@ -449,6 +449,11 @@ def resident_leg(ctx: Ctx, workload: str, steps: int, warmup: int, issue: str, a
         if name != issue:
             other[name] = ctx.max(router.launch_many(slots, steps, use_graph=mode)) / steps
     res["other"] = other
+    # parity gate on the timed path itself: one more pass of the SAME issue mode over the whole ring
+    # (so slot 0 is written by the kernel that was timed, not by the single launch above), then slot
+    # 0's records against the oracle's again
+    router.launch_many(slots, ring, use_graph=use_graph)
+    assert (router.fetch(0, n) == want).all(), f"records written under issue '{issue}' differ from the oracle"
     return router, res
 
 
@@ -839,7 +844,8 @@ def run_gpu(args):
                                 "serial_ms_per_step": s2["other"].get("serial"),
                                 "e2e": {k_: e2[k_] for k_ in ("value", "unit", "ms_per_step", "steps", "h2d_bytes_per_step",
                                                               "d2h_bytes_per_step", "pipeline_depth", "copies")},
-                                "parity_gate": "slot 0 and the last e2e batch bit-exact vs the oracle"}
+                                "parity_gate": "slot 0 (single launch before timing, and again as written by the timed issue "
+                                               "mode) and the last e2e batch bit-exact vs the oracle"}
         c4 = c4_record(ctx, c4_leg(ctx, args.c4_batch, 245 * 4, 5))
     gcm_rec = None
     if not args.lean and ctx.world == 1 and workload == "c1":
@@ -916,6 +922,8 @@ def run_gpu(args):
         "cpu_baseline": cpu_baseline,
         "e2e": e2e,
         "gpu_launches": res["launches"],
+        "parity_gate": "before timing: slot 0 routed by a single launch, bit-exact vs the oracle; after timing: slot 0 as "
+                       "written by the timed issue mode, again; the last e2e batch likewise",
         "clocks": clocks,
         "issue_modes_ms_per_step": dict(res["other"], **{issue: ms / args.steps}),
         "serial": {"ms_per_step": ms_serial, "value": ctx.world * n / (ms_serial / 1e3), "unit": UNIT,
