@@ -89,15 +89,15 @@ static inline uint32_t block_scalar(uint32_t st[4], const uint8_t* blk)
 /* Blocks [r0, nb) of segment `seg` (nb <= 1024 blocks of this segment; `p` points at the
  * segment's first byte; the payload's last block may be partial: `tail` = its byte count, 0 if
  * whole), stripe states in a[32][4].  One pass: hash round + token scan per block. */
-static uint32_t segment_tail_scalar(uint32_t a[32][4], const uint8_t* p, uint32_t r0, uint32_t nb, uint32_t tail)
+static uint32_t segment_tail_scalar(uint32_t a[32][4], const uint8_t* p, uint32_t r0, uint32_t nb, uint32_t tail, uint32_t smask)
 {
     uint32_t tok = 0;
     const uint32_t whole = tail ? nb - 1u : nb;
-    for (uint32_t r = r0; r < whole; ++r) tok += block_scalar(a[r & 31u], p + (uint64_t)r * 16u);
+    for (uint32_t r = r0; r < whole; ++r) tok += block_scalar(a[r & smask], p + (uint64_t)r * 16u);
     if (tail && nb > r0) {
         uint8_t last[16] = {0};
         memcpy(last, p + (uint64_t)(nb - 1u) * 16u, tail);
-        tok += block_scalar(a[(nb - 1u) & 31u], last);
+        tok += block_scalar(a[(nb - 1u) & smask], last);
     }
     return tok;
 }
@@ -107,13 +107,14 @@ static void scan_hash_scalar(const uint8_t* p, uint32_t len, uint32_t* tok_out, 
     const uint32_t nblk = (len >> 4) + ((len & 15u) ? 1u : 0u);
     uint64_t sum = 0;
     uint32_t tok = 0;
+    const uint32_t stripes = nblk <= 16u ? 8u : 32u;                  /* SPEC v3: short payloads have 8 stripes */
     for (uint32_t first = 0, seg = 0; first < nblk; first += 1024u, ++seg) {
         const uint32_t nb = nblk - first < 1024u ? nblk - first : 1024u;
-        const uint32_t ns = nb < 32u ? nb : 32u;
+        const uint32_t ns = nb < stripes ? nb : stripes;
         uint32_t a[32][4];
         for (uint32_t s = 0; s < ns; ++s) stripe_init(a[s], seg * 32u + s);
         const uint32_t tail = (first + nb == nblk) ? (len & 15u) : 0u;
-        tok += segment_tail_scalar(a, p + (uint64_t)first * 16u, 0, nb, tail);
+        tok += segment_tail_scalar(a, p + (uint64_t)first * 16u, 0, nb, tail, stripes - 1u);
         for (uint32_t s = 0; s < ns; ++s) sum += stripe_digest(a[s]);
     }
     *tok_out = tok;
@@ -172,6 +173,7 @@ AVX512 static void scan_hash_avx512(const uint8_t* p, uint32_t len, uint32_t* to
     const __m512i iv = _mm512_setr_epi32((int)(P1 + P2), (int)P2, 0, (int)(0u - P1), (int)(P1 + P2), (int)P2, 0, (int)(0u - P1),
                                          (int)(P1 + P2), (int)P2, 0, (int)(0u - P1), (int)(P1 + P2), (int)P2, 0, (int)(0u - P1));
     const __m512i q4 = _mm512_setr_epi32(0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3);
+    const uint32_t stripes = nblk <= 16u ? 8u : 32u;                  /* SPEC v3: short payloads have 8 stripes = 2 registers */
     for (uint32_t first = 0, seg = 0; first < nblk; first += 1024u, ++seg) {
         const uint32_t nb = nblk - first < 1024u ? nblk - first : 1024u;
         const uint32_t tail = (first + nb == nblk) ? (len & 15u) : 0u;
@@ -191,8 +193,9 @@ AVX512 static void scan_hash_avx512(const uint8_t* p, uint32_t len, uint32_t* to
                 tok += tokens64(x);
             }
         }
-        for (int v = 0; r + 4u <= whole; r += 4u, ++v) {              /* 64-byte steps */
+        for (; r + 4u <= whole; r += 4u) {                            /* 64-byte steps */
             const __m512i x = _mm512_loadu_si512((const void*)(sp + (uint64_t)r * 16u));
+            const int v = (int)((r & (stripes - 1u)) >> 2);
             st[v] = round512(st[v], x);
             tok += tokens64(x);
         }
@@ -201,13 +204,13 @@ AVX512 static void scan_hash_avx512(const uint8_t* p, uint32_t len, uint32_t* to
             const uint32_t bytes = (left - (tail ? 1u : 0u)) * 16u + tail;
             const __mmask64 km = bytes >= 64u ? ~0ull : ((1ull << bytes) - 1ull);
             const __m512i x = _mm512_maskz_loadu_epi8(km, (const void*)(sp + (uint64_t)r * 16u));
-            const int v = (int)((r & 31u) >> 2);
+            const int v = (int)((r & (stripes - 1u)) >> 2);
             const __mmask16 blocks = (__mmask16)((1u << (4u * left)) - 1u);   /* only stripes that own a block advance */
             st[v] = _mm512_mask_mov_epi32(st[v], blocks, round512(st[v], x));
             tok += tokens64(x);
         }
         /* digests of the stripes that saw a block */
-        const uint32_t ns = nb < 32u ? nb : 32u;
+        const uint32_t ns = nb < stripes ? nb : stripes;
         for (uint32_t v = 0; v * 4u < ns; ++v) {
             __m512i d = digest512(st[v]);
             const uint32_t have = ns - v * 4u;                        /* stripes of this register in use */

@@ -40,6 +40,8 @@
 /* ---- SPEC constants (duplicated on purpose from the product's pk_spec.cuh) ---- */
 #define SPEC_BLOCK        16u
 #define SPEC_STRIPES      32u
+#define SPEC_TINY_BLOCKS  16u      /* payloads of at most this many blocks ... */
+#define SPEC_TINY_STRIPES 8u       /* ... have this many stripes */
 #define SPEC_SEG_BLOCKS   1024u                 /* 16 KiB segments                 */
 #define SPEC_P1           0x9E3779B1u
 #define SPEC_P2           0x85EBCA77u
@@ -121,18 +123,21 @@ uint64_t pk_ref_payload_sum(const uint8_t* p, uint64_t len)
     uint64_t nblk = (len + SPEC_BLOCK - 1) / SPEC_BLOCK;
     uint64_t nseg = (nblk + SPEC_SEG_BLOCKS - 1) / SPEC_SEG_BLOCKS;
     uint64_t sum = 0;
+    /* SPEC v3: a payload of at most 16 blocks (256 bytes) has 8 stripes, not 32 — blocks k and
+     * k + 8 share one — so that a short payload pays half as many stripe digests */
+    const uint32_t stripes = nblk <= SPEC_TINY_BLOCKS ? SPEC_TINY_STRIPES : SPEC_STRIPES;
     for (uint64_t seg = 0; seg < nseg; ++seg) {
         uint64_t first = seg * SPEC_SEG_BLOCKS;
         uint64_t in_seg = nblk - first;
         if (in_seg > SPEC_SEG_BLOCKS) in_seg = SPEC_SEG_BLOCKS;
-        for (uint32_t s = 0; s < SPEC_STRIPES && s < in_seg; ++s) {
+        for (uint32_t s = 0; s < stripes && s < in_seg; ++s) {
             uint32_t q = (uint32_t)(seg * SPEC_STRIPES + s);
             uint32_t a[4];
             a[0] = SPEC_P1 + SPEC_P2 + q * SPEC_P5;
             a[1] = SPEC_P2 + q * SPEC_P5;
             a[2] = 0u + q * SPEC_P5;
             a[3] = 0u - SPEC_P1 + q * SPEC_P5;
-            for (uint64_t r = s; r < in_seg; r += SPEC_STRIPES) {
+            for (uint64_t r = s; r < in_seg; r += stripes) {
                 uint64_t at = (first + r) * SPEC_BLOCK;
                 for (unsigned j = 0; j < 4; ++j) {
                     uint32_t w = load_le32_padded(p, len, at + 4u * j);

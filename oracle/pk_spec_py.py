@@ -55,9 +55,10 @@ def payload_sum(p: bytes):
     nblk = (len(p) + 15) // 16
     padded = p + b"\0" * (nblk * 16 - len(p))
     stripes = {}                                      # q -> state, insertion in block order
+    width = 8 if nblk <= 16 else 32                   # SPEC v3: payloads of at most 16 blocks have 8 stripes
     for k in range(nblk):
         seg, r = divmod(k, 1024)
-        q = (seg * 32 + (r % 32)) & M32
+        q = (seg * 32 + (r % width)) & M32
         if q not in stripes:
             base = (q * P5) & M32
             stripes[q] = [(P1 + P2 + base) & M32, (P2 + base) & M32, base, (base - P1) & M32]

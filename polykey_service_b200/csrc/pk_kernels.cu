@@ -116,6 +116,7 @@ __device__ __forceinline__ void scan_segment(const uint8_t* __restrict__ pay, ui
                                              uint64_t& digest, uint32_t& tok, TmaRing ring = TmaRing{nullptr, nullptr})
 {
     const uint32_t nblk   = (len >> 4) + ((len & 15u) ? 1u : 0u);
+    const bool     tiny   = nblk <= kTinyBlocks;                    // SPEC v3: 8 stripes instead of 32 (see the remainder loop)
     const uint32_t first  = seg * kSegBlocks;
     const uint32_t nb     = min(kSegBlocks, nblk - first);          // blocks of this segment
     const uint32_t nwhole = min(kSegBlocks, (len >> 4) - first);    // ... lying wholly inside the payload
@@ -184,12 +185,23 @@ __device__ __forceinline__ void scan_segment(const uint8_t* __restrict__ pay, ui
             if (k < nb) {
                 const uint32_t valid = len - (first + k) * kBlockBytes;   // >= 1
                 if (valid < kBlockBytes) mask_tail(w, valid);
-                stripe_round(st, w);
+                if (!tiny) stripe_round(st, w);
             }
-            scan_block(w, one, tok128);          // an all-zero block counts nothing
+            if (tiny) {                          // warp-uniform; only u == 0 gets here (nb <= 16)
+                // SPEC v3: a payload of at most 16 blocks has 8 stripes — lane l < 8 folds block l and
+                // then block l + 8, which lane l + 8 loaded and masked (the words move in place, after
+                // the lane has counted its own block's tokens: no extra registers)
+                if (lane < kTinyStripes && lane < nb) stripe_round(st, w);
+                scan_block(w, one, tok128);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) w.w[j] = __shfl_down_sync(0xFFFFFFFFu, w.w[j], kTinyStripes);
+                if (lane + kTinyStripes < nb && lane < kTinyStripes) stripe_round(st, w);
+            } else {
+                scan_block(w, one, tok128);      // an all-zero block counts nothing
+            }
         }
     }
-    digest = (lane < nb) ? stripe_digest(st) : 0ull;
+    digest = (lane < (tiny ? min(nb, kTinyStripes) : nb)) ? stripe_digest(st) : 0ull;
     tok    = tok128 >> 7;
 }
 
@@ -201,23 +213,31 @@ template <int G, int B>
 __device__ __forceinline__ void scan_tiny(const uint4 (&x)[B], uint32_t len, uint32_t lig, uint32_t one,
                                           uint64_t& digest, uint32_t& tok)
 {
+    // SPEC v3: a payload of at most 16 blocks has kTinyStripes = 8 stripes, block k in stripe k mod 8.
+    // This lane's blocks are lig, lig + G, ...: they fall into kPer = 8 / G stripes (two for four
+    // lanes, one for eight), which the lane keeps and finalises — half as many digests as blocks
+    // once a payload is longer than 128 bytes.
+    static_assert(G == 4 || G == 8, "lane groups of 4 or 8: a stripe never spans two lanes");
+    constexpr int kPer = (int)kTinyStripes / G;
     const uint32_t nblk = (len + 15u) >> 4;                            // <= G * B
     uint32_t tok128 = 0;
-    digest = 0ull;
+    Stripe st[kPer];
 #pragma unroll
     for (int b = 0; b < B; ++b) {
         const uint32_t k = lig + (uint32_t)b * G;
+        if (b < kPer) stripe_init(st[b], k);                           // (k < 8 here: the stripe's own number)
         if (k < nblk) {
             Words4 w = {{x[b].x, x[b].y, x[b].z, x[b].w}};
             const uint32_t valid = len - k * kBlockBytes;
             if (valid < kBlockBytes) mask_tail(w, valid);
-            Stripe st;
-            stripe_init(st, k);
-            stripe_round(st, w);
-            digest += stripe_digest(st);
+            stripe_round(st[b % kPer], w);
             scan_block(w, one, tok128);
         }
     }
+    digest = 0ull;
+#pragma unroll
+    for (int q = 0; q < kPer && q < B; ++q)
+        if (lig + (uint32_t)q * G < nblk) digest += stripe_digest(st[q]);
     tok = tok128 >> 7;
 }
 
@@ -431,7 +451,7 @@ __device__ __forceinline__ void route_body(const RouteParams& P, const DevTable&
     }
 
     // ---- phase 1: scan (first segment of) each request ----
-    if (G == 32) {
+    if constexpr (G == 32) {
         // the next request's length and offset are loaded while this one is scanned
         uint32_t len_next = 0u;
         uint64_t off_next = 0ull;
@@ -625,15 +645,14 @@ Shape choose_shape(RouteParams& p, uint32_t max_len, int num_sms, bool& pdl, uin
     // block (round 1) and 8 x 2 the loop overhead per request and the partial sums phase 2 adds up
     // halve each time; the four loads in flight per lane cost registers (40: six CTAs per SM instead
     // of eight), which the measurement pays for: 65,536 x 256 B under the bench's issue 5.01 µs per
-    // batch at 4 x 4 against 5.15 at 8 x 2 (PK_TINY_SHAPE=8 / 16 select the older shapes).
+    // batch at 4 x 4 against 5.15 at 8 x 2 (PK_TINY_SHAPE=8 selects the older shape).
     static const char* const t_env = std::getenv("PK_TINY_SHAPE");
     const int t_shape = t_env ? std::atoi(t_env) : 4;
     int G = 32, B = 1;
     if (max_len <= 16u * kBlockBytes) {
         const uint32_t nblk_max = (max_len + kBlockBytes - 1u) / kBlockBytes;
         G = 4; B = nblk_max <= 4u ? 1 : nblk_max <= 8u ? 2 : 4;
-        if (t_shape == 8 || (t_shape == 16 && nblk_max <= 8u)) { G = 8; B = nblk_max <= 8u ? 1 : 2; }
-        else if (t_shape == 16) { G = 16; B = 1; }
+        if (t_shape == 8) { G = 8; B = nblk_max <= 8u ? 1 : 2; }   // (16 lanes x 1 block went with SPEC v3: a stripe would span two lanes)
     }
     // Few tiny requests: a warp each (latency mode below) beats packing them 2 or 4 to a warp —
     // the packed path pays a CTA barrier and a second phase that only pay off when warps are scarce.
@@ -689,7 +708,6 @@ cudaError_t launch_route(RouteParams p, const DevTable& table, uint32_t max_len,
     case 8:  le = B == 2 ? launch_one<8, false, 2>(p, table, ctas, stream) : launch_one<8, false, 1>(p, table, ctas, stream); break;
     case 4:  le = B == 4 ? launch_one<4, false, 4>(p, table, ctas, stream)
                 : B == 2 ? launch_one<4, false, 2>(p, table, ctas, stream) : launch_one<4, false, 1>(p, table, ctas, stream); break;
-    case 16: le = launch_one<16, false>(p, table, ctas, stream); break;
     default: le = warp_final ? launch_one<32, true>(p, table, ctas, stream) : launch_one<32, false>(p, table, ctas, stream); break;
     }
     if (le != cudaSuccess) return le;
@@ -753,7 +771,6 @@ cudaError_t launch_route_fused(const RouteParams* batches, const uint32_t* max_l
     case 8:  le = sh.B == 2 ? launch_fused<8, false, 2>(f, table, ctas, stream) : launch_fused<8, false, 1>(f, table, ctas, stream); break;
     case 4:  le = sh.B == 4 ? launch_fused<4, false, 4>(f, table, ctas, stream)
                 : sh.B == 2 ? launch_fused<4, false, 2>(f, table, ctas, stream) : launch_fused<4, false, 1>(f, table, ctas, stream); break;
-    case 16: le = launch_fused<16, false>(f, table, ctas, stream); break;
     default: le = sh.warp_final ? launch_fused<32, true>(f, table, ctas, stream) : launch_fused<32, false>(f, table, ctas, stream); break;
     }
     if (le != cudaSuccess) return le;

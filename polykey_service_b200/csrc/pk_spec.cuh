@@ -23,6 +23,8 @@ constexpr uint32_t kBlockBytes   = 16;      // one 16-byte block = one lane's ve
 constexpr uint32_t kStripes      = 32;      // stripes per segment = warp width
 constexpr uint32_t kSegBlocks    = 1024;    // blocks per segment (16 KiB)
 constexpr uint32_t kSegBytes     = kSegBlocks * kBlockBytes;
+constexpr uint32_t kTinyBlocks   = 16;      // SPEC v3: a payload of at most 16 blocks (256 bytes) ...
+constexpr uint32_t kTinyStripes  = 8;       // ... has 8 stripes (block k in stripe k mod 8), not 32
 constexpr uint32_t kP1 = 0x9E3779B1u, kP2 = 0x85EBCA77u, kP5 = 0x165667B1u;
 constexpr uint64_t kNameMul = 0xD6E8FEB86659FD93ull;
 constexpr uint64_t kFmixC1 = 0xFF51AFD7ED558CCDull, kFmixC2 = 0xC4CEB9FE1A85EC53ull;

@@ -16,19 +16,25 @@ using namespace pk;
 namespace {
 struct Partial { uint64_t sum; uint32_t tok; };
 
-// one (request, segment) task walked the way scan_segment() in pk_kernels.cu walks it:
-// lane l owns blocks 32*i + l of the segment, with its own stripe and token counter
+// one (request, segment) task walked the way the kernels walk it.  A block k of the segment belongs
+// to stripe k % width (width = 8 for payloads of at most 16 blocks, else 32) and is folded by lane
+// k % min(lanes, width): the full warp's lane l owns blocks l, l + 32, ... (scan_segment), and for a
+// short payload lanes 0..7 fold blocks l and l + 8; a lane group of 4 or 8 lanes (scan_tiny) gives
+// lane l the blocks l, l + G, ... and with them the one or two stripes those fall into.  Each lane
+// keeps its own stripes and token counter; the merge is a commutative sum.
 Partial scan_segment_emul(const uint8_t* pay, uint32_t len, uint32_t seg, uint32_t lanes)
 {
     const uint32_t nblk = (len >> 4) + ((len & 15u) ? 1u : 0u);
     const uint32_t first = seg * kSegBlocks;
     const uint32_t nb = (nblk - first) < kSegBlocks ? (nblk - first) : kSegBlocks;
+    const uint32_t width = nblk <= kTinyBlocks ? kTinyStripes : kStripes;
+    const uint32_t owners = lanes < width ? lanes : width;
     Partial p{0, 0};
-    for (uint32_t lane = 0; lane < lanes; ++lane) {
-        Stripe st;
-        stripe_init(st, seg * kStripes + lane);
+    for (uint32_t lane = 0; lane < owners; ++lane) {
+        Stripe st[2];
+        bool used[2] = {false, false};
         uint32_t tok128 = 0;
-        for (uint32_t k = lane; k < nb; k += lanes) {
+        for (uint32_t k = lane; k < nb; k += owners) {
             // the device reads a full 16-byte block even past the payload end (arena padding
             // holds garbage there): emulate with 0xEE filler, then mask as the kernel does
             uint8_t raw[16];
@@ -38,18 +44,21 @@ Partial scan_segment_emul(const uint8_t* pay, uint32_t len, uint32_t seg, uint32
             Words4 w;
             std::memcpy(&w, raw, 16);
             if (valid < 16) mask_tail(w, valid);
-            stripe_round(st, w);
+            const uint32_t s = k % width;                      // the block's stripe
+            const uint32_t slot = (s / owners) & 1u;           // a lane owns width / owners <= 2 stripes
+            if (!used[slot]) { stripe_init(st[slot], seg * kStripes + s); used[slot] = true; }
+            stripe_round(st[slot], w);
             scan_block(w, 1u, tok128);
         }
-        if (lane < nb) p.sum += stripe_digest(st);
+        for (int slot = 0; slot < 2; ++slot)
+            if (used[slot]) p.sum += stripe_digest(st[slot]);
         p.tok += tok128 >> 7;
     }
     return p;
 }
 }  // namespace
 
-// lanes = 32 (full warp) or 16 / 8 (the tiny-payload lane groups; valid when the payload has
-// at most `lanes` blocks, where both walks visit the same (stripe, block) pairs)
+// lanes = 32 (full warp) or 4 / 8 (the tiny-payload lane groups: payloads of at most 16 blocks)
 extern "C" void emul_route_one(const pk_table* t, const uint8_t* pay, uint32_t len,
                                const uint8_t* name, uint32_t nlen, uint32_t lanes, pk_decision* d)
 {

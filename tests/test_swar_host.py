@@ -52,9 +52,10 @@ def test_warp_emulation_golden(emul, oracle):
         assert {k: int(r[k]) for k in r.dtype.names} == want, (nm, len(p))
 
 
-@pytest.mark.parametrize("lanes,maxlen", [(16, 256), (8, 128)])
+@pytest.mark.parametrize("lanes,maxlen", [(4, 256), (8, 256), (4, 64), (8, 128)])
 def test_lane_group_emulation(emul, oracle, lanes, maxlen):
-    """The 16- and 8-lane groups used for batches of tiny payloads."""
+    """The 4- and 8-lane groups used for batches of tiny payloads (8 stripes: a lane folds the
+    blocks l, l + G, ... into the one or two stripes they fall into)."""
     t = oracle.default_table()
     for mode in range(5):
         b = oracle.gen_batch(77 + mode, 300, 0, maxlen, mode=mode)
