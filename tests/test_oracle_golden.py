@@ -162,3 +162,56 @@ def test_fast_cpu_port_equals_plain_oracle(oracle, mode, impl, monkeypatch):
     finally:
         monkeypatch.delenv("PK_CPU_FAST_IMPL")
         oracle.lib().pk_cpu_fast_reselect()
+
+
+@pytest.mark.parametrize("impl", ["avx512", "scalar"])
+def test_spec_v3_stripe_boundary(oracle, impl, monkeypatch):
+    """SPEC v3: payloads of at most 16 blocks (256 bytes) have 8 stripes, longer ones 32.  Every
+    length from 0 to 300 bytes — both sides of the boundary, every partial last block — through the
+    plain oracle, the timed CPU port (both inner loops) and the independent Python restatement; and
+    the boundary is where it should be: a 256-byte payload's sum changes if it is hashed with 32
+    stripes, a 257-byte payload's if hashed with 8."""
+    from oracle import pk_spec_py as S
+    monkeypatch.setenv("PK_CPU_FAST_IMPL", impl)
+    oracle.lib().pk_cpu_fast_reselect()
+    try:
+        if impl == "avx512" and oracle.fast_impl() != "avx512":
+            pytest.skip("this CPU has no AVX-512")
+        t = oracle.default_table()
+        tools = [(bytes(t.tools[k].name[:t.tools[k].name_len]), t.tools[k].class_id) for k in range(t.n_tools)]
+        provs = [(p.max_tokens, p.weight, p.tool_mask, p.reserved) for p in list(t.providers)[:t.n_providers]]
+        rng = np.random.default_rng(316)
+        reqs = [(b"example_tool", rng.integers(1, 256, l, dtype=np.uint8).tobytes()) for l in range(301)]
+        b = oracle.pack_batch(reqs)
+        plain = oracle.route_batch(t, b, threads=2)[1]
+        rc, fast = oracle.route_batch(t, b, threads=3, fast=True)
+        assert rc == 0 and (fast == plain).all(), np.nonzero(fast != plain)[0][:8]
+        for (nm, p), rec in zip(reqs, plain):
+            assert record_as_dict(rec) == S.route_one(tools, 3, provs, nm, p), len(p)
+    finally:
+        monkeypatch.delenv("PK_CPU_FAST_IMPL")
+        oracle.lib().pk_cpu_fast_reselect()
+
+    def sum_with(p, width):                          # the payload sum with a forced stripe count
+        nblk = (len(p) + 15) // 16
+        padded = p + b"\0" * (nblk * 16 - len(p))
+        st = {}
+        for k in range(nblk):
+            q = k % width
+            if q not in st:
+                base = (q * S.P5) & S.M32
+                st[q] = [(S.P1 + S.P2 + base) & S.M32, (S.P2 + base) & S.M32, base, (base - S.P1) & S.M32]
+            a = st[q]
+            for j in range(4):
+                w = int.from_bytes(padded[16 * k + 4 * j:16 * k + 4 * j + 4], "little")
+                a[j] = (S.rotl((a[j] + w * S.P2) & S.M32, 13) * S.P1) & S.M32
+        total = 0
+        for a in st.values():
+            lo = (S.rotl(a[0], 1) + S.rotl(a[1], 7) + S.rotl(a[2], 12) + S.rotl(a[3], 18)) & S.M32
+            hi = (S.rotl(a[0], 24) + S.rotl(a[1], 3) + S.rotl(a[2], 19) + S.rotl(a[3], 10)) & S.M32
+            total = (total + S.fmix64((hi << 32) | lo)) & S.M64
+        return total
+
+    p256, p257 = reqs[256][1], reqs[257][1]
+    assert S.payload_sum(p256) == sum_with(p256, 8) != sum_with(p256, 32)
+    assert S.payload_sum(p257) == sum_with(p257, 32) != sum_with(p257, 8)
