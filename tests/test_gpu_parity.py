@@ -90,6 +90,19 @@ def test_length_edges(router, oracle, length):
         check(router, oracle, b, f"len {length} mode {mode}")
 
 
+def test_spec_v3_stripe_boundary_on_gpu(pk, router, oracle):
+    """SPEC v3 (8 stripes up to 256 bytes, 32 above): every length 0..300 in one batch — the
+    full-warp kernel, whose lanes 0..7 fold blocks l and l + 8 of a short payload — and every length
+    0..256 many times over in a batch of short payloads only — the four-lane kernels, at each of
+    their blocks-per-lane shapes."""
+    rng = np.random.default_rng(317)
+    mixed = [(b"struct_tool", rng.integers(1, 256, l, dtype=np.uint8).tobytes()) for l in range(301)]
+    check(router, oracle, pk.pack_requests(mixed), "lengths 0..300, one each")
+    for top in (64, 128, 256):
+        short = [(b"file_tool", rng.integers(1, 256, l % (top + 1), dtype=np.uint8).tobytes()) for l in range(6000)]
+        check(router, oracle, pk.pack_requests(short), f"6000 payloads of 0..{top} bytes")
+
+
 def test_empty_batch_and_empty_fields(pk, router, oracle):
     out = router.route_batch(pk.pack_requests([]))
     assert out.size == 0
